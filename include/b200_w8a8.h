@@ -1,0 +1,143 @@
+/* b200_w8a8 -- C ABI of the B200-native (sm_100a) W8A8 quantized-linear library.
+ *
+ * This is the drop-in boundary under the `torch.ops.sgl_kernel.*` operators of the
+ * reference (analytics-zoo/sglang-diffusion): plain pointers, sizes and a CUDA
+ * stream; no torch types.  Every entry point names the reference interface it
+ * replaces (paths relative to the reference root).  The torch registration shim
+ * (sglang-diffusion_b200/csrc/torch_ops.cpp) and the ctypes binding
+ * (sglang-diffusion_b200/capi.py) are both thin callers of these functions.
+ *
+ * Conventions
+ *  - All data pointers are DEVICE pointers valid on the current CUDA device; the
+ *    call enqueues work on `stream` and returns without synchronising.  Calls are
+ *    CUDA-graph capturable (no allocation, no sync, no host round trip).
+ *  - Return value: 0 on success, a negative B2_ERR_* code otherwise;
+ *    b2_last_error() returns a thread-local human-readable message.
+ *  - Weights `W` are the checkpoint layout [N, K], K contiguous (the reference
+ *    passes the same memory as mat_b = weight.t(), i.e. logical [K,N] with
+ *    stride(0) == 1; `ldw` = mat_b.stride(1)).
+ *  - `ld*` are row strides in ELEMENTS.
+ *  - There is no CPU fallback: on a device that is not sm_100 every compute entry
+ *    returns B2_ERR_ARCH.
+ */
+#ifndef B200_W8A8_H_
+#define B200_W8A8_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_ABI_VERSION 1
+
+/* element types (activations in, outputs, bias) */
+#define B2_DTYPE_BF16 0
+#define B2_DTYPE_F16 1
+#define B2_DTYPE_F32 2
+#define B2_DTYPE_S32 3 /* output only: raw int32 accumulators of b2_gemm_s8 (verification) */
+
+/* status codes */
+#define B2_OK 0
+#define B2_ERR_ARG (-1)   /* shape / alignment / dtype violation (message says which) */
+#define B2_ERR_ARCH (-2)  /* device is not sm_100 (B200) */
+#define B2_ERR_CUDA (-3)  /* a CUDA runtime / driver call failed */
+
+typedef void* b2_stream_t; /* cudaStream_t */
+
+int b2_abi_version(void);
+const char* b2_last_error(void);
+
+/* SM count and compute capability of the current device (cached per device). */
+int b2_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- activation quantizers ------------------------------------------------ */
+
+/* Per-token symmetric int8 quantization with the arithmetic of the reference CPU op
+ * per_token_quant_int8_cpu (sgl-kernel/csrc/cpu/gemm_int8.cpp:382-410,
+ * vec.h:190-228): amax = max(max|x|,1e-7), s = amax/127, q = RNE(x*(127/amax)).
+ * Also the GPU replacement for the Triton per_token_quant_int8
+ * (python/sglang/srt/layers/quantization/int8_kernel.py:28-89).
+ * q is SIGNED int8 (= reference u8 code - 128).  x_dtype: BF16 or F16. */
+int b2_quant_int8_rows(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s, int M, int K,
+                       b2_stream_t stream);
+
+/* Per-token e4m3 quantization: sgl_per_token_quant_fp8
+ * (sgl-kernel/csrc/gemm/per_token_quant_fp8.cu:242-314; kernel :17-121).
+ * s = max|x|/448, q = e4m3_rn_satfinite(clamp(x*(1/s), +-448)); all-zero row -> s=0, q=0. */
+int b2_quant_fp8_rows(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s, int M, int K,
+                      b2_stream_t stream);
+
+/* 1x128 group e4m3 quantization with fp32 scales: sgl_per_token_group_quant_8bit
+ * (sgl-kernel/csrc/gemm/per_token_group_quant_8bit.cu:116-217; kernel :19-114)
+ * with group_size = 128, scale_ue8m0 = false.  Scale of (row m, group g) is written to
+ * s[m*s_row_stride + g*s_grp_stride]: (1, M) gives the column-major / M-major layout the
+ * block-wise GEMM consumes, (K/128, 1) the row-major one. */
+int b2_quant_fp8_group128(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s,
+                          int64_t s_row_stride, int64_t s_grp_stride, int M, int K, float eps, float fp8_min,
+                          float fp8_max, b2_stream_t stream);
+
+/* ---- scaled GEMMs ---------------------------------------------------------- */
+
+/* int8_scaled_mm (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:663-747 -- which has NO
+ * sm_100 path) with the bit-exact epilogue of the reference CPU op int8_scaled_mm_cpu
+ * (sgl-kernel/csrc/cpu/gemm_int8.cpp:422-478; scale_C :20-60):
+ *     D[m,n] = out_t( fma( f32(acc)*As[m], Bs[n], bias[n] ) )   (no bias: (f32(acc)*As)*Bs)
+ * acc = exact s8 x s8 -> s32 dot over K.  out_dtype BF16/F16, or S32 for the raw
+ * accumulators (As/Bs/bias ignored).  bias may be NULL; bias_dtype BF16/F16/F32.
+ * Requires K % 16 == 0, N % 8 == 0 (as the reference, :677-679), 16-byte aligned bases. */
+int b2_gemm_s8(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
+               const void* bias, int bias_dtype, void* D, int64_t ldd, int out_dtype, int M, int N, int K,
+               b2_stream_t stream);
+
+/* fp8_scaled_mm (sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1450-1532; sm100 kernel
+ * :796-1170):  D = out_t( As[m] * (Bs[n] * f32(A.W^T)) [+ bias] ), e4m3 x e4m3, f32 accumulate.
+ * out_dtype BF16/F16/F32. */
+int b2_gemm_e4m3(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* As, const float* Bs,
+                 const void* bias, int bias_dtype, void* D, int64_t ldd, int out_dtype, int M, int N, int K,
+                 b2_stream_t stream);
+
+/* fp8_blockwise_scaled_mm (sgl-kernel/csrc/gemm/fp8_blockwise_gemm_kernel.cu:368-465):
+ *     D[m,n] = out_t( sum_kb SFA[m,kb] * SFB[n/128,kb] * f32(A_kb . W_kb^T) [+ bias] )
+ * SFA element (m,kb) at sfa[m*sfa_m_stride + kb*sfa_k_stride] (reference: M-major => (1, M));
+ * SFB element (nb,kb) at sfb[nb*sfb_n_stride + kb*sfb_k_stride].  The reference op has no
+ * bias (fp8_utils.py:546-547 adds it in a second kernel); here it may be fused (NULL = none). */
+int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* sfa,
+                          int64_t sfa_m_stride, int64_t sfa_k_stride, const float* sfb, int64_t sfb_n_stride,
+                          int64_t sfb_k_stride, const void* bias, int bias_dtype, void* D, int64_t ldd,
+                          int out_dtype, int M, int N, int K, b2_stream_t stream);
+
+/* ---- fused linear ----------------------------------------------------------- */
+
+/* int8_scaled_mm_with_quant (sgl-kernel/csrc/cpu/gemm_int8.cpp:481-547):
+ * bf16/f16 activations in, per-token int8 quantization, int8 GEMM, scaled + biased output
+ * of the same dtype.  `workspace` must hold b2_linear_w8a8_int8_workspace(M, K) bytes
+ * (quantized activations + row scales; stays L2-resident between the two kernels). */
+size_t b2_linear_w8a8_int8_workspace(int M, int K);
+int b2_linear_w8a8_int8(const void* x, int x_dtype, int64_t ldx, const int8_t* W, int64_t ldw, const float* Bs,
+                        const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
+                        void* workspace, size_t workspace_bytes, b2_stream_t stream);
+
+/* Same composition for per-token fp8 (W8A8Fp8LinearMethod.apply ->
+ * apply_fp8_linear, python/sglang/srt/layers/quantization/fp8_utils.py:1194-1276). */
+size_t b2_linear_w8a8_fp8_workspace(int M, int K);
+int b2_linear_w8a8_fp8(const void* x, int x_dtype, int64_t ldx, const uint8_t* W, int64_t ldw, const float* Bs,
+                       const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
+                       void* workspace, size_t workspace_bytes, b2_stream_t stream);
+
+/* ---- introspection (tests / bench) ----------------------------------------- */
+
+/* Number of kernels launched by this library on the calling thread since the last reset. */
+uint64_t b2_launch_count(void);
+void b2_launch_count_reset(void);
+
+/* Force a GEMM tile configuration (0 = automatic).  For benchmarks and parity sweeps. */
+void b2_set_gemm_config(int config_id);
+/* Name of the tile configuration the last GEMM call on this thread used. */
+const char* b2_last_gemm_config(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_W8A8_H_ */

@@ -1,0 +1,47 @@
+// Internal declarations shared by the .cu translation units of libb200_w8a8.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b200_w8a8.h"
+
+namespace b2 {
+
+// quant.cu
+cudaError_t quant_rows_int8(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s, int M,
+                            int K, cudaStream_t st);
+cudaError_t quant_rows_fp8(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s, int M,
+                           int K, cudaStream_t st);
+cudaError_t quant_fp8_group128(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s,
+                               int64_t s_row_stride, int64_t s_grp_stride, int M, int K, float eps, float fmin,
+                               float fmax, cudaStream_t st);
+
+// gemm_sm100.cu
+struct GemmArgs {
+  const void* A;   // [M,K] 8-bit, K contiguous
+  int64_t lda;
+  const void* W;   // [N,K] 8-bit, K contiguous
+  int64_t ldw;
+  const float* As; // [M] per-token scales (per-tensor kernels) or SFA (block-wise)
+  const float* Bs; // [N] per-channel scales or SFB
+  const void* bias;
+  int bias_dtype;
+  void* D;
+  int64_t ldd;
+  int out_dtype;
+  int M, N, K;
+  // block-wise (128x128) only
+  int64_t sfa_m_stride, sfa_k_stride, sfb_n_stride, sfb_k_stride;
+};
+
+enum GemmFlavor { GEMM_S8 = 0, GEMM_E4M3 = 1, GEMM_E4M3_BLOCK128 = 2 };
+
+// Returns B2_OK or a B2_ERR_* code; `err` receives a message on failure.
+int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const char** used_config,
+                cudaStream_t st, char* err, size_t err_len);
+
+// capi.cu
+void count_launch(int n = 1);
+int device_sm_count();
+
+}  // namespace b2

@@ -1,0 +1,278 @@
+// C-ABI entry points of libb200_w8a8.so (see include/b200_w8a8.h for the contract
+// and the reference interface each function replaces).  Argument validation mirrors
+// the reference ops' TORCH_CHECKs (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:670-695,
+// fp8_gemm_kernel.cu:1465-1487, fp8_blockwise_gemm_kernel.cu:374-403) but reports
+// through status codes + b2_last_error() instead of exceptions.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "b200_w8a8_internal.h"
+
+namespace b2 {
+
+static thread_local char g_err[512] = "";
+static thread_local uint64_t g_launches = 0;
+static thread_local int g_forced_config = 0;
+static thread_local const char* g_last_config = "";
+
+void count_launch(int n) { g_launches += static_cast<uint64_t>(n); }
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+struct DevInfo {
+  int sms = 0, major = 0, minor = 0;
+  bool valid = false;
+};
+static DevInfo g_dev[64];
+
+static const DevInfo* dev_info() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  DevInfo& d = g_dev[dev];
+  if (!d.valid) {
+    if (cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return nullptr;
+    cudaDeviceGetAttribute(&d.major, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDeviceGetAttribute(&d.minor, cudaDevAttrComputeCapabilityMinor, dev);
+    d.valid = true;
+  }
+  return &d;
+}
+
+int device_sm_count() {
+  const DevInfo* d = dev_info();
+  return d ? d->sms : 148;
+}
+
+// No CPU path and no other-architecture path: the kernels are sm_100a only.
+static int check_arch() {
+  const DevInfo* d = dev_info();
+  if (!d) {
+    cudaGetLastError();
+    return fail(B2_ERR_ARCH, "b200_w8a8: no usable CUDA device (this library has no CPU fallback)");
+  }
+  if (d->major != 10 || d->minor != 0)
+    return fail(B2_ERR_ARCH, "b200_w8a8: kernels are built for sm_100a (B200) only, device is sm_%d%d", d->major,
+                d->minor);
+  return B2_OK;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+static int check_act_dtype(int dt, const char* what) {
+  if (dt != B2_DTYPE_BF16 && dt != B2_DTYPE_F16) return fail(B2_ERR_ARG, "%s must be bfloat16 or float16", what);
+  return B2_OK;
+}
+
+static int check_cuda(cudaError_t e, const char* what) {
+  if (e != cudaSuccess) return fail(B2_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+  return B2_OK;
+}
+
+static int check_gemm_common(const void* A, int64_t lda, const void* W, int64_t ldw, const void* D, int64_t ldd,
+                             int out_bytes, int M, int N, int K) {
+  if (M < 0 || N <= 0 || K <= 0) return fail(B2_ERR_ARG, "bad GEMM shape M=%d N=%d K=%d", M, N, K);
+  if (!A || !W || !D) return fail(B2_ERR_ARG, "null matrix pointer");
+  if (K % 16 != 0) return fail(B2_ERR_ARG, "mat_a/mat_b must be multiple of 16 bytes for memory alignment (K=%d)", K);
+  if ((static_cast<int64_t>(N) * 2) % 16 != 0)
+    return fail(B2_ERR_ARG, "out must be multiple of 16 bytes for memory alignment (N=%d must be a multiple of 8)", N);
+  if (lda < K || ldw < K || ldd < N) return fail(B2_ERR_ARG, "row stride smaller than row length");
+  if (lda % 16 != 0 || ldw % 16 != 0) return fail(B2_ERR_ARG, "row strides of A and W must be multiples of 16 bytes");
+  if ((ldd * out_bytes) % 16 != 0) return fail(B2_ERR_ARG, "row stride of D must be a multiple of 16 bytes");
+  if (!aligned16(A) || !aligned16(W) || !aligned16(D)) return fail(B2_ERR_ARG, "A, W and D must be 16-byte aligned");
+  return B2_OK;
+}
+
+}  // namespace b2
+
+using namespace b2;
+
+extern "C" {
+
+int b2_abi_version(void) { return B2_ABI_VERSION; }
+
+const char* b2_last_error(void) { return g_err; }
+
+int b2_device_info(int* sm_count, int* cc_major, int* cc_minor) {
+  const DevInfo* d = dev_info();
+  if (!d) {
+    cudaGetLastError();
+    return fail(B2_ERR_CUDA, "no CUDA device");
+  }
+  if (sm_count) *sm_count = d->sms;
+  if (cc_major) *cc_major = d->major;
+  if (cc_minor) *cc_minor = d->minor;
+  return B2_OK;
+}
+
+uint64_t b2_launch_count(void) { return g_launches; }
+void b2_launch_count_reset(void) { g_launches = 0; }
+void b2_set_gemm_config(int config_id) { g_forced_config = config_id; }
+const char* b2_last_gemm_config(void) { return g_last_config; }
+
+int b2_quant_int8_rows(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s, int M, int K,
+                       b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (int r = check_act_dtype(x_dtype, "per_token_quant_int8: input")) return r;
+  if (M < 0 || K <= 0 || !x || !q || !s || ldx < K || ldq < K)
+    return fail(B2_ERR_ARG, "per_token_quant_int8: bad arguments (M=%d K=%d)", M, K);
+  if (M == 0) return B2_OK;
+  if (int r = check_cuda(quant_rows_int8(x, x_dtype, ldx, q, ldq, s, M, K, static_cast<cudaStream_t>(stream)),
+                         "per_token_quant_int8 launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
+int b2_quant_fp8_rows(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s, int M, int K,
+                      b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (int r = check_act_dtype(x_dtype, "sgl_per_token_quant_fp8: input")) return r;
+  if (M < 0 || K <= 0 || !x || !q || !s || ldx < K || ldq < K)
+    return fail(B2_ERR_ARG, "sgl_per_token_quant_fp8: bad arguments (M=%d K=%d)", M, K);
+  if (M == 0) return B2_OK;
+  if (int r = check_cuda(quant_rows_fp8(x, x_dtype, ldx, q, ldq, s, M, K, static_cast<cudaStream_t>(stream)),
+                         "sgl_per_token_quant_fp8 launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
+int b2_quant_fp8_group128(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s,
+                          int64_t s_row_stride, int64_t s_grp_stride, int M, int K, float eps, float fp8_min,
+                          float fp8_max, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (int r = check_act_dtype(x_dtype, "sgl_per_token_group_quant_8bit: input")) return r;
+  if (M < 0 || K <= 0 || !x || !q || !s) return fail(B2_ERR_ARG, "sgl_per_token_group_quant_8bit: bad arguments");
+  if (K % 128 != 0) return fail(B2_ERR_ARG, "sgl_per_token_group_quant_8bit: K=%d must be a multiple of group_size 128", K);
+  if (ldx % 8 != 0 || ldq % 8 != 0 || !aligned16(x) || (reinterpret_cast<uintptr_t>(q) & 7u))
+    return fail(B2_ERR_ARG, "sgl_per_token_group_quant_8bit: input rows must be 16-byte aligned, output rows 8-byte aligned");
+  if (M == 0) return B2_OK;
+  if (int r = check_cuda(quant_fp8_group128(x, x_dtype, ldx, q, ldq, s, s_row_stride, s_grp_stride, M, K, eps,
+                                            fp8_min, fp8_max, static_cast<cudaStream_t>(stream)),
+                         "sgl_per_token_group_quant_8bit launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
+int b2_gemm_s8(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
+               const void* bias, int bias_dtype, void* D, int64_t ldd, int out_dtype, int M, int N, int K,
+               b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16 && out_dtype != B2_DTYPE_S32)
+    return fail(B2_ERR_ARG, "int8_scaled_mm: out_dtype must be Half or BFloat16");
+  const int ob = out_dtype == B2_DTYPE_S32 ? 4 : 2;
+  if (int r = check_gemm_common(A, lda, W, ldw, D, ldd, ob, M, N, K)) return r;
+  if (out_dtype != B2_DTYPE_S32) {
+    if (!As || !Bs) return fail(B2_ERR_ARG, "int8_scaled_mm: scales_a / scales_b must not be null");
+    if (!aligned16(Bs)) return fail(B2_ERR_ARG, "int8_scaled_mm: scales_b must be 16-byte aligned");
+    if (bias && !aligned16(bias)) return fail(B2_ERR_ARG, "int8_scaled_mm: bias must be 16-byte aligned");
+    if (bias && bias_dtype != B2_DTYPE_BF16 && bias_dtype != B2_DTYPE_F16 && bias_dtype != B2_DTYPE_F32)
+      return fail(B2_ERR_ARG, "int8_scaled_mm: unsupported bias dtype");
+  }
+  if (M == 0) return B2_OK;
+  GemmArgs a{};
+  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = As; a.Bs = Bs;
+  a.bias = out_dtype == B2_DTYPE_S32 ? nullptr : bias;
+  a.bias_dtype = bias_dtype; a.D = D; a.ldd = ldd; a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K;
+  char err[256];
+  int r = gemm_launch(GEMM_S8, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err, sizeof(err));
+  if (r) return fail(r, "int8_scaled_mm: %s", err);
+  return B2_OK;
+}
+
+int b2_gemm_e4m3(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* As, const float* Bs,
+                 const void* bias, int bias_dtype, void* D, int64_t ldd, int out_dtype, int M, int N, int K,
+                 b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16 && out_dtype != B2_DTYPE_F32)
+    return fail(B2_ERR_ARG, "fp8_scaled_mm: out_dtype must be Half or BFloat16");
+  const int ob = out_dtype == B2_DTYPE_F32 ? 4 : 2;
+  if (int r = check_gemm_common(A, lda, W, ldw, D, ldd, ob, M, N, K)) return r;
+  if (!As || !Bs) return fail(B2_ERR_ARG, "fp8_scaled_mm: scales_a / scales_b must not be null");
+  if (!aligned16(Bs)) return fail(B2_ERR_ARG, "fp8_scaled_mm: scales_b must be 16-byte aligned");
+  if (bias && !aligned16(bias)) return fail(B2_ERR_ARG, "fp8_scaled_mm: bias must be 16-byte aligned");
+  if (bias && bias_dtype != B2_DTYPE_BF16 && bias_dtype != B2_DTYPE_F16 && bias_dtype != B2_DTYPE_F32)
+    return fail(B2_ERR_ARG, "fp8_scaled_mm: unsupported bias dtype");
+  if (M == 0) return B2_OK;
+  GemmArgs a{};
+  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = As; a.Bs = Bs; a.bias = bias; a.bias_dtype = bias_dtype;
+  a.D = D; a.ldd = ldd; a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K;
+  char err[256];
+  int r = gemm_launch(GEMM_E4M3, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err, sizeof(err));
+  if (r) return fail(r, "fp8_scaled_mm: %s", err);
+  return B2_OK;
+}
+
+int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* sfa,
+                          int64_t sfa_m_stride, int64_t sfa_k_stride, const float* sfb, int64_t sfb_n_stride,
+                          int64_t sfb_k_stride, const void* bias, int bias_dtype, void* D, int64_t ldd,
+                          int out_dtype, int M, int N, int K, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16 && out_dtype != B2_DTYPE_F32)
+    return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: out_dtype must be Half or BFloat16");
+  const int ob = out_dtype == B2_DTYPE_F32 ? 4 : 2;
+  if (int r = check_gemm_common(A, lda, W, ldw, D, ldd, ob, M, N, K)) return r;
+  if (K % 128 != 0) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: K=%d must be a multiple of 128", K);
+  if (!sfa || !sfb) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: scales must not be null");
+  if (bias && !aligned16(bias)) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: bias must be 16-byte aligned");
+  if (M == 0) return B2_OK;
+  GemmArgs a{};
+  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = sfa; a.Bs = sfb; a.bias = bias; a.bias_dtype = bias_dtype;
+  a.D = D; a.ldd = ldd; a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K;
+  a.sfa_m_stride = sfa_m_stride; a.sfa_k_stride = sfa_k_stride;
+  a.sfb_n_stride = sfb_n_stride; a.sfb_k_stride = sfb_k_stride;
+  char err[256];
+  int r = gemm_launch(GEMM_E4M3_BLOCK128, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err,
+                      sizeof(err));
+  if (r) return fail(r, "fp8_blockwise_scaled_mm: %s", err);
+  return B2_OK;
+}
+
+static size_t ws_bytes(int M, int K) {
+  // [ q : M x K bytes, padded to 256 ][ scales : M floats ]
+  size_t q = (static_cast<size_t>(M) * static_cast<size_t>(K) + 255) & ~static_cast<size_t>(255);
+  return q + static_cast<size_t>(M) * sizeof(float) + 256;
+}
+
+size_t b2_linear_w8a8_int8_workspace(int M, int K) { return ws_bytes(M, K); }
+size_t b2_linear_w8a8_fp8_workspace(int M, int K) { return ws_bytes(M, K); }
+
+int b2_linear_w8a8_int8(const void* x, int x_dtype, int64_t ldx, const int8_t* W, int64_t ldw, const float* Bs,
+                        const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
+                        void* workspace, size_t workspace_bytes, b2_stream_t stream) {
+  if (int r = check_act_dtype(x_dtype, "int8_scaled_mm_with_quant: mat1")) return r;
+  if (M == 0) return B2_OK;
+  if (!workspace || workspace_bytes < ws_bytes(M, K) || !aligned16(workspace))
+    return fail(B2_ERR_ARG, "int8_scaled_mm_with_quant: workspace too small or misaligned (need %zu bytes)", ws_bytes(M, K));
+  int8_t* q = static_cast<int8_t*>(workspace);
+  float* s = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) +
+                                      ((static_cast<size_t>(M) * K + 255) & ~static_cast<size_t>(255)));
+  if (int r = b2_quant_int8_rows(x, x_dtype, ldx, q, K, s, M, K, stream)) return r;
+  // reference: out_dtype must equal the input dtype (gemm_int8.cpp:509)
+  return b2_gemm_s8(q, K, W, ldw, s, Bs, bias, bias_dtype, D, ldd, x_dtype, M, N, K, stream);
+}
+
+int b2_linear_w8a8_fp8(const void* x, int x_dtype, int64_t ldx, const uint8_t* W, int64_t ldw, const float* Bs,
+                       const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
+                       void* workspace, size_t workspace_bytes, b2_stream_t stream) {
+  if (int r = check_act_dtype(x_dtype, "w8a8_fp8 linear: input")) return r;
+  if (M == 0) return B2_OK;
+  if (!workspace || workspace_bytes < ws_bytes(M, K) || !aligned16(workspace))
+    return fail(B2_ERR_ARG, "w8a8_fp8 linear: workspace too small or misaligned (need %zu bytes)", ws_bytes(M, K));
+  uint8_t* q = static_cast<uint8_t*>(workspace);
+  float* s = reinterpret_cast<float*>(q + ((static_cast<size_t>(M) * K + 255) & ~static_cast<size_t>(255)));
+  if (int r = b2_quant_fp8_rows(x, x_dtype, ldx, q, K, s, M, K, stream)) return r;
+  return b2_gemm_e4m3(q, K, W, ldw, s, Bs, bias, bias_dtype, D, ldd, x_dtype, M, N, K, stream);
+}
+
+}  // extern "C"

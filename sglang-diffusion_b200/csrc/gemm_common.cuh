@@ -1,0 +1,144 @@
+// Device + host helpers shared by the tcgen05 GEMM translation units.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cudaTypedefs.h>
+
+#include <cstdio>
+#include <cstring>
+
+#include "b200_w8a8_internal.h"
+#include "ptx.cuh"
+
+namespace b2 {
+
+constexpr int BM = 128;          // rows per CTA tile (= UMMA M, TMEM lanes)
+constexpr int BK = 128;          // bytes of K per pipeline stage (= one 128 B swizzle row)
+constexpr int UMMA_K = 32;       // bytes of K per tcgen05.mma for 8-bit kinds
+constexpr int NUM_THREADS = 192;
+constexpr int EPI_WARP0 = 2;
+constexpr int EPI_BUF_BYTES = 32 * 128;  // one warp's staging box: 32 rows x 128 B
+constexpr int SMEM_LIMIT = 232448;       // 227 KB opt-in limit per CTA
+
+struct KernelParams {
+  const float* As;
+  const float* Bs;
+  const void* bias;
+  int bias_dtype;
+  int out_dtype;
+  int M, N, K;
+  int num_m_blocks, num_n_blocks, num_kb;
+  int stages;
+  int group_m;
+  int a_box_rows;  // rows of A actually fetched per stage (<= BM; small-M shapes fetch fewer)
+};
+
+B2_DEVICE void tile_coords(int tile, const KernelParams& p, int& m_blk, int& n_blk) {
+  // bands of `group_m` row-blocks, row-block fastest inside a band: the CTAs that run
+  // concurrently share a few A row-blocks and a few W column-blocks in L2.
+  const int band_tiles = p.group_m * p.num_n_blocks;
+  const int band = tile / band_tiles;
+  const int in_band = tile - band * band_tiles;
+  const int m_first = band * p.group_m;
+  const int rows_in_band = min(p.group_m, p.num_m_blocks - m_first);
+  m_blk = m_first + in_band % rows_in_band;
+  n_blk = in_band / rows_in_band;
+}
+
+B2_DEVICE float load_bias(const void* bias, int dtype, int col) {
+  if (dtype == B2_DTYPE_BF16) return __bfloat162float(__ldg(static_cast<const __nv_bfloat16*>(bias) + col));
+  if (dtype == B2_DTYPE_F16) return __half2float(__ldg(static_cast<const __half*>(bias) + col));
+  return __ldg(static_cast<const float*>(bias) + col);
+}
+
+// 8 consecutive per-column values starting at `col` (col % 8 == 0, col + 8 <= N guaranteed by N % 8 == 0)
+B2_DEVICE void load_cols8_f32(const float* p, int col, float (&v)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p + col));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p + col) + 1);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
+B2_DEVICE void load_bias8(const void* bias, int dtype, int col, float (&v)[8]) {
+  if (dtype == B2_DTYPE_F32) {
+    load_cols8_f32(static_cast<const float*>(bias), col, v);
+  } else {
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(bias) + col));
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (dtype == B2_DTYPE_BF16) {
+        v[2 * i] = __uint_as_float(w[i] << 16);
+        v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+      } else {
+        const __half2 h = *reinterpret_cast<const __half2*>(&w[i]);
+        v[2 * i] = __low2float(h);
+        v[2 * i + 1] = __high2float(h);
+      }
+    }
+  }
+}
+
+template <MmaKind KIND>
+B2_DEVICE float epilogue_value(uint32_t raw, float as, float bs, float bias, bool has_bias) {
+  if constexpr (KIND == MmaKind::I8) {
+    // gemm_int8.cpp:40-46: fmadd(mul(cvtepi32_ps(acc), As), Bs, bias)  |  mul(mul(.., As), Bs)
+    const float c = __int2float_rn(static_cast<int32_t>(raw));
+    const float t = __fmul_rn(c, as);
+    return has_bias ? __fmaf_rn(t, bs, bias) : __fmul_rn(t, bs);
+  } else {
+    // fp8_gemm_kernel.cu sm100 EVT: As * (Bs * acc) [+ bias]
+    const float c = __uint_as_float(raw);
+    const float t = __fmul_rn(as, __fmul_rn(bs, c));
+    return has_bias ? __fadd_rn(t, bias) : t;
+  }
+}
+
+B2_DEVICE uint32_t pack16(float lo, float hi, int out_dtype) {
+  if (out_dtype == B2_DTYPE_BF16) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+  }
+  const __half2 v = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static inline EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// 2-D row-major tensor [rows, cols] of `esize`-byte elements, row stride `ld_bytes`;
+// box = {box_cols elements (128 bytes), box_rows}, 128-byte swizzle.
+static inline bool make_tmap_2d(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* base, uint64_t rows,
+                         uint64_t cols, uint64_t ld_bytes, uint32_t box_rows, uint32_t box_cols) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_bytes};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  const uint32_t box_bytes = box_cols * static_cast<uint32_t>(esize);
+  const CUtensorMapSwizzle swz = box_bytes == 128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                                 : box_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                   : CU_TENSOR_MAP_SWIZZLE_NONE;
+  if (swz == CU_TENSOR_MAP_SWIZZLE_NONE) return false;
+  CUresult r = enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+}  // namespace b2

@@ -1,0 +1,376 @@
+// Persistent, warp-specialised tcgen05 GEMM for the W8A8 linear path (sm_100a).
+//
+//   D[M,N] = epilogue( A[M,K] (8-bit, K-major)  x  W[N,K]^T (8-bit, K-major) )
+//
+// kind::i8     (s8 x s8 -> s32 in TMEM): int8_scaled_mm
+//              (reference: sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:663-747, no sm_100 path;
+//               bit-exact epilogue of sgl-kernel/csrc/cpu/gemm_int8.cpp:20-60)
+// kind::f8f6f4 (e4m3 x e4m3 -> f32 in TMEM): fp8_scaled_mm
+//              (reference: sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:796-1170, 1450-1532)
+//
+// Structure (one CTA per SM, 192 threads, static round-robin tile schedule):
+//   warp 0   : TMA producer  -- cp.async.bulk.tensor 2-D boxes {128 B of K, rows} with the
+//              128-byte swizzle into a STAGES-deep ring, completion on `full[s]` mbarriers
+//   warp 1   : MMA issuer    -- one lane issues 4 x tcgen05.mma (K = 32 B each) per stage,
+//              tcgen05.commit -> `empty[s]` releases the stage, -> `acc_full[a]` hands the
+//              accumulator to the epilogue; owns the TMEM allocation
+//   warps 2-5: epilogue      -- tcgen05.ld 32 lanes x 32 columns, dequant/scale/bias in fp32,
+//              cast, swizzled st.shared, per-warp TMA store of 32 x 128 B boxes
+// Two TMEM accumulator buffers (2 x BN columns) let the epilogue of tile i overlap the
+// main loop of tile i+1.  M/N/K tails are handled by TMA zero-fill on loads and clipping
+// on stores; no padding copies are ever made.
+#include "gemm_common.cuh"
+
+namespace b2 {
+
+template <MmaKind KIND, int OUT_BYTES, int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+    gemm_w8a8_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                     const __grid_constant__ CUtensorMap tmap_d, const KernelParams p) {
+  constexpr uint32_t A_STAGE_BYTES = BM * BK;
+  constexpr uint32_t B_STAGE_BYTES = BN * BK;
+  constexpr uint32_t TMEM_COLS = (2 * BN) < 32 ? 32 : (2 * BN);
+  static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns must be a power of two");
+  constexpr int COLS_PER_BOX = 128 / OUT_BYTES;  // output columns in one 128-byte staging row
+  static_assert(BN % COLS_PER_BOX == 0 || BN < COLS_PER_BOX, "tile width vs store box");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stages = p.stages;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + static_cast<size_t>(stages) * A_STAGE_BYTES;
+  uint8_t* smem_epi = smem_b + static_cast<size_t>(stages) * B_STAGE_BYTES;  // 4 warps x 2 bufs x 4 KB
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_epi + 4 * 2 * EPI_BUF_BYTES);
+  uint64_t* empty_bar = full_bar + stages;
+  uint64_t* acc_full = empty_bar + stages;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    tma_prefetch_desc(&tmap_d);
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<1>(tmem_ptr, TMEM_COLS);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer ====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t tx_bytes = static_cast<uint32_t>(p.a_box_rows) * BK + B_STAGE_BYTES;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int m_blk, n_blk;
+        tile_coords(tile, p, m_blk, n_blk);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+          tma_load_2d(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES, &tmap_a, &full_bar[stage], kb * BK,
+                      m_blk * BM, kEvictNormal);
+          tma_load_2d(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES, &tmap_b, &full_bar[stage], kb * BK,
+                      n_blk * BN, kEvictNormal);
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================================= MMA issuer ====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc<KIND>(BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&acc_empty[acc], acc_phase ^ 1);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after_sync();
+          const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES));
+          const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advance 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
+            umma<KIND, 1>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
+                          db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&acc_full[acc]);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ========================================================= epilogue ====
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may read
+    uint8_t* my_epi = smem_epi + static_cast<size_t>(warp - EPI_WARP0) * 2 * EPI_BUF_BYTES;
+    const bool has_bias = p.bias != nullptr;
+    const bool raw_out = (KIND == MmaKind::I8) && p.out_dtype == B2_DTYPE_S32;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int buf = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int m_blk, n_blk;
+      tile_coords(tile, p, m_blk, n_blk);
+      const int row0 = m_blk * BM + quarter * 32;
+      const int row = row0 + lane;
+      const int col_tile = n_blk * BN;
+      float as = 0.f;
+      if (!raw_out && row < p.M) as = __ldg(p.As + row);
+
+      mbar_wait(&acc_full[acc], acc_phase);
+      tc_fence_after_sync();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
+
+      constexpr int NBOX = (BN + COLS_PER_BOX - 1) / COLS_PER_BOX;
+#pragma unroll 1
+      for (int bx = 0; bx < NBOX; ++bx) {
+        const int col_box = col_tile + bx * COLS_PER_BOX;
+        uint8_t* stage_buf = my_epi + buf * EPI_BUF_BYTES;
+        // the TMA store that last read this staging buffer must have drained it
+        if (lane == 0) tma_store_wait_read<1>();
+        __syncwarp();
+        constexpr int BOX_COLS = COLS_PER_BOX < BN ? COLS_PER_BOX : BN;
+        constexpr int BOX_BYTES = BOX_COLS * OUT_BYTES;  // 128 (SW128 box) or 64 (SW64 box, BN = 32 @ 16 bit)
+        static_assert(BOX_BYTES == 128 || BOX_BYTES == 64, "store box is 128 or 64 bytes wide");
+        constexpr int LDS_PER_BOX = BOX_COLS / 32;
+        // TMA swizzle of the staging box: 16-byte chunk index ^= (byte offset >> 7) & (BOX_BYTES/16 - 1)
+        const int swz = BOX_BYTES == 128 ? (lane & 7) : ((lane >> 1) & 3);
+#pragma unroll
+        for (int h = 0; h < LDS_PER_BOX; ++h) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(t_row + static_cast<uint32_t>(bx * COLS_PER_BOX + h * 32), r);
+          tmem_ld_wait();
+          const int col_h = col_box + h * 32;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {  // 8 columns per group
+            const int col = col_h + g * 8;
+            float v[8];
+            if (raw_out) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+            } else if (col < p.N) {
+              float bs[8], bi[8];
+              load_cols8_f32(p.Bs, col, bs);
+              if (has_bias) load_bias8(p.bias, p.bias_dtype, col, bi);
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                v[j] = epilogue_value<KIND>(r[g * 8 + j], as, bs[j], has_bias ? bi[j] : 0.f, has_bias);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = 0.f;
+            }
+            if constexpr (OUT_BYTES == 2) {
+              // 8 columns -> one 16-byte chunk; chunk index inside the 128 B row = h*4 + g
+              uint4 o;
+              o.x = pack16(v[0], v[1], p.out_dtype);
+              o.y = pack16(v[2], v[3], p.out_dtype);
+              o.z = pack16(v[4], v[5], p.out_dtype);
+              o.w = pack16(v[6], v[7], p.out_dtype);
+              const int chunk = (h * 4 + g) ^ swz;
+              *reinterpret_cast<uint4*>(stage_buf + lane * BOX_BYTES + chunk * 16) = o;
+            } else {
+              // 8 columns -> two 16-byte chunks 2g, 2g+1
+#pragma unroll
+              for (int c = 0; c < 2; ++c) {
+                uint4 o;
+                o.x = __float_as_uint(v[4 * c + 0]);
+                o.y = __float_as_uint(v[4 * c + 1]);
+                o.z = __float_as_uint(v[4 * c + 2]);
+                o.w = __float_as_uint(v[4 * c + 3]);
+                const int chunk = (g * 2 + c) ^ swz;
+                *reinterpret_cast<uint4*>(stage_buf + lane * BOX_BYTES + chunk * 16) = o;
+              }
+            }
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0 && row0 < p.M && col_box < p.N) {
+          tma_store_2d(&tmap_d, stage_buf, col_box, row0);
+          tma_store_commit();
+        }
+        buf ^= 1;
+      }
+      // accumulator fully read: hand the TMEM buffer back to the MMA warp
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+    if (lane == 0) tma_store_wait_all<0>();
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc<1>(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------ host ----
+
+struct TileConfig {
+  int id;
+  int bn;
+  const char* name;
+};
+static const TileConfig kConfigs[] = {
+    {1, 32, "1cta_128x32"}, {2, 64, "1cta_128x64"}, {3, 128, "1cta_128x128"}, {4, 256, "1cta_128x256"}};
+
+static int stages_for(int bn) {
+  const int fixed = 4 * 2 * EPI_BUF_BYTES + 1024 /*align slack*/ + 512 /*barriers*/;
+  int s = (SMEM_LIMIT - fixed) / (BM * BK + bn * BK);
+  return s > 12 ? 12 : s;
+}
+
+static size_t smem_bytes_for(int bn, int stages) {
+  return static_cast<size_t>(stages) * (BM * BK + bn * BK) + 4 * 2 * EPI_BUF_BYTES + 1024 + 512;
+}
+
+static const TileConfig& pick_config(int M, int N, int sms) {
+  // relative MMA-side efficiency of a 128 x BN tile (smem operand bandwidth bound for narrow tiles)
+  const double rate[] = {0.35, 0.55, 0.8, 1.0};
+  const int num_m = (M + BM - 1) / BM;
+  int best = 3;
+  double best_score = -1;
+  for (int i = 0; i < 4; ++i) {
+    const int bn = kConfigs[i].bn;
+    const long tiles = static_cast<long>(num_m) * ((N + bn - 1) / bn);
+    const long waves = (tiles + sms - 1) / sms;
+    const double score = static_cast<double>(tiles) / static_cast<double>(waves * sms) * rate[i];
+    if (score > best_score + 1e-9) {
+      best_score = score;
+      best = i;
+    }
+  }
+  return kConfigs[best];
+}
+
+template <MmaKind KIND, int OUT_BYTES, int BN>
+static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const KernelParams& p,
+                      int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
+  auto kern = gemm_w8a8_kernel<KIND, OUT_BYTES, BN>;
+  static bool attr_set = false;  // per instantiation; the attribute is per-function, per-device context
+  static int attr_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set || attr_dev != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+    if (e != cudaSuccess) {
+      snprintf(err, err_len, "cudaFuncSetAttribute(max dynamic smem): %s", cudaGetErrorString(e));
+      return B2_ERR_CUDA;
+    }
+    attr_set = true;
+    attr_dev = dev;
+  }
+  kern<<<grid, NUM_THREADS, smem, st>>>(ta, tb, td, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(err, err_len, "gemm kernel launch: %s", cudaGetErrorString(e));
+    return B2_ERR_CUDA;
+  }
+  count_launch();
+  return B2_OK;
+}
+
+template <MmaKind KIND, int OUT_BYTES>
+static int launch_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
+                     const KernelParams& p, int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
+  switch (bn) {
+    case 32: return launch_one<KIND, OUT_BYTES, 32>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 64: return launch_one<KIND, OUT_BYTES, 64>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 128: return launch_one<KIND, OUT_BYTES, 128>(ta, tb, td, p, grid, smem, st, err, err_len);
+    default: return launch_one<KIND, OUT_BYTES, 256>(ta, tb, td, p, grid, smem, st, err, err_len);
+  }
+}
+
+int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** used_config, cudaStream_t st,
+                          char* err, size_t err_len);
+
+int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const char** used_config,
+                cudaStream_t st, char* err, size_t err_len) {
+  if (flavor == GEMM_E4M3_BLOCK128) return gemm_launch_blockwise(a, forced_config, used_config, st, err, err_len);
+  const int sms = device_sm_count();
+  const TileConfig* cfg = &pick_config(a.M, a.N, sms);
+  if (forced_config >= 1 && forced_config <= 4) cfg = &kConfigs[forced_config - 1];
+  if (used_config) *used_config = cfg->name;
+  const int bn = cfg->bn;
+
+  const int out_bytes = (a.out_dtype == B2_DTYPE_BF16 || a.out_dtype == B2_DTYPE_F16) ? 2 : 4;
+  CUtensorMapDataType d_dt = a.out_dtype == B2_DTYPE_BF16  ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                             : a.out_dtype == B2_DTYPE_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                             : a.out_dtype == B2_DTYPE_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                                           : CU_TENSOR_MAP_DATA_TYPE_INT32;
+  KernelParams p;
+  p.As = a.As;
+  p.Bs = a.Bs;
+  p.bias = a.bias;
+  p.bias_dtype = a.bias_dtype;
+  p.out_dtype = a.out_dtype;
+  p.M = a.M;
+  p.N = a.N;
+  p.K = a.K;
+  p.num_m_blocks = (a.M + BM - 1) / BM;
+  p.num_n_blocks = (a.N + bn - 1) / bn;
+  p.num_kb = (a.K + BK - 1) / BK;
+  p.stages = stages_for(bn);
+  p.group_m = 16;
+  // decode shapes: fetch only the rows that exist (rounded to the 8-row swizzle atom);
+  // the untouched tail of the smem tile feeds MMA rows whose outputs are clipped by the store.
+  p.a_box_rows = a.M >= BM ? BM : ((a.M + 7) / 8) * 8;
+
+  CUtensorMap ta, tb, td;
+  if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, p.a_box_rows, BK) ||
+      !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, bn, BK) ||
+      !make_tmap_2d(&td, d_dt, out_bytes, a.D, a.M, a.N, a.ldd * out_bytes, 32,
+                    (128 / out_bytes) < bn ? (128 / out_bytes) : bn)) {  // 64-byte boxes use SWIZZLE_64B
+    snprintf(err, err_len, "cuTensorMapEncodeTiled failed (M=%d N=%d K=%d lda=%lld ldw=%lld ldd=%lld)", a.M, a.N,
+             a.K, (long long)a.lda, (long long)a.ldw, (long long)a.ldd);
+    return B2_ERR_CUDA;
+  }
+  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  const int grid = tiles < sms ? tiles : sms;
+  const size_t smem = smem_bytes_for(bn, p.stages);
+  if (flavor == GEMM_S8) {
+    if (out_bytes == 2) return launch_bn<MmaKind::I8, 2>(bn, ta, tb, td, p, grid, smem, st, err, err_len);
+    return launch_bn<MmaKind::I8, 4>(bn, ta, tb, td, p, grid, smem, st, err, err_len);
+  }
+  if (out_bytes == 2) return launch_bn<MmaKind::F8, 2>(bn, ta, tb, td, p, grid, smem, st, err, err_len);
+  return launch_bn<MmaKind::F8, 4>(bn, ta, tb, td, p, grid, smem, st, err, err_len);
+}
+
+}  // namespace b2

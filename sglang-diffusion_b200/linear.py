@@ -1,0 +1,217 @@
+"""Host-side mirror of the reference's W8A8 linear methods and their tensor-parallel callers.
+
+Mirrors, with the same names / argument meaning / weight layouts:
+  W8A8Int8LinearMethod  python/sglang/srt/layers/quantization/w8a8_int8.py:155-231
+  W8A8Fp8LinearMethod   python/sglang/srt/layers/quantization/w8a8_fp8.py:103-194
+  apply_fp8_linear      python/sglang/srt/layers/quantization/fp8_utils.py:1194-1276 (dynamic per-token branch)
+  cutlass_w8a8_block_fp8_linear_with_fallback   fp8_utils.py:518-548
+  QuantLinear           the slice of ColumnParallelLinear / RowParallelLinear.forward that touches
+                        the path (python/sglang/srt/layers/linear.py:448-456, 1467-1496):
+                        quant_method.apply(...) then, for a row-parallel shard, one in-place
+                        all-reduce of the [M,N] output with the bias added on tp_rank 0 only.
+
+`fused=True` on the int8 method routes through the single entry
+torch.ops.sgl_kernel.int8_scaled_mm_with_quant (the name the reference's CPU backend calls,
+w8a8_int8.py:207-215), which runs quantizer + GEMM back to back inside the library with
+the quantized activations kept in an L2-resident workspace.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+
+
+# --------------------------------------------------------------- int8 W8A8 ----
+
+class W8A8Int8LinearMethod:
+    """Per-channel int8 weights [N,K] + fp32 scales [N,1]; dynamic per-token int8 activations."""
+
+    def __init__(self, fused: bool = False):
+        self.fused = fused
+
+    def create_weights(self, layer: torch.nn.Module, input_size_per_partition: int,
+                       output_partition_sizes: List[int], input_size: int, output_size: int,
+                       params_dtype: torch.dtype, device=None, **_):
+        n = sum(output_partition_sizes)
+        layer.logical_widths = output_partition_sizes
+        layer.weight = torch.nn.Parameter(
+            torch.empty(n, input_size_per_partition, dtype=torch.int8, device=device), requires_grad=False)
+        layer.weight_scale = torch.nn.Parameter(
+            torch.empty(n, 1, dtype=torch.float32, device=device), requires_grad=False)
+
+    def process_weights_after_loading(self, layer: torch.nn.Module) -> None:
+        # w8a8_int8.py:160-168: a transposed VIEW ([K,N], stride(0)==1) -- no repacking on GPU;
+        # both operands are already K-major, which is what the tcgen05 smem descriptors want.
+        layer.weight = torch.nn.Parameter(layer.weight.t(), requires_grad=False)
+        layer.weight_scale = torch.nn.Parameter(layer.weight_scale.data, requires_grad=False)
+
+    def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None):
+        if self.fused:
+            x2d = x.view(-1, x.shape[-1])
+            out = ops.int8_scaled_mm_with_quant(x2d, layer.weight.t(), layer.weight_scale, bias, x.dtype, False)
+            return out.view(*x.shape[:-1], layer.weight.shape[1])
+        x_q, x_scale = ops.per_token_quant_int8(x)
+        x_q_2d = x_q.view(-1, x_q.shape[-1])
+        x_scale_2d = x_scale.view(-1, x_scale.shape[-1])
+        output_shape = [*x_q.shape[:-1], layer.weight.shape[1]]
+        output = ops.int8_scaled_mm(x_q_2d, layer.weight, x_scale_2d, layer.weight_scale, out_dtype=x.dtype,
+                                    bias=bias)
+        return output.view(output_shape)
+
+
+# ---------------------------------------------------------------- fp8 W8A8 ----
+
+def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor,
+                     input_scale: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
+                     **_ignored) -> torch.Tensor:
+    """Dynamic per-token branch of fp8_utils.py:1194-1276 (weight is [K,N] with stride(0)==1)."""
+    if input_scale is not None:
+        raise NotImplementedError("static per-tensor fp8 activation scales are a 'next' row (SURVEY 8f rank 4)")
+    input_2d = input.view(-1, input.shape[-1])
+    output_shape = [*input.shape[:-1], weight.shape[1]]
+    assert weight_scale.numel() == weight.shape[1], "per-channel weight scales expected"
+    qinput, x_scale = ops.sglang_per_token_quant_fp8(input_2d)
+    output = ops.fp8_scaled_mm(qinput, weight, x_scale, weight_scale, out_dtype=input.dtype, bias=bias)
+    return output.view(*output_shape)
+
+
+class W8A8Fp8LinearMethod:
+    """Per-channel e4m3 weights [N,K] + fp32 scales [N,1]; dynamic per-token e4m3 activations."""
+
+    def create_weights(self, layer, input_size_per_partition, output_partition_sizes, input_size, output_size,
+                       params_dtype, device=None, **_):
+        n = sum(output_partition_sizes)
+        layer.logical_widths = output_partition_sizes
+        layer.weight = torch.nn.Parameter(
+            torch.empty(n, input_size_per_partition, dtype=torch.float8_e4m3fn, device=device), requires_grad=False)
+        layer.weight_scale = torch.nn.Parameter(
+            torch.empty(n, 1, dtype=torch.float32, device=device), requires_grad=False)
+
+    def process_weights_after_loading(self, layer) -> None:
+        layer.weight = torch.nn.Parameter(layer.weight.t(), requires_grad=False)  # w8a8_fp8.py:120
+        layer.weight_scale = torch.nn.Parameter(layer.weight_scale.data, requires_grad=False)
+
+    def apply(self, layer, x: torch.Tensor, bias: Optional[torch.Tensor] = None):
+        return apply_fp8_linear(x, layer.weight, layer.weight_scale, bias=bias)
+
+
+def cutlass_w8a8_block_fp8_linear_with_fallback(input: torch.Tensor, weight: torch.Tensor, block_size: List[int],
+                                                weight_scale: torch.Tensor,
+                                                input_scale: Optional[torch.Tensor] = None,
+                                                bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp8_utils.py:518-548.  weight [N,K] e4m3, weight_scale [N/128, K/128]."""
+    assert input_scale is None
+    assert list(block_size) == [128, 128], "only 128x128 weight blocks are built"
+    if weight.shape[0] % 128 != 0 or weight.shape[1] % 128 != 0:
+        raise NotImplementedError("block-fp8 shapes off the 128 grid take the reference's Triton fallback (out of scope)")
+    input_2d = input.view(-1, input.shape[-1])
+    output_shape = [*input.shape[:-1], weight.shape[0]]
+    q_input, x_scale = ops.per_token_group_quant_fp8(input_2d, block_size[1], column_major_scales=True)
+    output = ops.fp8_blockwise_scaled_mm(q_input, weight.T, x_scale, weight_scale.T, out_dtype=input_2d.dtype)
+    if bias is not None:
+        output += bias
+    return output.to(dtype=input_2d.dtype).view(*output_shape)
+
+
+class W8A8BlockFp8LinearMethod:
+    """Block-quantized e4m3 weights [N,K] + weight_scale_inv [N/128, K/128]
+    (multimodal_gen/runtime/layers/quantization/fp8.py:459-488)."""
+
+    block_size = [128, 128]
+
+    def create_weights(self, layer, input_size_per_partition, output_partition_sizes, input_size, output_size,
+                       params_dtype, device=None, **_):
+        n = sum(output_partition_sizes)
+        layer.weight = torch.nn.Parameter(
+            torch.empty(n, input_size_per_partition, dtype=torch.float8_e4m3fn, device=device), requires_grad=False)
+        layer.weight_scale_inv = torch.nn.Parameter(
+            torch.empty((n + 127) // 128, (input_size_per_partition + 127) // 128, dtype=torch.float32,
+                        device=device), requires_grad=False)
+
+    def process_weights_after_loading(self, layer) -> None:
+        pass
+
+    def apply(self, layer, x, bias=None):
+        return cutlass_w8a8_block_fp8_linear_with_fallback(x, layer.weight, self.block_size, layer.weight_scale_inv,
+                                                           None, bias)
+
+
+# ------------------------------------------------------ TP caller (linear.py) ----
+
+class QuantLinear(torch.nn.Module):
+    """The part of Column/RowParallelLinear.forward that is on the path.
+
+    parallel = "replicated" | "column" | "row".  Column: W split on N, no collective
+    (gather_output is never set inside transformer blocks).  Row: W split on K, the input is
+    already K-sharded, per-token scales are local to the shard, partial outputs are summed
+    with ONE all-reduce; bias only on tp_rank 0 (linear.py:1480).
+    """
+
+    def __init__(self, input_size: int, output_size: int, quant_method, bias: bool = False,
+                 params_dtype: torch.dtype = torch.bfloat16, parallel: str = "replicated",
+                 tp_rank: int = 0, tp_size: int = 1, tp_group=None, device=None):
+        super().__init__()
+        assert parallel in ("replicated", "column", "row")
+        self.parallel, self.tp_rank, self.tp_size, self.tp_group = parallel, tp_rank, tp_size, tp_group
+        self.input_size, self.output_size = input_size, output_size
+        k_local = input_size // tp_size if parallel == "row" else input_size
+        n_local = output_size // tp_size if parallel == "column" else output_size
+        self.quant_method = quant_method
+        quant_method.create_weights(self, k_local, [n_local], input_size, output_size, params_dtype, device=device)
+        self.bias = (torch.nn.Parameter(torch.zeros(n_local, dtype=params_dtype, device=device), requires_grad=False)
+                     if bias else None)
+
+    def shard_of(self, full: torch.Tensor, dim_n: int = 0, dim_k: int = 1) -> torch.Tensor:
+        """Slice a full [N,K]-shaped (or [N,...]-shaped) checkpoint tensor for this rank."""
+        if self.parallel == "column":
+            n = full.shape[dim_n] // self.tp_size
+            return full.narrow(dim_n, self.tp_rank * n, n)
+        if self.parallel == "row" and full.dim() > dim_k and full.shape[dim_k] > 1:
+            k = full.shape[dim_k] // self.tp_size
+            return full.narrow(dim_k, self.tp_rank * k, k)
+        return full
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        bias = self.bias
+        if self.parallel == "row" and self.tp_rank != 0:
+            bias = None
+        out = self.quant_method.apply(self, x, bias)
+        if self.parallel == "row" and self.tp_size > 1:
+            dist.all_reduce(out, group=self.tp_group)  # in place, on the compute stream (NCCL) / gloo on CPU
+        return out
+
+
+# ----------------------------------------------------------- sglang plug-in ----
+
+def install_into_sglang() -> List[str]:
+    """Monkey-patch an importable sglang / sgl_kernel so that their W8A8 linear methods call
+    this library (SURVEY 7.2 "coexistence").  Returns the names that were patched; with
+    neither package importable it returns [] (the torch.ops.sgl_kernel.* registration done
+    at import time is then the whole integration)."""
+    patched: List[str] = []
+    try:
+        import sgl_kernel  # type: ignore
+
+        for name in ("int8_scaled_mm", "fp8_scaled_mm", "fp8_blockwise_scaled_mm", "sgl_per_token_quant_fp8"):
+            setattr(sgl_kernel, name, getattr(ops, name))
+            patched.append(f"sgl_kernel.{name}")
+    except Exception:
+        pass
+    try:
+        from sglang.srt.layers.quantization import fp8_kernel, fp8_utils, int8_kernel, w8a8_int8  # type: ignore
+
+        int8_kernel.per_token_quant_int8 = ops.per_token_quant_int8
+        w8a8_int8.per_token_quant_int8 = ops.per_token_quant_int8
+        w8a8_int8.int8_scaled_mm = ops.int8_scaled_mm
+        fp8_kernel.sglang_per_token_quant_fp8 = ops.sglang_per_token_quant_fp8
+        fp8_utils.sglang_per_token_quant_fp8 = ops.sglang_per_token_quant_fp8
+        fp8_utils.fp8_scaled_mm = ops.fp8_scaled_mm
+        fp8_utils.fp8_blockwise_scaled_mm = ops.fp8_blockwise_scaled_mm
+        patched += ["sglang.srt.layers.quantization.{int8_kernel,w8a8_int8,fp8_kernel,fp8_utils}"]
+    except Exception:
+        pass
+    return patched

@@ -1,0 +1,380 @@
+"""bench.py -- the W8A8 quantized-linear hot path on B200, one JSON line per run.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+A "step" = one pass of the hot path (dynamic per-token int8 quantization -> tcgen05 int8 GEMM -> scale/bias
+epilogue -> bf16) over one batch of M synthetic tokens through every linear of the workload.  Default workload
+(BASELINE.json configs[1]): the Llama-3-8B W8A8-int8 linears QKV 4096->6144, gate_up 4096->28672,
+down 14336->4096 at M = 8192 tokens per GPU.  Weights are random-init int8 with per-channel fp32 scales and stay
+resident in HBM; activations are synthetic bf16 (reference test distribution, test/srt/cpu/test_gemm.py:133).
+
+  value     TOPS (2*M*N*K summed over the layers / device time), inputs already in HBM, CUDA events, max over ranks
+  e2e       same metric through the host-buffer entry (HostW8A8Int8Linear): pinned host activations -> device,
+            quantize + GEMM, bf16 outputs -> pinned host, every step, copies inside the timed region
+  roofline  the int8 GEMM kernel alone (events around its launches): achieved TOPS vs 2 x the measured cuBLAS bf16
+            peak of MEASURED_PEAKS.json (int8 tensor rate = 2 x bf16 on sm_100a); datasheet fraction alongside
+  cpu_baseline  the reference's own CPU path (oracle/_ref, compiled from /root/reference) -- or the oracle port
+            where that cannot run -- on the host cores, on a bounded row sample of the same workload
+  --impl reference   times only that CPU path (rank 0), same metric/config keys
+
+N > 1: one process per GPU, every rank runs the full workload on its own M tokens (rows are independent:
+M-sharded data parallel, weights replicated, NO collective on the data path) -> "scaling": "weak".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (description, M per GPU, [(layer, K, N)], has_bias)
+    "llama3-8b-w8a8-int8": ("Llama-3-8B W8A8-int8 linears (qkv 4096x6144, gate_up 4096x28672, down 14336x4096), "
+                            "M=8192 tokens/GPU", 8192,
+                            [("qkv_proj", 4096, 6144), ("gate_up_proj", 4096, 28672), ("down_proj", 14336, 4096)], False),
+    "c1-int8-128x4096x4096": ("int8 W8A8 linear M=128 K=4096 N=4096 bf16 out, bias", 128, [("linear", 4096, 4096)], True),
+    "wan2.1-14b-dit-int8": ("Wan2.1-14B DiT W8A8-int8 linears (5120x5120, 5120x13824, 13824x5120), M=32768 tokens "
+                            "sharded over the GPUs", 32768,
+                            [("attn_proj", 5120, 5120), ("ffn_up", 5120, 13824), ("ffn_down", 13824, 5120)], True),
+}
+DEFAULT_WORKLOAD = "llama3-8b-w8a8-int8"
+DATASHEET_INT8_TOPS = 4500.0
+CPU_SAMPLE_ROWS = 1024
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d.get("hbm_gbs", 6650.0), "bf16_burst": d.get("bf16_tflops", 1590.0),
+                "bf16_sustained": d.get("bf16_tflops_sustained", 1400.0), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "source": "fallback"}
+
+
+def total_ops(M, layers):
+    return sum(2.0 * M * N * K for _, K, N in layers)
+
+
+# ------------------------------------------------------------------ clocks ----
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU through NVML while the timed region runs."""
+
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, device_index: int, period_s: float = 0.02):
+        super().__init__(daemon=True)
+        self.period = period_s
+        self.samples, self.reason_bits, self.power = [], 0, []
+        self.sm_max = None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.nv = pynvml
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                self.reason_bits |= int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.power.append(self.nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def finish(self):
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": [], "samples": 0}
+        s = sorted(self.samples)
+        reasons = [n for b, n in self.REASONS.items() if self.reason_bits & b and n != "gpu_idle"]
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.sm_max, "reasons": reasons, "samples": len(s),
+                "power_w_max": round(max(self.power), 1) if self.power else None}
+
+
+# ------------------------------------------------------------ CPU reference ----
+
+def cpu_reference_run(layers, has_bias, sample_rows, warmup, steps, min_seconds=0.0):
+    """Times the reference CPU path on the host cores: int8_scaled_mm_with_quant on `sample_rows` rows of
+    every layer of the workload (weights prepacked once, untimed, as the reference does at load).
+    Returns (TOPS, seconds per step, kind, cores, steps actually timed)."""
+    from oracle import build_ref, restate
+
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    use_ref = build_ref.load()
+    kind = "reference" if use_ref else "port"
+    rows = sample_rows if use_ref else min(sample_rows, 64)  # the scalar port is ~100x slower
+    g = torch.Generator().manual_seed(1234)
+    probs = []
+    for _, K, N in layers:
+        x = (torch.randn(rows, K, generator=g) / 10).bfloat16()
+        W = ((torch.rand(N, K, generator=g) - 0.5) * 2 * 127).clamp(-128, 127).to(torch.int8)
+        Bs = torch.rand(N, generator=g) * 1e-2
+        b = torch.randn(N, generator=g).bfloat16().float() if has_bias else None
+        if use_ref:
+            W = torch.ops.sgl_kernel_ref.convert_weight_packed(W)
+        probs.append((x, W, Bs, b))
+
+    def step():
+        for x, W, Bs, b in probs:
+            if use_ref:
+                torch.ops.sgl_kernel_ref.int8_scaled_mm_with_quant(x, W, Bs, b, torch.bfloat16, True)
+            else:
+                restate.int8_scaled_mm_with_quant(x, W, Bs, b)
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    n = 0
+    while n < steps or (time.perf_counter() - t0) < min_seconds:
+        step()
+        n += 1
+        if n >= steps and min_seconds == 0.0:
+            break
+        if n >= 100000:
+            break
+    dt = (time.perf_counter() - t0) / n
+    tops = total_ops(rows, layers) / dt / 1e12
+    sample = (f"{rows} token rows of each of the {len(layers)} layers per step, {n} steps, weights prepacked once "
+              f"(untimed); {'oracle/_ref (reference sources compiled in place, AMX/AVX512)' if use_ref else 'oracle/restate.c scalar port (host lacks AMX/AVX512-BF16 or oracle/_ref missing)'}")
+    return tops, dt, kind, cores, n, sample, rows
+
+
+# ------------------------------------------------------------------- main ----
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    desc, M_cfg, layers, has_bias = WORKLOADS[args.workload]
+    sharded_total = args.workload.startswith("wan")
+    M = M_cfg // max(world, 1) if sharded_total else M_cfg
+    scaling = "strong" if sharded_total else "weak"
+    config = {"workload": desc, "name": args.workload, "tokens_per_gpu": M,
+              "layers": [{"name": n, "K": K, "N": N} for n, K, N in layers], "bias": has_bias,
+              "parallelism": f"dp{world} (M-sharded rows, weights replicated, no collective)",
+              "l2": "weights + activations per step exceed the 126 MB L2 (inputs larger than L2; no flush needed)"
+                    if sum(K * N for _, K, N in layers) > 126e6 else "L2 flushed between steps by a 256 MB memset"}
+
+    # ------------------------------------------------------ reference arm ----
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        tops, dt, kind, cores, n, sample, rows = cpu_reference_run(layers, has_bias, CPU_SAMPLE_ROWS, args.warmup,
+                                                                   args.steps)
+        config["tokens_per_gpu"] = rows
+        line = {"impl": "reference", "metric": "w8a8_int8_linear_tops", "value": round(tops, 4), "unit": "TOPS",
+                "n_gpus": args.gpus, "steps": n, "warmup": args.warmup, "ms_per_step": round(dt * 1e3, 4),
+                "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "int8",
+                "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": round(tops, 4), "unit": "TOPS", "cores": cores, "kind": kind, "sample": sample},
+                "e2e": {"value": round(tops, 4), "unit": "TOPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
+        return
+
+    # ------------------------------------------------------------ our arm ----
+    import torch.distributed as dist
+
+    import sglang_diffusion_b200 as b2  # fails loudly when the CUDA library is missing
+
+    assert torch.cuda.is_available(), "bench.py (impl ours) needs a B200; there is no CPU fallback"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local_rank])
+        torch.cuda.synchronize(dev)
+
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    probs = []
+    for _, K, N in layers:
+        x = (torch.randn(M, K, generator=g, device=dev) / 10).bfloat16()
+        W = torch.randint(-127, 128, (N, K), dtype=torch.int8, generator=g, device=dev)
+        Bs = torch.rand(N, generator=g, device=dev) * 1e-2
+        b = torch.randn(N, generator=g, device=dev).bfloat16() if has_bias else None
+        probs.append((x, W, Bs, b))
+    flush = None
+    if sum(K * N for _, K, N in layers) <= 126e6:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step():
+        outs = []
+        for x, W, Bs, b in probs:
+            outs.append(b2.int8_scaled_mm_with_quant(x, W, Bs, b, torch.bfloat16, False))
+        return outs
+
+    ops_step = total_ops(M, layers)
+    for _ in range(args.warmup):
+        step()
+    barrier()
+
+    # -- value: K steps, device-timed, barrier + synchronize on both sides, max over ranks
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    b2.capi.reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    flush_ms = 0.0
+    barrier()
+    if flush is None:
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+        barrier()
+        elapsed_ms = e0.elapsed_time(e1)
+    else:  # small working set: flush L2 before every step, time each step on its own
+        elapsed_ms = 0.0
+        for _ in range(args.steps):
+            flush.zero_()
+            e0.record()
+            step()
+            e1.record()
+            torch.cuda.synchronize(dev)
+            elapsed_ms += e0.elapsed_time(e1)
+        barrier()
+    launches = b2.capi.launch_count()
+    clocks = sampler.finish()
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(t.item())
+    ms_per_step = elapsed_ms / args.steps
+    value = world * ops_step / (ms_per_step * 1e-3) / 1e12
+
+    # -- roofline: the GEMM kernel alone (quantized activations prepared outside the timed launches)
+    peaks = load_peaks()
+    qs = [b2.per_token_quant_int8(x) for x, _, _, _ in probs]
+    gemm_ms = 0.0
+    n_gemm = 0
+    ge0, ge1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = max(3, min(args.steps, 50))
+    for it in range(3 + reps):
+        for (x, W, Bs, b), (q, s) in zip(probs, qs):
+            if flush is not None:
+                flush.zero_()
+            ge0.record()
+            b2.int8_scaled_mm(q, W.t(), s, Bs.view(-1, 1), torch.bfloat16, b)
+            ge1.record()
+            torch.cuda.synchronize(dev)
+            if it >= 3:
+                gemm_ms += ge0.elapsed_time(ge1)
+                n_gemm += 1
+    gemm_cfg = b2.capi.last_gemm_config()
+    gemm_tops = reps * ops_step / (gemm_ms * 1e-3) / 1e12
+    peak_tops = 2.0 * peaks["bf16_sustained"]
+    roofline = {"bound": "tensor", "kernel": f"gemm_w8a8_kernel<kind::i8> ({gemm_cfg})",
+                "achieved": round(gemm_tops, 1), "peak": round(peak_tops, 1), "unit": "TFLOP/s",
+                "frac": round(gemm_tops / peak_tops, 4), "traffic": None,
+                "peak_source": f"2 x bf16_tflops_sustained of MEASURED_PEAKS.json ({peaks['source']}); int8 MMA rate = 2 x bf16",
+                "frac_of_datasheet_4500": round(gemm_tops / DATASHEET_INT8_TOPS, 4),
+                "frac_of_2x_bf16_burst": round(gemm_tops / (2.0 * peaks["bf16_burst"]), 4),
+                "avg_launch_us": round(gemm_ms * 1e3 / n_gemm, 2), "launches_timed": n_gemm}
+    del qs
+
+    # -- e2e: host buffers in, host buffers out, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        host_layers = []
+        for (x, W, Bs, b) in probs:
+            hl = b2.HostW8A8Int8Linear(W, Bs, b, device=dev, chunk_rows=min(1024, M))
+            xh = torch.empty(x.shape, dtype=torch.bfloat16).pin_memory()
+            xh.copy_(x)
+            oh = torch.empty(M, W.shape[0], dtype=torch.bfloat16).pin_memory()
+            host_layers.append((hl, xh, oh))
+        e2e_steps = max(3, min(args.steps, 20))
+        for _ in range(2):
+            for hl, xh, oh in host_layers:
+                hl(xh, oh)
+        barrier()
+        t0 = time.perf_counter()
+        ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ee0.record()
+        for _ in range(e2e_steps):
+            for hl, xh, oh in host_layers:
+                hl(xh, oh)
+        ee1.record()
+        barrier()
+        e2e_ms = max(ee0.elapsed_time(ee1), 0.0)
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        e2e_ms = max(e2e_ms, 0.0)
+        tt = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tt.item()) / e2e_steps
+        h2d = sum(xh.numel() * 2 for _, xh, _ in host_layers)
+        d2h = sum(oh.numel() * 2 for _, _, oh in host_layers)
+        # check the host result of the last step against the device-resident path (bitwise)
+        ref_out = step()
+        same = all(torch.equal(oh.view(torch.int16), o.cpu().view(torch.int16)) for (_, _, oh), o in zip(host_layers, ref_out))
+        e2e = {"value": round(world * ops_step / (e2e_ms * 1e-3) / 1e12, 2), "unit": "TOPS",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": round(e2e_ms, 3),
+               "steps": e2e_steps, "host_wall_ms_per_step": round(wall_ms / e2e_steps, 3),
+               "pcie_gbs": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1), "matches_device_path_bitwise": bool(same)}
+        del host_layers
+
+    # -- cpu baseline (rank 0, N = 1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        tops, dt, kind, cores, n, sample, rows = cpu_reference_run(layers, has_bias, CPU_SAMPLE_ROWS, 2, 5, min_seconds=8.0)
+        cpu = {"value": round(tops, 4), "unit": "TOPS", "cores": cores, "kind": kind, "sample": sample,
+               "ms_per_step": round(dt * 1e3, 3)}
+
+    if rank == 0:
+        line = {"metric": "w8a8_int8_linear_tops", "value": round(value, 1), "unit": "TOPS", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
+                "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "int8",
+                "data": "synthetic", "config": config, "tokens_per_s": round(world * M / (ms_per_step * 1e-3), 1),
+                "frac_of_datasheet_int8_4500_tops": round(value / world / DATASHEET_INT8_TOPS, 4),
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

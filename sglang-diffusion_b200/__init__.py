@@ -57,12 +57,16 @@ from .linear import (  # noqa: E402,F401
     apply_fp8_linear,
     cutlass_w8a8_block_fp8_linear_with_fallback,
     install_into_sglang,
+    shard_rows,
 )
 
+from .host_api import HostW8A8Int8Linear  # noqa: E402,F401
+
 __all__ = [
+    "HostW8A8Int8Linear",
     "capi", "ops", "int8_scaled_mm", "fp8_scaled_mm", "fp8_blockwise_scaled_mm", "sgl_per_token_quant_fp8",
     "sgl_per_token_group_quant_8bit", "per_token_quant_int8", "per_token_quant_int8_cpu",
     "int8_scaled_mm_with_quant", "sglang_per_token_quant_fp8", "sglang_per_token_group_quant_fp8",
     "per_token_group_quant_fp8", "W8A8Int8LinearMethod", "W8A8Fp8LinearMethod", "W8A8BlockFp8LinearMethod",
-    "QuantLinear", "apply_fp8_linear", "cutlass_w8a8_block_fp8_linear_with_fallback", "install_into_sglang",
+    "QuantLinear", "apply_fp8_linear", "cutlass_w8a8_block_fp8_linear_with_fallback", "install_into_sglang", "shard_rows",
 ]

@@ -142,6 +142,17 @@ class W8A8BlockFp8LinearMethod:
 
 # ------------------------------------------------------ TP caller (linear.py) ----
 
+def shard_rows(M: int, rank: int, world_size: int):
+    """Contiguous row block [start, stop) of rank `rank` when M token rows are split over
+    `world_size` data-parallel ranks (weights replicated, no collective: per-token scales make
+    every output row depend on its own input row only -- SURVEY 8e).  The first M % world_size
+    ranks take one extra row, so block sizes differ by at most one and concatenate in rank order."""
+    assert 0 <= rank < world_size and M >= 0
+    base, extra = divmod(M, world_size)
+    start = rank * base + min(rank, extra)
+    return start, start + base + (1 if rank < extra else 0)
+
+
 class QuantLinear(torch.nn.Module):
     """The part of Column/RowParallelLinear.forward that is on the path.
 

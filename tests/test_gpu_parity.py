@@ -1,0 +1,479 @@
+"""GPU parity tests (-m gpu): the CUDA path vs the oracle on the same seeded inputs, called through
+the C ABI (ctypes, exactly what a cgo/JNI/FFI host would bind) and through the torch ops registered
+over it.  Bars: integer codes, scales, int32 accumulators and the int8 path's bf16 outputs are
+BIT-EXACT; e4m3 codes are bit-exact against the IEEE restatement; fp8 GEMM outputs are held to the
+reference's own test tolerance (sgl-kernel/tests/test_fp8_gemm.py:33-35: rtol 0.02, atol 1 on +-448
+inputs) and to 1 bf16 ulp of the fp64-accumulated restatement on realistic inputs.
+"""
+from __future__ import annotations
+
+import pytest
+import torch
+
+from conftest import (bf16_bits, golden_names, load_golden, mk_fp8_block_weight, mk_fp8_weight, mk_int8_problem)
+
+pytestmark = pytest.mark.gpu
+
+import sglang_diffusion_b200 as b2  # noqa: E402
+from oracle import restate  # noqa: E402  (the checker)
+
+capi = b2.capi
+DEV = "cuda:0"
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def c_quant_int8(x: torch.Tensor):
+    M, K = x.shape
+    q = torch.empty(M, K, dtype=torch.int8, device=x.device)
+    s = torch.empty(M, dtype=torch.float32, device=x.device)
+    dt = capi.DTYPE_BF16 if x.dtype == torch.bfloat16 else capi.DTYPE_F16
+    capi.check(capi.lib.b2_quant_int8_rows(x.data_ptr(), dt, x.stride(0), q.data_ptr(), K, s.data_ptr(), M, K, _stream()))
+    return q, s
+
+
+def c_gemm_s8(A, W, As, Bs, bias, out_dtype=torch.bfloat16, cfg=0):
+    M, K = A.shape
+    N = W.shape[0]
+    if out_dtype == torch.int32:
+        D = torch.empty(M, N, dtype=torch.int32, device=A.device)
+        od = capi.DTYPE_S32
+    else:
+        D = torch.empty(M, N, dtype=out_dtype, device=A.device)
+        od = capi.DTYPE_BF16 if out_dtype == torch.bfloat16 else capi.DTYPE_F16
+    bd = capi.DTYPE_F32
+    if bias is not None:
+        bd = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16, torch.float32: capi.DTYPE_F32}[bias.dtype]
+    capi.set_gemm_config(cfg)
+    try:
+        capi.check(capi.lib.b2_gemm_s8(A.data_ptr(), A.stride(0), W.data_ptr(), W.stride(0),
+                                       None if As is None else As.data_ptr(), None if Bs is None else Bs.data_ptr(),
+                                       None if bias is None else bias.data_ptr(), bd, D.data_ptr(), N, od, M, N, K,
+                                       _stream()))
+    finally:
+        capi.set_gemm_config(0)
+    return D
+
+
+def exact_acc(A: torch.Tensor, W: torch.Tensor) -> torch.Tensor:
+    """Exact int32 accumulators on the GPU in fp64 (|acc| <= 127*128*K << 2^53); independent of our kernels."""
+    return (A.double() @ W.double().t()).to(torch.int32)
+
+
+# ============================================================ int8 quantizer ====
+
+@pytest.mark.parametrize("M,K", [(1, 32), (1, 512), (3, 544), (5, 4096), (128, 4096), (257, 14336), (7, 16384),
+                                 (33, 5120), (2, 13824), (1024, 3072), (4, 32768)])
+def test_quant_int8_bit_exact(M, K):
+    x, _, _, _ = mk_int8_problem(M, 8, K, seed=M * 131 + K)
+    q_ref, s_ref = restate.per_token_quant_int8_cpu(x)
+    q, s = c_quant_int8(x.to(DEV))
+    assert torch.equal((q.cpu().to(torch.int16) + 128).to(torch.uint8), q_ref)
+    assert torch.equal(s.cpu().view(torch.int32), s_ref.view(torch.int32))
+
+
+@pytest.mark.parametrize("name", golden_names("int8_"))
+def test_quant_int8_matches_reference_golden(name):
+    g = load_golden(name)
+    q, s = c_quant_int8(g["A"].to(DEV))
+    assert torch.equal((q.cpu().to(torch.int16) + 128).to(torch.uint8), g["Aq_u8"])
+    assert torch.equal(s.cpu().view(torch.int32), g["As"].view(torch.int32))
+
+
+def test_quant_int8_edge_rows_and_strided_input():
+    K = 1024
+    x = torch.zeros(6, K + 64, dtype=torch.bfloat16)
+    x[1, 5] = 3.0e38          # near bf16 max
+    x[2] = 1e-8               # below the 1e-7 eps
+    x[3, ::2] = 0.5           # ties: 63.5 -> 64 (half to even)
+    x[3, 1::2] = -1.0
+    x[4] = torch.linspace(-1, 1, K + 64).bfloat16()
+    x[5, :K] = -7.0
+    x[:, K:] = 1000.0         # the padding columns must not be read
+    xv = x[:, :K]
+    q_ref, s_ref = restate.per_token_quant_int8_cpu(xv)
+    q, s = c_quant_int8(x.to(DEV)[:, :K])
+    assert torch.equal((q.cpu().to(torch.int16) + 128).to(torch.uint8), q_ref)
+    assert torch.equal(s.cpu().view(torch.int32), s_ref.view(torch.int32))
+    assert torch.all(q[0] == 0) and torch.all(q[3, ::2] == 64) and torch.all(q[5] == -127)
+
+
+def test_quant_int8_python_wrapper_shapes():
+    """Signature of int8_kernel.py:59-89: any leading dims, scales [..., 1]."""
+    x = (torch.randn(2, 5, 256) / 10).bfloat16().to(DEV)
+    q, s = b2.per_token_quant_int8(x)
+    assert q.shape == x.shape and q.dtype == torch.int8 and s.shape == (2, 5, 1) and s.dtype == torch.float32
+    q_ref, s_ref = restate.per_token_quant_int8_cpu(x.cpu().view(-1, 256))
+    assert torch.equal((q.cpu().view(-1, 256).to(torch.int16) + 128).to(torch.uint8), q_ref)
+
+
+def test_quant_int8_f16_input_supported_on_gpu():
+    """The CPU reference aborts on fp16; the GPU op takes it, with the same arithmetic."""
+    x = (torch.randn(9, 512) / 10).half()
+    q, s = c_quant_int8(x.to(DEV))
+    xf = x.float()
+    amax = xf.abs().amax(dim=1).clamp_min(1e-7)
+    inv = torch.full_like(amax, 127.0) / amax
+    want = torch.round(xf * inv[:, None]).to(torch.int8)  # torch.round = half to even
+    assert torch.equal(q.cpu(), want)
+    assert torch.equal(s.cpu(), amax / 127.0)
+
+
+# ====================================================== int8 GEMM accumulators ====
+
+@pytest.mark.parametrize("cfg", [1, 2, 3, 4])
+@pytest.mark.parametrize("M,N,K", [(128, 256, 256), (300, 1000, 544), (1, 264, 16), (129, 8, 4096), (5, 384, 544)])
+def test_gemm_s8_raw_accumulators_exact_every_tile_config(cfg, M, N, K):
+    g = torch.Generator().manual_seed(M * 7 + N * 3 + K + cfg)
+    A = torch.randint(-128, 128, (M, K), dtype=torch.int8, generator=g).to(DEV)
+    W = torch.randint(-128, 128, (N, K), dtype=torch.int8, generator=g).to(DEV)
+    D = c_gemm_s8(A, W, None, None, None, torch.int32, cfg)
+    assert torch.equal(D, exact_acc(A, W))
+
+
+def test_gemm_s8_extreme_codes_do_not_saturate():
+    """K = 16384 of (-128)*(-128) = 2.7e8 < 2^31: the accumulator must be exact, not saturated."""
+    M, N, K = 130, 136, 16384
+    A = torch.full((M, K), -128, dtype=torch.int8, device=DEV)
+    W = torch.full((N, K), -128, dtype=torch.int8, device=DEV)
+    W[1] = 127
+    D = c_gemm_s8(A, W, None, None, None, torch.int32)
+    assert torch.all(D[:, 0] == 128 * 128 * K) and torch.all(D[:, 1] == -128 * 127 * K)
+
+
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 5, 8, 16, 17, 127, 128, 129, 255, 256, 257, 1000])
+def test_gemm_s8_accumulators_m_sweep_auto_config(M):
+    N, K = 1536, 1024
+    g = torch.Generator().manual_seed(M)
+    A = torch.randint(-127, 128, (M, K), dtype=torch.int8, generator=g).to(DEV)
+    W = torch.randint(-128, 128, (N, K), dtype=torch.int8, generator=g).to(DEV)
+    assert torch.equal(c_gemm_s8(A, W, None, None, None, torch.int32), exact_acc(A, W))
+
+
+def test_gemm_s8_strided_a_and_w():
+    """mat_a may have stride(0) != K (int8_gemm_kernel.cu:674 only checks stride(1) == 1)."""
+    M, N, K = 70, 200, 512
+    g = torch.Generator().manual_seed(3)
+    Ab = torch.randint(-127, 128, (M, K + 128), dtype=torch.int8, generator=g).to(DEV)
+    Wb = torch.randint(-127, 128, (N, K + 64), dtype=torch.int8, generator=g).to(DEV)
+    A, W = Ab[:, :K], Wb[:, :K]
+    assert torch.equal(c_gemm_s8(A, W, None, None, None, torch.int32), exact_acc(A, W))
+
+
+# ============================================ int8 linear: bf16 output bit-exact ====
+
+@pytest.mark.parametrize("name", golden_names("int8_"))
+@pytest.mark.parametrize("fused", [False, True])
+def test_int8_linear_matches_reference_golden_bitwise(name, fused):
+    g = load_golden(name)
+    x, W, Bs = g["A"].to(DEV), g["W"].to(DEV), g["Bs"].to(DEV)
+    bias = g["bias"].to(DEV) if "bias" in g else None  # fp32, as the CPU op takes it
+    if fused:
+        out = b2.int8_scaled_mm_with_quant(x, W, Bs, bias, torch.bfloat16, False)
+    else:
+        q, s = c_quant_int8(x)
+        out = c_gemm_s8(q, W, s, Bs, bias)
+    assert torch.equal(bf16_bits(out.cpu()), bf16_bits(g["out"]))
+
+
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 5, 127, 128, 130])
+@pytest.mark.parametrize("has_bias", [False, True])
+def test_int8_linear_reference_test_grid_bitwise(M, has_bias):
+    """test/srt/cpu/test_gemm.py grid: N=384, K=544 (K % 128 != 0 exercises the TMA K tail)."""
+    x, W, Bs, b = mk_int8_problem(M, 384, 544, seed=1234 + M, bias=has_bias)
+    ref = restate.int8_scaled_mm_with_quant(x, W, Bs, b.float() if has_bias else None)
+    out = b2.int8_scaled_mm_with_quant(x.to(DEV), W.to(DEV), Bs.to(DEV), b.to(DEV) if has_bias else None,
+                                       torch.bfloat16, False)
+    assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref))
+
+
+@pytest.mark.parametrize("cfg", [1, 2, 3, 4])
+def test_int8_c1_bitwise_every_tile_config(cfg):
+    """BASELINE config C1: M=128 K=4096 N=4096, bf16 out, bias."""
+    x, W, Bs, b = mk_int8_problem(128, 4096, 4096)
+    ref, q_ref, s_ref, acc_ref = restate.int8_scaled_mm_with_quant(x, W, Bs, b.float(), return_parts=True)
+    q, s = c_quant_int8(x.to(DEV))
+    Wd = W.to(DEV)
+    acc = c_gemm_s8(q, Wd, None, None, None, torch.int32, cfg)
+    assert torch.equal(acc.cpu(), acc_ref)
+    out = c_gemm_s8(q, Wd, s, Bs.to(DEV), b.to(DEV), torch.bfloat16, cfg)
+    assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref))
+
+
+def test_int8_scaled_mm_op_reference_call_convention():
+    """The call W8A8Int8LinearMethod.apply makes (w8a8_int8.py:216-231): mat_b = weight.t(), scales [M,1]/[N,1]."""
+    x, W, Bs, b = mk_int8_problem(33, 160, 1024, seed=5)
+    ref = restate.int8_scaled_mm_with_quant(x, W, Bs, b.float())
+    layer = torch.nn.Module()
+    m = b2.W8A8Int8LinearMethod()
+    m.create_weights(layer, 1024, [160], 1024, 160, torch.bfloat16, device=DEV)
+    layer.weight.data.copy_(W)
+    layer.weight_scale.data.copy_(Bs.view(-1, 1))
+    m.process_weights_after_loading(layer)
+    out = m.apply(layer, x.to(DEV).view(3, 11, 1024), b.to(DEV))
+    assert out.shape == (3, 11, 160)
+    assert torch.equal(bf16_bits(out.cpu().view(33, 160)), bf16_bits(ref))
+    out_f = b2.W8A8Int8LinearMethod(fused=True).apply(layer, x.to(DEV), b.to(DEV))
+    assert torch.equal(bf16_bits(out_f.cpu()), bf16_bits(ref))
+
+
+def test_int8_f16_output_epilogue():
+    x, W, Bs, b = mk_int8_problem(17, 64, 256, seed=8)
+    xh = x.half()
+    q, s = c_quant_int8(xh.to(DEV))
+    out = c_gemm_s8(q, W.to(DEV), s, Bs.to(DEV), b.half().to(DEV), torch.float16)
+    acc = exact_acc(q, W.to(DEV)).float()
+    want = torch.addcmul(b.half().float().to(DEV).double(), (acc * s[:, None]).double(), Bs.to(DEV).double()[None, :])
+    # fma(t, Bs, bias) rounded once to fp32 == fp64 addcmul rounded to fp32 except for double rounding (rare): allow 1 ulp of f16
+    torch.testing.assert_close(out.float(), want.float().half().float(), rtol=2e-3, atol=1e-3)
+
+
+# =========================================== full BASELINE sizes: property tests ====
+
+@pytest.mark.parametrize("K,N", [(4096, 6144), (4096, 28672), (14336, 4096)])
+def test_llama8b_shapes_m8192_checksum_and_sampled_rows(K, N):
+    """C2 at M=8192.  Size-independent properties: (1) column checksum -- sum_n acc[m,n] == A[m,:] . (sum_n W[n,:])
+    exactly, in int64; (2) 48 sampled rows bit-exact against the CPU oracle end to end (codes, scales, bf16)."""
+    M = 8192
+    g = torch.Generator(device=DEV).manual_seed(K + N)
+    x = (torch.randn(M, K, generator=g, device=DEV) / 10).bfloat16()
+    x[:, ::512] *= 30  # outlier channels
+    W = torch.randint(-128, 128, (N, K), dtype=torch.int8, generator=g, device=DEV)
+    Bs = torch.rand(N, generator=g, device=DEV) * 1e-2
+    bias = torch.randn(N, generator=g, device=DEV).bfloat16()
+    q, s = c_quant_int8(x)
+    acc = c_gemm_s8(q, W, None, None, None, torch.int32)
+    wsum = W.double().sum(dim=0)                       # exact: |.| <= 128*28672
+    want = (q.double() @ wsum).to(torch.int64)         # exact: < 2^53
+    got = acc.to(torch.int64).sum(dim=1)
+    assert torch.equal(got, want)
+    out = b2.int8_scaled_mm_with_quant(x, W, Bs, bias, torch.bfloat16, False)
+    rows = torch.randperm(M, generator=torch.Generator().manual_seed(1))[:48].sort().values
+    ref, q_ref, s_ref, acc_ref = restate.int8_scaled_mm_with_quant(x[rows.to(DEV)].cpu(), W.cpu(), Bs.cpu(),
+                                                                   bias.float().cpu(), return_parts=True)
+    assert torch.equal((q[rows.to(DEV)].cpu().to(torch.int16) + 128).to(torch.uint8), q_ref)
+    assert torch.equal(acc[rows.to(DEV)].cpu(), acc_ref)
+    assert torch.equal(bf16_bits(out[rows.to(DEV)].cpu()), bf16_bits(ref))
+
+
+def test_m_sharded_rows_equal_unsharded_bitwise():
+    """C4 (DiT, Wan2.1 hidden 5120): splitting M over ranks changes nothing -- rows are independent."""
+    M, K, N = 4096, 5120, 5120
+    g = torch.Generator(device=DEV).manual_seed(4)
+    x = (torch.randn(M, K, generator=g, device=DEV) / 10).bfloat16()
+    W = torch.randint(-127, 128, (N, K), dtype=torch.int8, generator=g, device=DEV)
+    Bs = torch.rand(N, generator=g, device=DEV) * 1e-2
+    full = b2.int8_scaled_mm_with_quant(x, W, Bs, None, torch.bfloat16, False)
+    for world in (2, 8):
+        parts = []
+        for r in range(world):
+            a, b = b2.shard_rows(M, r, world)
+            parts.append(b2.int8_scaled_mm_with_quant(x[a:b], W, Bs, None, torch.bfloat16, False))
+        assert torch.equal(bf16_bits(torch.cat(parts)), bf16_bits(full))
+
+
+def test_gemm_s8_linearity_in_weights():
+    """acc(A, W1 + W2) == acc(A, W1) + acc(A, W2) exactly (int32), at a DiT shape."""
+    M, K, N = 2048, 3072, 9216
+    g = torch.Generator(device=DEV).manual_seed(6)
+    A = torch.randint(-127, 128, (M, K), dtype=torch.int8, generator=g, device=DEV)
+    W1 = torch.randint(-60, 61, (N, K), dtype=torch.int8, generator=g, device=DEV)
+    W2 = torch.randint(-60, 61, (N, K), dtype=torch.int8, generator=g, device=DEV)
+    a12 = c_gemm_s8(A, W1 + W2, None, None, None, torch.int32)
+    assert torch.equal(a12, c_gemm_s8(A, W1, None, None, None, torch.int32) + c_gemm_s8(A, W2, None, None, None, torch.int32))
+
+
+# ================================================================ fp8 quantizers ====
+
+@pytest.mark.parametrize("M", [128, 256, 512])
+@pytest.mark.parametrize("K", [512, 1076, 1368, 2048, 4096])
+def test_per_token_quant_fp8_reference_grid(M, K):
+    """Grid of sgl-kernel/tests/test_per_token_quant_fp8.py (1076/1368 are the vec-4 shapes); bit-exact vs the
+    IEEE restatement, which is tighter than the reference's own 1e-3 check."""
+    g = torch.Generator().manual_seed(M + K)
+    x = torch.randn(M, K, generator=g).bfloat16()
+    q_ref, s_ref = restate.per_token_quant_fp8(x)
+    q, s = b2.sglang_per_token_quant_fp8(x.to(DEV))
+    assert s.shape == (M, 1)
+    assert torch.equal(q.cpu().view(torch.uint8), q_ref)
+    assert torch.equal(s.cpu().view(-1).view(torch.int32), s_ref.view(torch.int32))
+
+
+def test_per_token_quant_fp8_zero_row_and_saturation():
+    x = torch.zeros(4, 256, dtype=torch.bfloat16)
+    x[1, 3] = 5.0
+    x[2] = -2.0
+    x[3, 0] = 3.0e38
+    q, s = b2.sglang_per_token_quant_fp8(x.to(DEV))
+    q8 = q.cpu().view(torch.uint8)
+    assert s[0].item() == 0 and torch.all(q8[0] == 0)            # per_token_quant_fp8.cu: s == 0 -> inv = 0
+    assert q8[1, 3].item() == 0x7E and q8[2, 0].item() == 0xFE   # +-448 codes
+    q_ref, s_ref = restate.per_token_quant_fp8(x)
+    assert torch.equal(q8, q_ref) and torch.equal(s.cpu().view(-1), s_ref)
+
+
+@pytest.mark.parametrize("M,K", [(1, 128), (1, 512), (3, 7168), (127, 7168), (512, 2048), (4096, 1536)])
+@pytest.mark.parametrize("colmajor", [True, False])
+def test_group_quant_fp8_128_bit_exact(M, K, colmajor):
+    g = torch.Generator().manual_seed(M * 3 + K)
+    x = (torch.randn(M, K, generator=g) / 10).bfloat16()
+    if M > 2:
+        x[2, :128].zero_()   # eps path
+    q_ref, s_ref = restate.per_token_group_quant_fp8(x, 128, 1e-10, colmajor)
+    q, s = b2.per_token_group_quant_fp8(x.to(DEV), 128, column_major_scales=colmajor)
+    assert s.shape == (M, K // 128)
+    if colmajor and M > 1 and K > 128:
+        assert s.stride() == (1, M)
+    assert torch.equal(q.cpu().view(torch.uint8), q_ref)
+    assert torch.equal(s.cpu().contiguous().view(torch.int32), s_ref.contiguous().view(torch.int32))
+
+
+# ===================================================================== fp8 GEMMs ====
+
+def _ulp_bf16(t: torch.Tensor) -> torch.Tensor:
+    return torch.maximum(t.abs(), torch.full_like(t, 2.0 ** -126)).log2().floor().exp2() * 2.0 ** -7
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 512, 512), (5, 128, 512), (64, 1280, 8192), (64, 8192, 1024),
+                                   (300, 7168, 1024), (1024, 8192, 3584)])
+@pytest.mark.parametrize("has_bias", [False, True])
+def test_fp8_scaled_mm_vs_restatement(M, N, K, has_bias):
+    """C5 shard shapes.  fp32 tensor-core accumulation vs exact-product fp64 accumulation: within
+    1e-2 normalised, and >= 99 % of outputs equal to the bf16 rounding of the exact result (<= 1 ulp all)."""
+    g = torch.Generator().manual_seed(M + N + K)
+    x = (torch.randn(M, K, generator=g) / 10).bfloat16()
+    Wq, ws = mk_fp8_weight(N, K)
+    bias = torch.randn(N, generator=g).bfloat16() if has_bias else None
+    q_ref, s_ref = restate.per_token_quant_fp8(x)
+    ref = restate.fp8_scaled_mm(q_ref, Wq.view(torch.uint8), s_ref, ws, bias.float() if has_bias else None)
+    out = b2.apply_fp8_linear(x.to(DEV), Wq.to(DEV).t(), ws.to(DEV), bias=bias.to(DEV) if has_bias else None)
+    o = out.float().cpu()
+    assert ((o - ref).abs().max() / ref.abs().max()).item() < 1e-2
+    assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 1e-6 * ref.abs().max())
+    assert (o == ref.bfloat16().float()).float().mean().item() > 0.99
+
+
+@pytest.mark.parametrize("cfg", [1, 2, 3, 4])
+def test_fp8_scaled_mm_reference_test_distribution(cfg):
+    """sgl-kernel/tests/test_fp8_gemm.py: operands uniform in +-448, scales randn*1e-3... rtol 0.02, atol 1."""
+    M, N, K = 257, 1024, 2048
+    g = torch.Generator(device=DEV).manual_seed(cfg)
+    a = ((torch.rand(M, K, generator=g, device=DEV) * 2 - 1) * 448).to(torch.float8_e4m3fn)
+    b = ((torch.rand(N, K, generator=g, device=DEV) * 2 - 1) * 448).to(torch.float8_e4m3fn)
+    sa = torch.randn(M, generator=g, device=DEV) * 1e-3
+    sb = torch.randn(N, generator=g, device=DEV) * 1e-3
+    bias = torch.randn(N, generator=g, device=DEV).bfloat16()
+    capi.set_gemm_config(cfg)
+    try:
+        out = b2.fp8_scaled_mm(a, b.t(), sa.view(-1, 1), sb.view(-1, 1), torch.bfloat16, bias)
+    finally:
+        capi.set_gemm_config(0)
+    o = (a.double() @ b.double().t()) * sa.double()[:, None] * sb.double()[None, :] + bias.double()
+    torch.testing.assert_close(out.double(), o, rtol=0.02, atol=1)
+    torch.testing.assert_close(out.double(), o, rtol=1e-2, atol=1e-2 * o.abs().max().item())
+
+
+@pytest.mark.parametrize("M", [1, 3, 5, 127, 128, 512, 1024])
+@pytest.mark.parametrize("N,K", [(512, 512), (2048, 7168), (4096, 1536)])
+def test_fp8_blockwise_scaled_mm(M, N, K):
+    """Grid after sgl-kernel/tests/test_fp8_blockwise_gemm.py (M list incl. non-multiples of 4: no padding copies
+    here); scales in the reference's layouts -- SFA M-major, SFB K-major (:76-77)."""
+    g = torch.Generator().manual_seed(M + N)
+    x = (torch.randn(M, K, generator=g) / 10).bfloat16()
+    Wq, sfb = mk_fp8_block_weight(N, K)
+    q_ref, sfa_ref = restate.per_token_group_quant_fp8(x, 128, 1e-10, True)
+    ref = restate.fp8_blockwise_scaled_mm(q_ref, Wq.view(torch.uint8), sfa_ref, sfb)
+    out = b2.cutlass_w8a8_block_fp8_linear_with_fallback(x.to(DEV), Wq.to(DEV), [128, 128], sfb.to(DEV))
+    o = out.float().cpu()
+    assert ((o - ref).abs().max() / ref.abs().max()).item() < 1e-2
+    assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 2e-6 * ref.abs().max())
+
+
+@pytest.mark.parametrize("name", golden_names("fp8w8a16_"))
+def test_fp8_blockwise_vs_reference_cpu_golden(name):
+    """Against the reference's own fp8_scaled_mm_cpu output (W8A16): agreement is bounded by the e4m3
+    rounding of the activations (~2.5 % Frobenius, see tests/test_oracle.py); bound 4 %."""
+    g = load_golden(name)
+    out = b2.cutlass_w8a8_block_fp8_linear_with_fallback(
+        g["A"].to(DEV), g["W"].view(torch.float8_e4m3fn).to(DEV), [128, 128], g["sfb"].to(DEV),
+        bias=g["bias"].bfloat16().to(DEV) if "bias" in g else None)
+    ref = g["out"].float()
+    assert ((out.float().cpu() - ref).norm() / ref.norm()).item() < 4e-2
+
+
+def test_fp8_blockwise_c3_shape_m4096_sampled():
+    """C3 (DeepSeek-V3, M=4096): (N,K) = (7168, 2048); 16 sampled rows against the restatement."""
+    M, N, K = 4096, 7168, 2048
+    g = torch.Generator().manual_seed(2)
+    x = (torch.randn(M, K, generator=g) / 10).bfloat16()
+    Wq, sfb = mk_fp8_block_weight(N, K)
+    out = b2.cutlass_w8a8_block_fp8_linear_with_fallback(x.to(DEV), Wq.to(DEV), [128, 128], sfb.to(DEV))
+    rows = torch.arange(0, M, 257)[:16]
+    q_ref, sfa_ref = restate.per_token_group_quant_fp8(x[rows].contiguous(), 128, 1e-10, True)
+    ref = restate.fp8_blockwise_scaled_mm(q_ref, Wq.view(torch.uint8), sfa_ref, sfb)
+    o = out[rows.to(DEV)].float().cpu()
+    assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 2e-6 * ref.abs().max())
+
+
+# ================================================== boundary behaviour on the GPU ====
+
+def test_argument_errors_follow_reference_checks():
+    a = torch.zeros(4, 64, dtype=torch.int8, device=DEV)
+    w = torch.zeros(32, 64, dtype=torch.int8, device=DEV)
+    sa, sb = torch.ones(4, device=DEV), torch.ones(32, device=DEV)
+    with pytest.raises(RuntimeError, match="column major"):
+        b2.int8_scaled_mm(a, w.t().contiguous(), sa, sb, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="Half or BFloat16"):
+        b2.int8_scaled_mm(a, w.t(), sa, sb, torch.float32)
+    with pytest.raises(RuntimeError, match="scales_a"):
+        b2.int8_scaled_mm(a, w.t(), sa[:3], sb, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="bias dtype"):
+        b2.int8_scaled_mm(a, w.t(), sa, sb, torch.bfloat16, torch.zeros(32, device=DEV))
+    with pytest.raises(RuntimeError, match="multiple of 16"):
+        b2.int8_scaled_mm(a[:, :40], w[:, :40].t(), sa, sb, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="Int8"):
+        b2.int8_scaled_mm(a.to(torch.uint8), w.t(), sa, sb, torch.bfloat16)
+    # C ABI: status code + message, no exception type
+    st = capi.lib.b2_gemm_s8(a.data_ptr(), 64, w.data_ptr(), 64, sa.data_ptr(), sb.data_ptr(), None, 0, a.data_ptr(),
+                             30, capi.DTYPE_BF16, 4, 30, 64, _stream())
+    assert st == capi.ERR_ARG and "multiple of 8" in capi.last_error()
+
+
+def test_empty_batch_is_a_noop():
+    w = torch.zeros(32, 64, dtype=torch.int8, device=DEV)
+    x = torch.zeros(0, 64, dtype=torch.bfloat16, device=DEV)
+    capi.reset_launch_count()
+    out = b2.int8_scaled_mm_with_quant(x, w, torch.ones(32, device=DEV), None, torch.bfloat16, False)
+    assert out.shape == (0, 32) and capi.launch_count() == 0
+
+
+def test_ops_are_cuda_graph_capturable_and_use_the_current_stream():
+    x, W, Bs, b = mk_int8_problem(64, 256, 512, seed=21)
+    xd, Wd, Bsd, bd = x.to(DEV), W.to(DEV), Bs.to(DEV), b.to(DEV)
+    ref = restate.int8_scaled_mm_with_quant(x, W, Bs, b.float())
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        b2.int8_scaled_mm_with_quant(xd, Wd, Bsd, bd, torch.bfloat16, False)  # warm-up (func attributes)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            out = b2.int8_scaled_mm_with_quant(xd, Wd, Bsd, bd, torch.bfloat16, False)
+    torch.cuda.current_stream().wait_stream(side)
+    out.zero_()
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref))
+    xd.copy_((x * 2).to(DEV))
+    graph.replay()
+    torch.cuda.synchronize()
+    ref2 = restate.int8_scaled_mm_with_quant((x * 2), W, Bs, b.float())
+    assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref2))
+
+
+def test_launch_counter_counts_our_kernels():
+    x, W, Bs, b = mk_int8_problem(8, 64, 128, seed=2)
+    capi.reset_launch_count()
+    b2.int8_scaled_mm_with_quant(x.to(DEV), W.to(DEV), Bs.to(DEV), None, torch.bfloat16, False)
+    assert capi.launch_count() == 2  # quantizer + GEMM

@@ -137,6 +137,12 @@ void b2_set_gemm_config(int config_id);
 /* Name of the tile configuration the last GEMM call on this thread used. */
 const char* b2_last_gemm_config(void);
 
+/* Developer hook: when non-NULL, the per-token GEMM kernels write per-CTA wait-cycle counters
+ * (8 x uint64 per CTA: MMA-waits-for-operands, MMA-waits-for-accumulator, producer-waits-for-stage,
+ * epilogue-waits-for-accumulator, CTA lifetime, 3 reserved) into this device buffer
+ * (>= 8 * 8 * grid bytes).  NULL (default) disables it. */
+void b2_set_profile_buffer(void* device_buffer);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,6 +24,7 @@ SYMBOLS = [
     "b2_linear_w8a8_int8_workspace", "b2_linear_w8a8_int8",
     "b2_linear_w8a8_fp8_workspace", "b2_linear_w8a8_fp8",
     "b2_launch_count", "b2_launch_count_reset", "b2_set_gemm_config", "b2_last_gemm_config",
+    "b2_set_profile_buffer",
 ]
 
 if not os.path.isfile(LIB_PATH):
@@ -63,6 +64,8 @@ lib.b2_launch_count_reset.restype = None
 lib.b2_set_gemm_config.argtypes = [_i]
 lib.b2_set_gemm_config.restype = None
 lib.b2_last_gemm_config.restype = ctypes.c_char_p
+lib.b2_set_profile_buffer.argtypes = [_vp]
+lib.b2_set_profile_buffer.restype = None
 
 
 class B2Error(RuntimeError):

@@ -42,6 +42,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
 
 // capi.cu
 void count_launch(int n = 1);
+void* profile_buffer();  // device buffer set by b2_set_profile_buffer (nullptr = profiling off)
 int device_sm_count();
 
 }  // namespace b2

@@ -32,6 +32,11 @@ struct KernelParams {
   int stages;
   int group_m;
   int a_box_rows;  // rows of A actually fetched per stage (<= BM; small-M shapes fetch fewer)
+  // optional per-CTA wait-cycle counters (b2_set_profile_buffer): [cta][0]=MMA waits for operands,
+  // [1]=MMA waits for a free accumulator, [2]=producer waits for a free stage, [3]=epilogue waits
+  // for an accumulator (warp 2), [4]=CTA lifetime, all in SM clocks
+  unsigned long long* prof;
+  int debug_flags;  // developer experiments (env B2_GEMM_DEBUG): 1 = skip the MMAs, 2 = skip the epilogue body
 };
 
 B2_DEVICE void tile_coords(int tile, const KernelParams& p, int& m_blk, int& n_blk) {

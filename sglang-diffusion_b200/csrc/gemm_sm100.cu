@@ -19,16 +19,27 @@
 // Two TMEM accumulator buffers (2 x BN columns) let the epilogue of tile i overlap the
 // main loop of tile i+1.  M/N/K tails are handled by TMA zero-fill on loads and clipping
 // on stores; no padding copies are ever made.
+//
+// CG = 2 (large M): the two CTAs of a cluster (one TPC) work on ONE 256 x BN tile with
+// tcgen05.mma.cta_group::2.  Each CTA loads its own 128 rows of A and only HALF of the W tile
+// (BN/2 rows), the tensor cores of both SMs read both halves, so the L2->SM operand traffic per
+// MAC drops by a third against two independent 128 x BN tiles.  CTA 0 issues every MMA; the
+// TMA loads of both CTAs complete on CTA 0's `full` barriers; tcgen05.commit multicasts the
+// `empty` / `acc_full` arrivals to both CTAs; the epilogue warps of both CTAs hand their TMEM
+// buffer back on CTA 0's `acc_empty` barrier.
+#include <cstdlib>
+
 #include "gemm_common.cuh"
 
 namespace b2 {
 
-template <MmaKind KIND, int OUT_BYTES, int BN>
+template <MmaKind KIND, int OUT_BYTES, int BN, int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_w8a8_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                      const __grid_constant__ CUtensorMap tmap_d, const KernelParams p) {
+  constexpr int B_ROWS = BN / CG;  // rows of the W tile this CTA stages
   constexpr uint32_t A_STAGE_BYTES = BM * BK;
-  constexpr uint32_t B_STAGE_BYTES = BN * BK;
+  constexpr uint32_t B_STAGE_BYTES = B_ROWS * BK;
   constexpr uint32_t TMEM_COLS = (2 * BN) < 32 ? 32 : (2 * BN);
   static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns must be a power of two");
   constexpr int COLS_PER_BOX = 128 / OUT_BYTES;  // output columns in one 128-byte staging row
@@ -48,7 +59,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const long long t_start = p.prof ? clock64() : 0;
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;  // tiles of (BM*CG) x BN
+  const int cta_rank = CG == 1 ? 0 : static_cast<int>(cluster_ctarank());
+  const int unit = CG == 1 ? static_cast<int>(blockIdx.x) : static_cast<int>(blockIdx.x >> 1);
+  const int num_units = CG == 1 ? static_cast<int>(gridDim.x) : static_cast<int>(gridDim.x >> 1);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -60,13 +75,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[i], 4 * CG);  // one arrival per epilogue warp of every CTA of the cluster
     }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<1>(tmem_ptr, TMEM_COLS);
+  if (warp == 1) tmem_alloc<CG>(tmem_ptr, TMEM_COLS);
   tc_fence_before_sync();
-  __syncthreads();
+  if constexpr (CG == 1) {
+    __syncthreads();
+  } else {
+    __syncwarp();
+    cluster_sync_all();  // barrier inits of both CTAs visible before any remote arrival / TMA completion
+  }
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
 
@@ -75,58 +95,86 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t tx_bytes = static_cast<uint32_t>(p.a_box_rows) * BK + B_STAGE_BYTES;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const uint32_t tx_bytes = (static_cast<uint32_t>(p.a_box_rows) * BK + B_STAGE_BYTES) * CG;
+      long long prof_wait = 0;
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
         int m_blk, n_blk;
         tile_coords(tile, p, m_blk, n_blk);
+        const int m_row = (m_blk * CG + cta_rank) * BM;
+        const int n_row = n_blk * BN + cta_rank * B_ROWS;
         for (int kb = 0; kb < p.num_kb; ++kb) {
+          const long long w0 = p.prof ? clock64() : 0;
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-          tma_load_2d(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES, &tmap_a, &full_bar[stage], kb * BK,
-                      m_blk * BM, kEvictNormal);
-          tma_load_2d(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES, &tmap_b, &full_bar[stage], kb * BK,
-                      n_blk * BN, kEvictNormal);
+          if (p.prof) prof_wait += clock64() - w0;
+          if constexpr (CG == 1) {
+            mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+            tma_load_2d(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES, &tmap_a, &full_bar[stage], kb * BK,
+                        m_row, kEvictNormal);
+            tma_load_2d(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES, &tmap_b, &full_bar[stage], kb * BK,
+                        n_row, kEvictNormal);
+          } else {
+            // both CTAs' bytes are expected on (and complete on) the leader CTA's barrier
+            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+            const uint32_t bar0 = smem_u32(&full_bar[stage]) & kPeerBitMask;
+            tma_load_2d_cg2(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES), &tmap_a, bar0, kb * BK,
+                            m_row, kEvictNormal);
+            tma_load_2d_cg2(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES), &tmap_b, bar0, kb * BK,
+                            n_row, kEvictNormal);
+          }
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
           }
         }
       }
+      if (p.prof) p.prof[blockIdx.x * 8 + 2] = static_cast<unsigned long long>(prof_wait);
     }
   } else if (warp == 1) {
     // ======================================================= MMA issuer ====
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc<KIND>(BM, BN);
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = make_idesc<KIND>(BM * CG, BN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      long long prof_full = 0, prof_acc = 0;
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
+        long long w0 = p.prof ? clock64() : 0;
         mbar_wait(&acc_empty[acc], acc_phase ^ 1);
+        if (p.prof) prof_acc += clock64() - w0;
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
         for (int kb = 0; kb < p.num_kb; ++kb) {
+          w0 = p.prof ? clock64() : 0;
           mbar_wait(&full_bar[stage], phase);
+          if (p.prof) prof_full += clock64() - w0;
           tc_fence_after_sync();
           const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES));
           const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
+          if (!(p.debug_flags & 1))
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             // advance 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
-            umma<KIND, 1>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
-                          db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, (kb | k) != 0 ? 1u : 0u);
+            umma<KIND, CG>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
+                           db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);
+          if constexpr (CG == 1) umma_commit(&empty_bar[stage]);
+          else umma_commit_cg2(&empty_bar[stage], 0x3);
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&acc_full[acc]);
+        if constexpr (CG == 1) umma_commit(&acc_full[acc]);
+        else umma_commit_cg2(&acc_full[acc], 0x3);
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
         }
+      }
+      if (p.prof) {
+        p.prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(prof_full);
+        p.prof[blockIdx.x * 8 + 1] = static_cast<unsigned long long>(prof_acc);
       }
     }
   } else {
@@ -138,22 +186,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     int acc = 0;
     uint32_t acc_phase = 0;
     int buf = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    long long prof_epi = 0;
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
       int m_blk, n_blk;
       tile_coords(tile, p, m_blk, n_blk);
-      const int row0 = m_blk * BM + quarter * 32;
+      const int row0 = (m_blk * CG + cta_rank) * BM + quarter * 32;
       const int row = row0 + lane;
       const int col_tile = n_blk * BN;
       float as = 0.f;
       if (!raw_out && row < p.M) as = __ldg(p.As + row);
 
+      const long long w0 = p.prof ? clock64() : 0;
       mbar_wait(&acc_full[acc], acc_phase);
+      if (p.prof) prof_epi += clock64() - w0;
       tc_fence_after_sync();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
 
       constexpr int NBOX = (BN + COLS_PER_BOX - 1) / COLS_PER_BOX;
 #pragma unroll 1
-      for (int bx = 0; bx < NBOX; ++bx) {
+      for (int bx = 0; bx < ((p.debug_flags & 2) ? 0 : NBOX); ++bx) {
         const int col_box = col_tile + bx * COLS_PER_BOX;
         uint8_t* stage_buf = my_epi + buf * EPI_BUF_BYTES;
         // the TMA store that last read this staging buffer must have drained it
@@ -224,20 +275,30 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       // accumulator fully read: hand the TMEM buffer back to the MMA warp
       tc_fence_before_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      if (lane == 0) {
+        if constexpr (CG == 1) mbar_arrive(&acc_empty[acc]);
+        else mbar_arrive_cluster(&acc_empty[acc], 0);
+      }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
       }
     }
     if (lane == 0) tma_store_wait_all<0>();
+    if (p.prof && warp == EPI_WARP0 && lane == 0) p.prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(prof_epi);
   }
+  if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);
 
   tc_fence_before_sync();
-  __syncthreads();
+  if constexpr (CG == 1) {
+    __syncthreads();
+  } else {
+    __syncwarp();
+    cluster_sync_all();  // the peer's smem, TMEM and barriers stay alive until both CTAs are done
+  }
   if (warp == 1) {
     tc_fence_after_sync();
-    tmem_dealloc<1>(tmem_base, TMEM_COLS);
+    tmem_dealloc<CG>(tmem_base, TMEM_COLS);
   }
 }
 
@@ -246,32 +307,37 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 struct TileConfig {
   int id;
   int bn;
+  int cg;
+  double rate;  // relative tensor-side efficiency of the tile shape (measured, tools/gpu_probe.py)
   const char* name;
 };
 static const TileConfig kConfigs[] = {
-    {1, 32, "1cta_128x32"}, {2, 64, "1cta_128x64"}, {3, 128, "1cta_128x128"}, {4, 256, "1cta_128x256"}};
+    {1, 32, 1, 0.35, "1cta_128x32"},   {2, 64, 1, 0.55, "1cta_128x64"},   {3, 128, 1, 0.66, "1cta_128x128"},
+    {4, 256, 1, 1.0, "1cta_128x256"},  {5, 256, 2, 1.08, "2cta_256x256"}, {6, 128, 2, 0.8, "2cta_256x128"}};
+constexpr int kNumConfigs = sizeof(kConfigs) / sizeof(kConfigs[0]);
 
-static int stages_for(int bn) {
+static int stages_for(int b_rows) {
   const int fixed = 4 * 2 * EPI_BUF_BYTES + 1024 /*align slack*/ + 512 /*barriers*/;
-  int s = (SMEM_LIMIT - fixed) / (BM * BK + bn * BK);
+  int s = (SMEM_LIMIT - fixed) / (BM * BK + b_rows * BK);
   return s > 12 ? 12 : s;
 }
 
-static size_t smem_bytes_for(int bn, int stages) {
-  return static_cast<size_t>(stages) * (BM * BK + bn * BK) + 4 * 2 * EPI_BUF_BYTES + 1024 + 512;
+static size_t smem_bytes_for(int b_rows, int stages) {
+  return static_cast<size_t>(stages) * (BM * BK + b_rows * BK) + 4 * 2 * EPI_BUF_BYTES + 1024 + 512;
 }
 
 static const TileConfig& pick_config(int M, int N, int sms) {
-  // relative MMA-side efficiency of a 128 x BN tile (smem operand bandwidth bound for narrow tiles)
-  const double rate[] = {0.35, 0.55, 0.8, 1.0};
-  const int num_m = (M + BM - 1) / BM;
   int best = 3;
   double best_score = -1;
-  for (int i = 0; i < 4; ++i) {
-    const int bn = kConfigs[i].bn;
-    const long tiles = static_cast<long>(num_m) * ((N + bn - 1) / bn);
-    const long waves = (tiles + sms - 1) / sms;
-    const double score = static_cast<double>(tiles) / static_cast<double>(waves * sms) * rate[i];
+  for (int i = 0; i < kNumConfigs; ++i) {
+    const TileConfig& c = kConfigs[i];
+    if (c.cg == 2 && M <= BM) continue;  // the second CTA of the pair would only see padding rows
+    const int units = sms / c.cg;
+    const long tiles = static_cast<long>((M + BM * c.cg - 1) / (BM * c.cg)) * ((N + c.bn - 1) / c.bn);
+    const long waves = (tiles + units - 1) / units;
+    // fraction of useful rows in the M tiles (a 256-row tile on M = 300 is 41 % padding)
+    const double m_fill = static_cast<double>(M) / (static_cast<double>((M + BM * c.cg - 1) / (BM * c.cg)) * BM * c.cg);
+    const double score = static_cast<double>(tiles) / static_cast<double>(waves * units) * c.rate * m_fill;
     if (score > best_score + 1e-9) {
       best_score = score;
       best = i;
@@ -280,25 +346,34 @@ static const TileConfig& pick_config(int M, int N, int sms) {
   return kConfigs[best];
 }
 
-template <MmaKind KIND, int OUT_BYTES, int BN>
+template <MmaKind KIND, int OUT_BYTES, int BN, int CG>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const KernelParams& p,
                       int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
-  auto kern = gemm_w8a8_kernel<KIND, OUT_BYTES, BN>;
-  static bool attr_set = false;  // per instantiation; the attribute is per-function, per-device context
-  static int attr_dev = -1;
+  auto kern = gemm_w8a8_kernel<KIND, OUT_BYTES, BN, CG>;
+  static int attr_dev = -1;  // per instantiation; the attribute is per-function, per-device context
   int dev = 0;
   cudaGetDevice(&dev);
-  if (!attr_set || attr_dev != dev) {
+  if (attr_dev != dev) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
     if (e != cudaSuccess) {
       snprintf(err, err_len, "cudaFuncSetAttribute(max dynamic smem): %s", cudaGetErrorString(e));
       return B2_ERR_CUDA;
     }
-    attr_set = true;
     attr_dev = dev;
   }
-  kern<<<grid, NUM_THREADS, smem, st>>>(ta, tb, td, p);
-  cudaError_t e = cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = CG;
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p);
   if (e != cudaSuccess) {
     snprintf(err, err_len, "gemm kernel launch: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
@@ -308,13 +383,15 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
 }
 
 template <MmaKind KIND, int OUT_BYTES>
-static int launch_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
-                     const KernelParams& p, int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
-  switch (bn) {
-    case 32: return launch_one<KIND, OUT_BYTES, 32>(ta, tb, td, p, grid, smem, st, err, err_len);
-    case 64: return launch_one<KIND, OUT_BYTES, 64>(ta, tb, td, p, grid, smem, st, err, err_len);
-    case 128: return launch_one<KIND, OUT_BYTES, 128>(ta, tb, td, p, grid, smem, st, err, err_len);
-    default: return launch_one<KIND, OUT_BYTES, 256>(ta, tb, td, p, grid, smem, st, err, err_len);
+static int launch_cfg(const TileConfig& c, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
+                      const KernelParams& p, int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
+  switch (c.id) {
+    case 1: return launch_one<KIND, OUT_BYTES, 32, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 2: return launch_one<KIND, OUT_BYTES, 64, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 3: return launch_one<KIND, OUT_BYTES, 128, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 4: return launch_one<KIND, OUT_BYTES, 256, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 5: return launch_one<KIND, OUT_BYTES, 256, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
+    default: return launch_one<KIND, OUT_BYTES, 128, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
   }
 }
 
@@ -326,9 +403,11 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   if (flavor == GEMM_E4M3_BLOCK128) return gemm_launch_blockwise(a, forced_config, used_config, st, err, err_len);
   const int sms = device_sm_count();
   const TileConfig* cfg = &pick_config(a.M, a.N, sms);
-  if (forced_config >= 1 && forced_config <= 4) cfg = &kConfigs[forced_config - 1];
+  if (forced_config >= 1 && forced_config <= kNumConfigs) cfg = &kConfigs[forced_config - 1];
   if (used_config) *used_config = cfg->name;
   const int bn = cfg->bn;
+  const int cg = cfg->cg;
+  const int b_rows = bn / cg;
 
   const int out_bytes = (a.out_dtype == B2_DTYPE_BF16 || a.out_dtype == B2_DTYPE_F16) ? 2 : 4;
   CUtensorMapDataType d_dt = a.out_dtype == B2_DTYPE_BF16  ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
@@ -344,18 +423,31 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   p.M = a.M;
   p.N = a.N;
   p.K = a.K;
-  p.num_m_blocks = (a.M + BM - 1) / BM;
+  p.num_m_blocks = (a.M + BM * cg - 1) / (BM * cg);
   p.num_n_blocks = (a.N + bn - 1) / bn;
   p.num_kb = (a.K + BK - 1) / BK;
-  p.stages = stages_for(bn);
-  p.group_m = 16;
+  p.stages = stages_for(b_rows);
+  {  // developer override for pipeline-depth experiments (tools/gemm_prof.py); never deepens beyond what fits
+    static const int forced_stages = [] {
+      const char* e = getenv("B2_GEMM_STAGES");
+      return e ? atoi(e) : 0;
+    }();
+    if (forced_stages >= 2 && forced_stages < p.stages) p.stages = forced_stages;
+    static const int dbg = [] {
+      const char* e = getenv("B2_GEMM_DEBUG");
+      return e ? atoi(e) : 0;
+    }();
+    p.debug_flags = dbg;
+  }
+  p.group_m = 16 / cg;
+  p.prof = static_cast<unsigned long long*>(profile_buffer());
   // decode shapes: fetch only the rows that exist (rounded to the 8-row swizzle atom);
   // the untouched tail of the smem tile feeds MMA rows whose outputs are clipped by the store.
-  p.a_box_rows = a.M >= BM ? BM : ((a.M + 7) / 8) * 8;
+  p.a_box_rows = (a.M >= BM || cg == 2) ? BM : ((a.M + 7) / 8) * 8;
 
   CUtensorMap ta, tb, td;
   if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, p.a_box_rows, BK) ||
-      !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, bn, BK) ||
+      !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, b_rows, BK) ||
       !make_tmap_2d(&td, d_dt, out_bytes, a.D, a.M, a.N, a.ldd * out_bytes, 32,
                     (128 / out_bytes) < bn ? (128 / out_bytes) : bn)) {  // 64-byte boxes use SWIZZLE_64B
     snprintf(err, err_len, "cuTensorMapEncodeTiled failed (M=%d N=%d K=%d lda=%lld ldw=%lld ldd=%lld)", a.M, a.N,
@@ -363,14 +455,15 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
     return B2_ERR_CUDA;
   }
   const int tiles = p.num_m_blocks * p.num_n_blocks;
-  const int grid = tiles < sms ? tiles : sms;
-  const size_t smem = smem_bytes_for(bn, p.stages);
+  const int units = sms / cg;
+  const int grid = (tiles < units ? tiles : units) * cg;
+  const size_t smem = smem_bytes_for(b_rows, p.stages);
   if (flavor == GEMM_S8) {
-    if (out_bytes == 2) return launch_bn<MmaKind::I8, 2>(bn, ta, tb, td, p, grid, smem, st, err, err_len);
-    return launch_bn<MmaKind::I8, 4>(bn, ta, tb, td, p, grid, smem, st, err, err_len);
+    if (out_bytes == 2) return launch_cfg<MmaKind::I8, 2>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
+    return launch_cfg<MmaKind::I8, 4>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
   }
-  if (out_bytes == 2) return launch_bn<MmaKind::F8, 2>(bn, ta, tb, td, p, grid, smem, st, err, err_len);
-  return launch_bn<MmaKind::F8, 4>(bn, ta, tb, td, p, grid, smem, st, err, err_len);
+  if (out_bytes == 2) return launch_cfg<MmaKind::F8, 2>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
+  return launch_cfg<MmaKind::F8, 4>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
 }
 
 }  // namespace b2

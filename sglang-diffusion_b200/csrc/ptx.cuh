@@ -16,7 +16,7 @@ namespace b2 {
 #define B2_DEVICE __device__ __forceinline__
 
 // A wait that never completes would hang the GPU box; with the watchdog a lost
-// arrival becomes a trap (-> cudaErrorLaunchFailure) after ~4 s instead.
+// arrival becomes a trap (-> cudaErrorLaunchFailure) after a few seconds instead.
 #ifndef B2_WAIT_WATCHDOG
 #define B2_WAIT_WATCHDOG 1
 #endif
@@ -95,12 +95,17 @@ B2_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 
 B2_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
 #if B2_WAIT_WATCHDOG
-  const uint64_t t0 = globaltimer_ns();
+  // Reading %globaltimer costs several hundred cycles (measured: it put a ~580-cycle floor under
+  // every blocking wait), so the watchdog only starts looking at the time after 64 K failed polls.
   uint32_t spins = 0;
+  uint64_t t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0x3ffu) == 0 && globaltimer_ns() - t0 > 4000000000ull) __trap();
+    if (++spins >= 0x10000u && (spins & 0x3ffu) == 0) {
+      const uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ull) __trap();
+    }
   }
 #else
   while (!mbar_try_wait(bar, parity)) {
@@ -128,6 +133,10 @@ B2_DEVICE void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, 
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
       : "memory");
 }
+
+// shared::cluster address of a CTA-local barrier with the peer bit cleared = the same barrier in
+// the even (leader) CTA of a cta_group::2 pair
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
 
 // cta_group::2 flavour: data lands in this CTA's smem, the transaction bytes are
 // signalled on the barrier at the same offset in the cluster's leader CTA when

@@ -123,7 +123,7 @@ def test_quant_int8_f16_input_supported_on_gpu():
 
 # ====================================================== int8 GEMM accumulators ====
 
-@pytest.mark.parametrize("cfg", [1, 2, 3, 4])
+@pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5, 6])
 @pytest.mark.parametrize("M,N,K", [(128, 256, 256), (300, 1000, 544), (1, 264, 16), (129, 8, 4096), (5, 384, 544)])
 def test_gemm_s8_raw_accumulators_exact_every_tile_config(cfg, M, N, K):
     g = torch.Generator().manual_seed(M * 7 + N * 3 + K + cfg)
@@ -189,7 +189,7 @@ def test_int8_linear_reference_test_grid_bitwise(M, has_bias):
     assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref))
 
 
-@pytest.mark.parametrize("cfg", [1, 2, 3, 4])
+@pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5, 6])
 def test_int8_c1_bitwise_every_tile_config(cfg):
     """BASELINE config C1: M=128 K=4096 N=4096, bf16 out, bias."""
     x, W, Bs, b = mk_int8_problem(128, 4096, 4096)
@@ -355,7 +355,7 @@ def test_fp8_scaled_mm_vs_restatement(M, N, K, has_bias):
     assert (o == ref.bfloat16().float()).float().mean().item() > 0.99
 
 
-@pytest.mark.parametrize("cfg", [1, 2, 3, 4])
+@pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5, 6])
 def test_fp8_scaled_mm_reference_test_distribution(cfg):
     """sgl-kernel/tests/test_fp8_gemm.py: operands uniform in +-448, scales randn*1e-3... rtol 0.02, atol 1."""
     M, N, K = 257, 1024, 2048

@@ -1,0 +1,47 @@
+"""Where does the GEMM wait?  Runs one shape per tile config with the in-kernel wait-cycle counters on
+(b2_set_profile_buffer) and prints per-role waiting as a fraction of the CTA lifetime.
+Usage: python tools/gemm_prof.py [kind] [M N K] [cfgs...]"""
+import os, sys
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import sglang_diffusion_b200 as b2
+
+kind = sys.argv[1] if len(sys.argv) > 1 else "s8"
+M, N, K = (int(v) for v in sys.argv[2:5]) if len(sys.argv) > 4 else (8192, 28672, 4096)
+cfgs = [int(v) for v in sys.argv[5:]] or [4, 5]
+dev = "cuda:0"
+if kind == "s8":
+    A = torch.randint(-127, 128, (M, K), dtype=torch.int8, device=dev)
+    W = torch.randint(-127, 128, (N, K), dtype=torch.int8, device=dev)
+    op = b2.int8_scaled_mm
+else:
+    A = torch.randn(M, K, device=dev).to(torch.float8_e4m3fn)
+    W = torch.randn(N, K, device=dev).to(torch.float8_e4m3fn)
+    op = b2.fp8_scaled_mm
+As = torch.rand(M, 1, device=dev)
+Bs = torch.rand(N, 1, device=dev)
+prof = torch.zeros(148 * 8, dtype=torch.int64, device=dev)
+for cfg in cfgs:
+    b2.capi.set_gemm_config(cfg)
+    for _ in range(3):
+        op(A, W.t(), As, Bs, torch.bfloat16, None)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        op(A, W.t(), As, Bs, torch.bfloat16, None)
+    e1.record()
+    torch.cuda.synchronize()
+    t = e0.elapsed_time(e1) / 10 * 1e-3
+    b2.capi.lib.b2_set_profile_buffer(prof.data_ptr())
+    prof.zero_()
+    op(A, W.t(), As, Bs, torch.bfloat16, None)
+    torch.cuda.synchronize()
+    b2.capi.lib.b2_set_profile_buffer(None)
+    p = prof.view(148, 8).double().cpu()
+    life = p[:, 4].clamp_min(1)
+    lead = p[p[:, 0] > 0] if (p[:, 0] > 0).any() else p
+    print(f"{kind} M={M} N={N} K={K} cfg={cfg}:{b2.capi.last_gemm_config()}  {t*1e6:8.1f} us {2.0*M*N*K/t/1e12:7.1f} TOPS | "
+          f"CTA life {life.mean():.0f} clk (max {life.max():.0f}) | MMA waits operands {100*(lead[:,0]/lead[:,4]).mean():.1f}% "
+          f"accum {100*(lead[:,1]/lead[:,4]).mean():.1f}% | producer waits stage {100*(p[:,2]/life).mean():.1f}% | "
+          f"epilogue waits accum {100*(p[:,3]/life).mean():.1f}%", flush=True)
+b2.capi.set_gemm_config(0)

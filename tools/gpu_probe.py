@@ -233,10 +233,12 @@ def main():
     for M, K in [(1, 512), (3, 544), (128, 4096), (257, 14336), (7, 16384)]:
         probe_quant_int8(M, K)
     section("int8 GEMM raw accumulators (exact)")
-    for cfg in (3, 4, 2, 1):
+    for cfg in (3, 4, 2, 1, 5, 6):
         probe_gemm_s8_acc(128, 256, 256, cfg)
-    for cfg in (1, 2, 3, 4):
-        probe_gemm_s8_acc(300, 1000 if cfg < 4 else 1024, 544, cfg)
+    for cfg in (1, 2, 3, 4, 5, 6):
+        probe_gemm_s8_acc(300, 1000, 544, cfg)
+    probe_gemm_s8_acc(2048, 2048, 1024, 5)
+    probe_gemm_s8_acc(2048, 2048, 1024, 6)
     probe_gemm_s8_acc(1, 4096, 4096, 0)
     probe_gemm_s8_acc(5, 384, 544, 0)
     probe_gemm_s8_acc(1000, 6144, 4096, 0)
@@ -263,10 +265,11 @@ def main():
     for M, K in [(128, 4096), (8192, 4096), (32768, 5120), (16, 14336)]:
         bench_quant(M, K)
     for kind in ("s8", "f8"):
-        for cfg in (3, 4):
+        for cfg in (3, 4, 5, 6):
             bench_gemm(kind, 8192, 6144, 4096, cfg)
-        bench_gemm(kind, 8192, 28672, 4096, 4)
-        bench_gemm(kind, 8192, 4096, 14336, 4)
+        for cfg in (4, 5):
+            bench_gemm(kind, 8192, 28672, 4096, cfg)
+            bench_gemm(kind, 8192, 4096, 14336, cfg)
         bench_gemm(kind, 128, 4096, 4096, 0)
         for cfg in (1, 2, 3):
             bench_gemm(kind, 16, 28672, 4096, cfg)

@@ -1,0 +1,125 @@
+// MMA-only ceiling of the B200 tensor pipe for the 8-bit kinds (developer tool; SURVEY section 6 asks for it).
+// Every CTA (or CTA pair) loops tcgen05.mma on operand tiles that are already resident in shared memory --
+// no TMA, no epilogue -- so the number is what the tensor cores sustain under the board's power cap with
+// nothing else in the way.  Operand bytes are random (zeros would draw unrealistically little power).
+//
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I sglang-diffusion_b200/csrc -I include \
+//        tools/mma_peak.cu -o tools/bin/mma_peak && tools/bin/mma_peak
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "ptx.cuh"
+
+using namespace b2;
+
+template <MmaKind KIND, int CG, int BN>
+__global__ void __launch_bounds__(128, 1) mma_loop(const uint8_t* __restrict__ seed, int batches) {
+  constexpr int B_ROWS = BN / CG;
+  constexpr int K_STEPS = 4;   // 4 x 32 B along the 128 B swizzle row
+  constexpr int NBUF = 4;      // operand buffers cycled through (as a pipeline ring would)
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t A_BYTES = 128 * 128, B_BYTES = B_ROWS * 128;
+  uint8_t* sa = smem;
+  uint8_t* sb = smem + NBUF * A_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sb + NBUF * B_BYTES);
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2);
+  for (uint32_t i = threadIdx.x; i < NBUF * (A_BYTES + B_BYTES) / 16; i += blockDim.x)
+    reinterpret_cast<uint4*>(smem)[i] = reinterpret_cast<const uint4*>(seed)[(i + blockIdx.x * 977u) & 0xffffu];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = CG == 1 ? 0 : static_cast<int>(cluster_ctarank());
+  if (threadIdx.x == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+  }
+  fence_proxy_async_smem();
+  if (warp == 1) tmem_alloc<CG>(tmem_ptr, 512);
+  tc_fence_before_sync();
+  if (CG == 1) __syncthreads(); else { __syncwarp(); cluster_sync_all(); }
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+  if (warp == 0 && lane == 0 && rank == 0) {
+    constexpr uint32_t idesc = make_idesc<KIND>(128 * CG, BN);
+    uint32_t phase[2] = {0, 0};
+    for (int b = 0; b < batches; ++b) {
+      const int which = b & 1;
+      if (b >= 2) {  // keep at most two batches (2 x 32 MMAs) in flight
+        mbar_wait(&bars[which], phase[which]);
+        phase[which] ^= 1;
+      }
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        const int buf = s & (NBUF - 1);
+        const uint64_t da = make_smem_desc_sw128(smem_u32(sa + buf * A_BYTES));
+        const uint64_t db = make_smem_desc_sw128(smem_u32(sb + buf * B_BYTES));
+        const uint32_t d = tmem_base + ((s & 1) ? BN : 0);
+#pragma unroll
+        for (int k = 0; k < K_STEPS; ++k) umma<KIND, CG>(d, da + 2 * k, db + 2 * k, idesc, (b | s | k) != 0);
+      }
+      if (CG == 1) umma_commit(&bars[which]); else umma_commit_cg2(&bars[which], 0x1);
+    }
+    const int last = (batches - 1) & 1;
+    if (batches >= 2) mbar_wait(&bars[last ^ 1], phase[last ^ 1]);
+    mbar_wait(&bars[last], phase[last]);
+  }
+  tc_fence_before_sync();
+  if (CG == 1) __syncthreads(); else { __syncwarp(); cluster_sync_all(); }
+  if (warp == 1) { tc_fence_after_sync(); tmem_dealloc<CG>(tmem_base, 512); }
+}
+
+template <MmaKind KIND, int CG, int BN>
+static void run(const char* name, const uint8_t* seed, int sms, int batches) {
+  auto kern = mma_loop<KIND, CG, BN>;
+  const size_t smem = 4 * (128 * 128 + (BN / CG) * 128) + 1024 + 64;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(sms);
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CG; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaLaunchKernelEx(&cfg, kern, seed, 64);  // warm-up
+  cudaDeviceSynchronize();
+  cudaEventRecord(e0);
+  cudaLaunchKernelEx(&cfg, kern, seed, batches);
+  cudaEventRecord(e1);
+  cudaError_t err = cudaDeviceSynchronize();
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  const double macs = (double)(sms / CG) * batches * 32.0 * (128.0 * CG) * BN * 32.0;
+  printf("%-28s batches=%-7d %9.3f ms  %8.1f TOPS  (%s)\n", name, batches, ms, 2.0 * macs / (ms * 1e-3) / 1e12,
+         cudaGetErrorString(err));
+  fflush(stdout);
+}
+
+int main() {
+  int sms = 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+  std::vector<uint8_t> h(1 << 20);
+  srand(1);
+  for (auto& b : h) b = (uint8_t)(rand() & 0x77);  // e4m3-safe (no NaN codes), mixed signs via int8 view irrelevant
+  uint8_t* d;
+  cudaMalloc(&d, h.size());
+  cudaMemcpy(d, h.data(), h.size(), cudaMemcpyHostToDevice);
+  for (int rep = 0; rep < 2; ++rep) {
+    const int burst = 2000, sustained = 400000;  // ~1.5 ms and ~0.3 s per launch at full rate
+    run<MmaKind::I8, 1, 256>("i8  1cta 128x256 burst", d, sms, burst);
+    run<MmaKind::I8, 2, 256>("i8  2cta 256x256 burst", d, sms, burst);
+    run<MmaKind::F8, 1, 256>("f8  1cta 128x256 burst", d, sms, burst);
+    run<MmaKind::F8, 2, 256>("f8  2cta 256x256 burst", d, sms, burst);
+    run<MmaKind::I8, 1, 128>("i8  1cta 128x128 burst", d, sms, burst);
+    run<MmaKind::I8, 1, 64>("i8  1cta 128x64  burst", d, sms, burst);
+    run<MmaKind::I8, 1, 32>("i8  1cta 128x32  burst", d, sms, burst);
+    run<MmaKind::I8, 1, 256>("i8  1cta 128x256 sustained", d, sms, sustained);
+    run<MmaKind::I8, 2, 256>("i8  2cta 256x256 sustained", d, sms, sustained);
+    run<MmaKind::F8, 1, 256>("f8  1cta 128x256 sustained", d, sms, sustained);
+    run<MmaKind::F8, 2, 256>("f8  2cta 256x256 sustained", d, sms, sustained);
+  }
+  return 0;
+}

@@ -3,6 +3,7 @@
 // the reference ops' TORCH_CHECKs (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:670-695,
 // fp8_gemm_kernel.cu:1465-1487, fp8_blockwise_gemm_kernel.cu:374-403) but reports
 // through status codes + b2_last_error() instead of exceptions.
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #include <cstdarg>
@@ -52,7 +53,13 @@ static const DevInfo* dev_info() {
 
 int device_sm_count() {
   const DevInfo* d = dev_info();
-  return d ? d->sms : 148;
+  const int sms = d ? d->sms : 148;
+  // developer experiment (tools/power_probe.py): run the persistent GEMMs on fewer SMs
+  static const int cap = [] {
+    const char* e = getenv("B2_GEMM_MAX_SMS");
+    return e ? atoi(e) : 0;
+  }();
+  return (cap >= 2 && cap < sms) ? (cap & ~1) : sms;
 }
 
 // No CPU path and no other-architecture path: the kernels are sm_100a only.

@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   uint64_t* part_empty = part_full + BW_SLOTS;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(part_empty + BW_SLOTS);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);  // warp-uniform (see gemm_sm100.cu)
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.num_m_blocks * p.num_n_blocks;
 
@@ -88,42 +88,45 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   const uint32_t tmem_base = *tmem_ptr;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      const uint32_t tx_bytes = static_cast<uint32_t>(p.a_box_rows) * BK + B_STAGE_BYTES;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        int m_blk, n_blk;
-        bw_tile_coords(tile, p, m_blk, n_blk);
-        for (int kb = 0; kb < p.num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+    // TMA producer: whole warp walks the ring, one elected lane issues
+    int stage = 0;
+    uint32_t phase = 0;
+    const uint32_t tx_bytes = static_cast<uint32_t>(p.a_box_rows) * BK + B_STAGE_BYTES;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int m_blk, n_blk;
+      bw_tile_coords(tile, p, m_blk, n_blk);
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
           mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
           tma_load_2d(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES, &tmap_a, &full_bar[stage], kb * BK,
                       m_blk * BM, kEvictNormal);
           tma_load_2d(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES, &tmap_b, &full_bar[stage], kb * BK,
                       n_blk * BN, kEvictNormal);
-          if (++stage == stages) {
-            stage = 0;
-            phase ^= 1;
-          }
+        }
+        __syncwarp();
+        if (++stage == stages) {
+          stage = 0;
+          phase ^= 1;
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc<MmaKind::F8>(BM, BN);
-      int stage = 0;
-      uint32_t phase = 0;
-      int slot = 0;
-      uint32_t slot_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        for (int kb = 0; kb < p.num_kb; ++kb) {
-          mbar_wait(&part_empty[slot], slot_phase ^ 1);
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after_sync();
-          const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(slot * BN);
-          const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES));
-          const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
+    // MMA issuer: whole warp in the loop, the same elected lane issues every MMA and commit
+    constexpr uint32_t idesc = make_idesc<MmaKind::F8>(BM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int slot = 0;
+    uint32_t slot_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(&part_empty[slot], slot_phase ^ 1);
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(slot * BN);
+        const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES));
+        const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             umma<MmaKind::F8, 1>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
@@ -131,14 +134,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           }
           umma_commit(&empty_bar[stage]);
           umma_commit(&part_full[slot]);
-          if (++stage == stages) {
-            stage = 0;
-            phase ^= 1;
-          }
-          if (++slot == BW_SLOTS) {
-            slot = 0;
-            slot_phase ^= 1;
-          }
+        }
+        __syncwarp();
+        if (++stage == stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+        if (++slot == BW_SLOTS) {
+          slot = 0;
+          slot_phase ^= 1;
         }
       }
     }
@@ -209,7 +213,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       for (int bx = 0; bx < NBOX; ++bx) {
         const int col_box = col_tile + bx * COLS_PER_BOX;
         uint8_t* stage_buf = my_epi + buf * EPI_BUF_BYTES;
-        if (lane == 0) tma_store_wait_read<1>();
+        tma_store_wait_read<1>();
         __syncwarp();
 #pragma unroll
         for (int g = 0; g < COLS_PER_BOX / 8; ++g) {
@@ -246,14 +250,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         }
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0 && row0 < p.M && col_box < p.N) {
+        if (row0 < p.M && col_box < p.N && elect_one()) {
           tma_store_2d(&tmap_d, stage_buf, col_box, row0);
           tma_store_commit();
         }
         buf ^= 1;
       }
     }
-    if (lane == 0) tma_store_wait_all<0>();
+    tma_store_wait_all<0>();
   }
 
   tc_fence_before_sync();

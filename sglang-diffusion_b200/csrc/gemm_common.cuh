@@ -36,7 +36,7 @@ struct KernelParams {
   // [1]=MMA waits for a free accumulator, [2]=producer waits for a free stage, [3]=epilogue waits
   // for an accumulator (warp 2), [4]=CTA lifetime, all in SM clocks
   unsigned long long* prof;
-  int debug_flags;  // developer experiments (env B2_GEMM_DEBUG): 1 = skip the MMAs, 2 = skip the epilogue body
+  int debug_flags;  // developer experiments (env B2_GEMM_DEBUG): 1 = skip the MMAs, 2 = skip the epilogue body, 4 = skip the loads
 };
 
 B2_DEVICE void tile_coords(int tile, const KernelParams& p, int& m_blk, int& n_blk) {

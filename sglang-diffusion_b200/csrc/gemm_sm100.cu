@@ -45,19 +45,27 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   constexpr int COLS_PER_BOX = 128 / OUT_BYTES;  // output columns in one 128-byte staging row
   static_assert(BN % COLS_PER_BOX == 0 || BN < COLS_PER_BOX, "tile width vs store box");
 
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // The dynamic window is the only shared memory of the kernel, so it starts on a 1024-byte boundary (what
+  // the 128-byte swizzle needs); no slack is budgeted for rounding up, a misplaced base traps instead.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
   const int stages = p.stages;
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + static_cast<size_t>(stages) * A_STAGE_BYTES;
   uint8_t* smem_epi = smem_b + static_cast<size_t>(stages) * B_STAGE_BYTES;  // 4 warps x 2 bufs x 4 KB
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_epi + 4 * 2 * EPI_BUF_BYTES);
+  float* smem_bs = reinterpret_cast<float*>(smem_epi + 4 * 2 * EPI_BUF_BYTES);  // this tile's Bs[BN], bias[BN] (fp32)
+  float* smem_bias = smem_bs + BN;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_bias + BN);
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* acc_full = empty_bar + stages;
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
-  const int warp = threadIdx.x >> 5;
+  // warp-uniform role index (the shuffle tells the compiler so): everything the producer and MMA warps
+  // compute then lives in uniform registers, and UTMALDG / UTCIMMA / UTCBAR issue straight from them
+  // (a divergent `if (lane == 0)` region costs a 5 x R2UR + ELECT waterfall loop per instruction instead)
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const long long t_start = p.prof ? clock64() : 0;
   const int num_tiles = p.num_m_blocks * p.num_n_blocks;  // tiles of (BM*CG) x BN
@@ -92,7 +100,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 
   if (warp == 0) {
     // ===================================================== TMA producer ====
-    if (lane == 0) {
+    // the whole warp walks the ring (all lanes poll the barrier); one elected lane issues
+    {
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t tx_bytes = (static_cast<uint32_t>(p.a_box_rows) * BK + B_STAGE_BYTES) * CG;
@@ -106,32 +115,38 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           const long long w0 = p.prof ? clock64() : 0;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (p.prof) prof_wait += clock64() - w0;
-          if constexpr (CG == 1) {
-            mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-            tma_load_2d(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES, &tmap_a, &full_bar[stage], kb * BK,
-                        m_row, kEvictNormal);
-            tma_load_2d(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES, &tmap_b, &full_bar[stage], kb * BK,
-                        n_row, kEvictNormal);
+          uint8_t* a_dst = smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES;
+          uint8_t* b_dst = smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES;
+          if (p.debug_flags & 4) {  // experiment: no loads, the MMAs run over whatever the ring holds
+            if (cta_rank == 0 && elect_one()) mbar_arrive(&full_bar[stage]);
+          } else if constexpr (CG == 1) {
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+              tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kb * BK, m_row, kEvictNormal);
+              tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * BK, n_row, kEvictNormal);
+            }
           } else {
             // both CTAs' bytes are expected on (and complete on) the leader CTA's barrier
-            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-            const uint32_t bar0 = smem_u32(&full_bar[stage]) & kPeerBitMask;
-            tma_load_2d_cg2(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES), &tmap_a, bar0, kb * BK,
-                            m_row, kEvictNormal);
-            tma_load_2d_cg2(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES), &tmap_b, bar0, kb * BK,
-                            n_row, kEvictNormal);
+            if (elect_one()) {
+              if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+              const uint32_t bar0 = smem_u32(&full_bar[stage]) & kPeerBitMask;
+              tma_load_2d_cg2(smem_u32(a_dst), &tmap_a, bar0, kb * BK, m_row, kEvictNormal);
+              tma_load_2d_cg2(smem_u32(b_dst), &tmap_b, bar0, kb * BK, n_row, kEvictNormal);
+            }
           }
+          __syncwarp();
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
           }
         }
       }
-      if (p.prof) p.prof[blockIdx.x * 8 + 2] = static_cast<unsigned long long>(prof_wait);
+      if (p.prof && lane == 0) p.prof[blockIdx.x * 8 + 2] = static_cast<unsigned long long>(prof_wait);
     }
   } else if (warp == 1) {
     // ======================================================= MMA issuer ====
-    if (lane == 0 && cta_rank == 0) {
+    // whole warp in the loop, one elected lane (always the same one) issues every MMA and commit
+    if (cta_rank == 0) {
       constexpr uint32_t idesc = make_idesc<KIND>(BM * CG, BN);
       int stage = 0;
       uint32_t phase = 0;
@@ -151,28 +166,35 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           tc_fence_after_sync();
           const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES));
           const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
-          if (!(p.debug_flags & 1))
+          if (elect_one()) {
+            if (!(p.debug_flags & 1)) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            // advance 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
-            umma<KIND, CG>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
-                           db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < BK / UMMA_K; ++k) {
+                // advance 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
+                umma<KIND, CG>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
+                               db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, (kb | k) != 0 ? 1u : 0u);
+              }
+            }
+            if constexpr (CG == 1) umma_commit(&empty_bar[stage]);
+            else umma_commit_cg2(&empty_bar[stage], 0x3);
           }
-          if constexpr (CG == 1) umma_commit(&empty_bar[stage]);
-          else umma_commit_cg2(&empty_bar[stage], 0x3);
+          __syncwarp();
           if (++stage == stages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        if constexpr (CG == 1) umma_commit(&acc_full[acc]);
-        else umma_commit_cg2(&acc_full[acc], 0x3);
+        if (elect_one()) {
+          if constexpr (CG == 1) umma_commit(&acc_full[acc]);
+          else umma_commit_cg2(&acc_full[acc], 0x3);
+        }
+        __syncwarp();
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
         }
       }
-      if (p.prof) {
+      if (p.prof && lane == 0) {
         p.prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(prof_full);
         p.prof[blockIdx.x * 8 + 1] = static_cast<unsigned long long>(prof_acc);
       }
@@ -180,6 +202,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   } else {
     // ========================================================= epilogue ====
     const int quarter = warp & 3;  // TMEM lane quarter this warp may read
+    const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
     uint8_t* my_epi = smem_epi + static_cast<size_t>(warp - EPI_WARP0) * 2 * EPI_BUF_BYTES;
     const bool has_bias = p.bias != nullptr;
     const bool raw_out = (KIND == MmaKind::I8) && p.out_dtype == B2_DTYPE_S32;
@@ -187,12 +210,32 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     uint32_t acc_phase = 0;
     int buf = 0;
     long long prof_epi = 0;
+    constexpr int BOX_COLS = COLS_PER_BOX < BN ? COLS_PER_BOX : BN;
+    constexpr int BOX_BYTES = BOX_COLS * OUT_BYTES;  // 128 (SW128 box) or 64 (SW64 box, BN = 32 @ 16 bit)
+    static_assert(BOX_BYTES == 128 || BOX_BYTES == 64, "store box is 128 or 64 bytes wide");
+    constexpr int CH_PER_BOX = BOX_COLS / 32;  // 32-column TMEM loads per store box
+    constexpr int NCH = BN / 32;
+    // TMA swizzle of the staging box: 16-byte chunk index ^= (byte offset >> 7) & (BOX_BYTES/16 - 1)
+    const int swz = BOX_BYTES == 128 ? (lane & 7) : ((lane >> 1) & 3);
     for (int tile = unit; tile < num_tiles; tile += num_units) {
       int m_blk, n_blk;
       tile_coords(tile, p, m_blk, n_blk);
       const int row0 = (m_blk * CG + cta_rank) * BM + quarter * 32;
       const int row = row0 + lane;
       const int col_tile = n_blk * BN;
+
+      // Per-column scale and bias of this tile -> shared memory, once, while the main loop of the tile is
+      // still running (the four warps read them back as conflict-free broadcasts).  Columns beyond N get 0;
+      // the TMA store clips them.
+      epi_bar_sync();  // every warp is done with the previous tile's values
+      if (!raw_out) {
+        for (int c = epi_tid; c < BN; c += 128) {
+          const int col = col_tile + c;
+          smem_bs[c] = col < p.N ? __ldg(p.Bs + col) : 0.f;
+          smem_bias[c] = (has_bias && col < p.N) ? load_bias(p.bias, p.bias_dtype, col) : 0.f;
+        }
+      }
+      epi_bar_sync();
       float as = 0.f;
       if (!raw_out && row < p.M) as = __ldg(p.As + row);
 
@@ -202,46 +245,55 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       tc_fence_after_sync();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
 
-      constexpr int NBOX = (BN + COLS_PER_BOX - 1) / COLS_PER_BOX;
-#pragma unroll 1
-      for (int bx = 0; bx < ((p.debug_flags & 2) ? 0 : NBOX); ++bx) {
-        const int col_box = col_tile + bx * COLS_PER_BOX;
-        uint8_t* stage_buf = my_epi + buf * EPI_BUF_BYTES;
-        // the TMA store that last read this staging buffer must have drained it
-        if (lane == 0) tma_store_wait_read<1>();
-        __syncwarp();
-        constexpr int BOX_COLS = COLS_PER_BOX < BN ? COLS_PER_BOX : BN;
-        constexpr int BOX_BYTES = BOX_COLS * OUT_BYTES;  // 128 (SW128 box) or 64 (SW64 box, BN = 32 @ 16 bit)
-        static_assert(BOX_BYTES == 128 || BOX_BYTES == 64, "store box is 128 or 64 bytes wide");
-        constexpr int LDS_PER_BOX = BOX_COLS / 32;
-        // TMA swizzle of the staging box: 16-byte chunk index ^= (byte offset >> 7) & (BOX_BYTES/16 - 1)
-        const int swz = BOX_BYTES == 128 ? (lane & 7) : ((lane >> 1) & 3);
+      if (!(p.debug_flags & 2)) {
+        // 32-column TMEM loads, software-pipelined over two register sets: the load of chunk c+1 is in
+        // flight while chunk c is scaled, cast and staged
+        uint32_t r[2][32];
+        tmem_ld_32x32b_x32(t_row, r[0]);
 #pragma unroll
-        for (int h = 0; h < LDS_PER_BOX; ++h) {
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(t_row + static_cast<uint32_t>(bx * COLS_PER_BOX + h * 32), r);
+        for (int c = 0; c < NCH; ++c) {
+          const int h = c % CH_PER_BOX;
+          uint8_t* stage_buf = my_epi + buf * EPI_BUF_BYTES;
           tmem_ld_wait();
-          const int col_h = col_box + h * 32;
+          if (c + 1 < NCH) {
+            tmem_ld_32x32b_x32(t_row + static_cast<uint32_t>((c + 1) * 32), r[(c + 1) & 1]);
+          } else {
+            // accumulator fully read: hand the TMEM buffer back to the MMA warp before the last chunk's math
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) {
+              if constexpr (CG == 1) mbar_arrive(&acc_empty[acc]);
+              else mbar_arrive_cluster(&acc_empty[acc], 0);
+            }
+          }
+          if (h == 0) {
+            // the TMA store that last read this staging buffer must have drained it
+            tma_store_wait_read<1>();  // a no-op for the lanes that never committed a store group
+            __syncwarp();
+          }
+          const uint32_t(&rc)[32] = r[c & 1];
+          const float4* bs4 = reinterpret_cast<const float4*>(smem_bs + c * 32);
+          const float4* bi4 = reinterpret_cast<const float4*>(smem_bias + c * 32);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {  // 8 columns per group
-            const int col = col_h + g * 8;
             float v[8];
             if (raw_out) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-            } else if (col < p.N) {
-              float bs[8], bi[8];
-              load_cols8_f32(p.Bs, col, bs);
-              if (has_bias) load_bias8(p.bias, p.bias_dtype, col, bi);
-#pragma unroll
-              for (int j = 0; j < 8; ++j)
-                v[j] = epilogue_value<KIND>(r[g * 8 + j], as, bs[j], has_bias ? bi[j] : 0.f, has_bias);
+              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rc[g * 8 + j]);
             } else {
+              const float4 b0 = bs4[2 * g], b1 = bs4[2 * g + 1];
+              const float bs[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+              float bi[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+              if (has_bias) {
+                const float4 c0 = bi4[2 * g], c1 = bi4[2 * g + 1];
+                bi[0] = c0.x; bi[1] = c0.y; bi[2] = c0.z; bi[3] = c0.w;
+                bi[4] = c1.x; bi[5] = c1.y; bi[6] = c1.z; bi[7] = c1.w;
+              }
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = 0.f;
+              for (int j = 0; j < 8; ++j) v[j] = epilogue_value<KIND>(rc[g * 8 + j], as, bs[j], bi[j], has_bias);
             }
             if constexpr (OUT_BYTES == 2) {
-              // 8 columns -> one 16-byte chunk; chunk index inside the 128 B row = h*4 + g
+              // 8 columns -> one 16-byte chunk; chunk index inside the box row = h*4 + g
               uint4 o;
               o.x = pack16(v[0], v[1], p.out_dtype);
               o.y = pack16(v[2], v[3], p.out_dtype);
@@ -252,39 +304,42 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             } else {
               // 8 columns -> two 16-byte chunks 2g, 2g+1
 #pragma unroll
-              for (int c = 0; c < 2; ++c) {
+              for (int cc = 0; cc < 2; ++cc) {
                 uint4 o;
-                o.x = __float_as_uint(v[4 * c + 0]);
-                o.y = __float_as_uint(v[4 * c + 1]);
-                o.z = __float_as_uint(v[4 * c + 2]);
-                o.w = __float_as_uint(v[4 * c + 3]);
-                const int chunk = (g * 2 + c) ^ swz;
+                o.x = __float_as_uint(v[4 * cc + 0]);
+                o.y = __float_as_uint(v[4 * cc + 1]);
+                o.z = __float_as_uint(v[4 * cc + 2]);
+                o.w = __float_as_uint(v[4 * cc + 3]);
+                const int chunk = (g * 2 + cc) ^ swz;
                 *reinterpret_cast<uint4*>(stage_buf + lane * BOX_BYTES + chunk * 16) = o;
               }
             }
           }
+          if (h == CH_PER_BOX - 1) {
+            const int col_box = col_tile + (c / CH_PER_BOX) * BOX_COLS;
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (row0 < p.M && col_box < p.N && elect_one()) {  // the same lane every time
+              tma_store_2d(&tmap_d, stage_buf, col_box, row0);
+              tma_store_commit();
+            }
+            buf ^= 1;
+          }
         }
-        fence_proxy_async_smem();
+      } else {
+        tc_fence_before_sync();
         __syncwarp();
-        if (lane == 0 && row0 < p.M && col_box < p.N) {
-          tma_store_2d(&tmap_d, stage_buf, col_box, row0);
-          tma_store_commit();
+        if (lane == 0) {
+          if constexpr (CG == 1) mbar_arrive(&acc_empty[acc]);
+          else mbar_arrive_cluster(&acc_empty[acc], 0);
         }
-        buf ^= 1;
-      }
-      // accumulator fully read: hand the TMEM buffer back to the MMA warp
-      tc_fence_before_sync();
-      __syncwarp();
-      if (lane == 0) {
-        if constexpr (CG == 1) mbar_arrive(&acc_empty[acc]);
-        else mbar_arrive_cluster(&acc_empty[acc], 0);
       }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
       }
     }
-    if (lane == 0) tma_store_wait_all<0>();
+    tma_store_wait_all<0>();
     if (p.prof && warp == EPI_WARP0 && lane == 0) p.prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(prof_epi);
   }
   if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);
@@ -316,14 +371,16 @@ static const TileConfig kConfigs[] = {
     {4, 256, 1, 1.0, "1cta_128x256"},  {5, 256, 2, 1.08, "2cta_256x256"}, {6, 128, 2, 0.8, "2cta_256x128"}};
 constexpr int kNumConfigs = sizeof(kConfigs) / sizeof(kConfigs[0]);
 
-static int stages_for(int b_rows) {
-  const int fixed = 4 * 2 * EPI_BUF_BYTES + 1024 /*align slack*/ + 512 /*barriers*/;
-  int s = (SMEM_LIMIT - fixed) / (BM * BK + b_rows * BK);
+// fixed part of the shared-memory window: store staging, the tile's Bs / bias (fp32), barriers + TMEM pointer
+static int fixed_smem(int bn) { return 4 * 2 * EPI_BUF_BYTES + 2 * bn * 4 + 256; }
+
+static int stages_for(int bn, int b_rows) {
+  int s = (SMEM_LIMIT - fixed_smem(bn)) / (BM * BK + b_rows * BK);
   return s > 12 ? 12 : s;
 }
 
-static size_t smem_bytes_for(int b_rows, int stages) {
-  return static_cast<size_t>(stages) * (BM * BK + b_rows * BK) + 4 * 2 * EPI_BUF_BYTES + 1024 + 512;
+static size_t smem_bytes_for(int bn, int b_rows, int stages) {
+  return static_cast<size_t>(stages) * (BM * BK + b_rows * BK) + fixed_smem(bn);
 }
 
 static const TileConfig& pick_config(int M, int N, int sms) {
@@ -403,6 +460,8 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   if (flavor == GEMM_E4M3_BLOCK128) return gemm_launch_blockwise(a, forced_config, used_config, st, err, err_len);
   const int sms = device_sm_count();
   const TileConfig* cfg = &pick_config(a.M, a.N, sms);
+  const int forced_debug = forced_config >> 8;  // developer experiments ride in the upper bits of the forced id
+  forced_config &= 0xff;
   if (forced_config >= 1 && forced_config <= kNumConfigs) cfg = &kConfigs[forced_config - 1];
   if (used_config) *used_config = cfg->name;
   const int bn = cfg->bn;
@@ -426,7 +485,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   p.num_m_blocks = (a.M + BM * cg - 1) / (BM * cg);
   p.num_n_blocks = (a.N + bn - 1) / bn;
   p.num_kb = (a.K + BK - 1) / BK;
-  p.stages = stages_for(b_rows);
+  p.stages = stages_for(bn, b_rows);
   {  // developer override for pipeline-depth experiments (tools/gemm_prof.py); never deepens beyond what fits
     static const int forced_stages = [] {
       const char* e = getenv("B2_GEMM_STAGES");
@@ -437,7 +496,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
       const char* e = getenv("B2_GEMM_DEBUG");
       return e ? atoi(e) : 0;
     }();
-    p.debug_flags = dbg;
+    p.debug_flags = dbg | forced_debug;
   }
   p.group_m = 16 / cg;
   p.prof = static_cast<unsigned long long*>(profile_buffer());
@@ -457,7 +516,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   const int units = sms / cg;
   const int grid = (tiles < units ? tiles : units) * cg;
-  const size_t smem = smem_bytes_for(b_rows, p.stages);
+  const size_t smem = smem_bytes_for(bn, b_rows, p.stages);
   if (flavor == GEMM_S8) {
     if (out_bytes == 2) return launch_cfg<MmaKind::I8, 2>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
     return launch_cfg<MmaKind::I8, 4>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);

@@ -10,9 +10,12 @@ kind = sys.argv[1] if len(sys.argv) > 1 else "s8"
 M, N, K = (int(v) for v in sys.argv[2:5]) if len(sys.argv) > 4 else (8192, 28672, 4096)
 cfgs = [int(v) for v in sys.argv[5:]] or [4, 5]
 dev = "cuda:0"
+zeros = os.environ.get("B2_PROF_DATA") == "zeros"  # zero operands draw little power: structure without the power cap
 if kind == "s8":
     A = torch.randint(-127, 128, (M, K), dtype=torch.int8, device=dev)
     W = torch.randint(-127, 128, (N, K), dtype=torch.int8, device=dev)
+    if zeros:
+        A.zero_(); W.zero_()
     op = b2.int8_scaled_mm
 else:
     A = torch.randn(M, K, device=dev).to(torch.float8_e4m3fn)

@@ -6,6 +6,7 @@
 #include <cudaTypedefs.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "b200_w8a8_internal.h"
@@ -30,25 +31,68 @@ struct KernelParams {
   int M, N, K;
   int num_m_blocks, num_n_blocks, num_kb;
   int stages;
-  int group_m;
+  int group_m;     // tile rows (or columns, when band_n) per raster band
+  int band_n;      // 0: bands of `group_m` row-blocks sweeping N;  1: bands of `group_m` column-blocks sweeping M
+  uint64_t policy_a, policy_b;  // L2 eviction policy of the operand loads (the band-resident operand is kept)
   int a_box_rows;  // rows of A actually fetched per stage (<= BM; small-M shapes fetch fewer)
   // optional per-CTA wait-cycle counters (b2_set_profile_buffer): [cta][0]=MMA waits for operands,
   // [1]=MMA waits for a free accumulator, [2]=producer waits for a free stage, [3]=epilogue waits
-  // for an accumulator (warp 2), [4]=CTA lifetime, all in SM clocks
+  // for an accumulator (warp 2), [4]=CTA lifetime, [5]=epilogue waits for a staging buffer (TMA store read),
+  // [6]=epilogue waits for tcgen05.ld, [7]=epilogue tile bodies in total; all in SM clocks
   unsigned long long* prof;
   int debug_flags;  // developer experiments (env B2_GEMM_DEBUG): 1 = skip the MMAs, 2 = skip the epilogue body, 4 = skip the loads
 };
 
 B2_DEVICE void tile_coords(int tile, const KernelParams& p, int& m_blk, int& n_blk) {
-  // bands of `group_m` row-blocks, row-block fastest inside a band: the CTAs that run
-  // concurrently share a few A row-blocks and a few W column-blocks in L2.
-  const int band_tiles = p.group_m * p.num_n_blocks;
+  // Raster in bands.  band_n == 0: a band is `group_m` row-blocks wide and sweeps all of N, row-block fastest:
+  // the band's slice of A stays in L2 while W streams through once per band.  band_n == 1 is the transpose
+  // (the band's slice of W is kept, A streams).  The host picks orientation and width from the operand sizes
+  // so that the DRAM traffic is as close to "every operand byte once" as the 126 MB L2 allows.
+  const int fast_blocks = p.band_n ? p.num_n_blocks : p.num_m_blocks;
+  const int slow_blocks = p.band_n ? p.num_m_blocks : p.num_n_blocks;
+  const int band_tiles = p.group_m * slow_blocks;
   const int band = tile / band_tiles;
   const int in_band = tile - band * band_tiles;
-  const int m_first = band * p.group_m;
-  const int rows_in_band = min(p.group_m, p.num_m_blocks - m_first);
-  m_blk = m_first + in_band % rows_in_band;
-  n_blk = in_band / rows_in_band;
+  const int first = band * p.group_m;
+  const int in_band_width = min(p.group_m, fast_blocks - first);
+  const int f = first + in_band % in_band_width;
+  const int s = in_band / in_band_width;
+  m_blk = p.band_n ? s : f;
+  n_blk = p.band_n ? f : s;
+}
+
+// Host: choose the raster (see tile_coords).  tile_m / tile_n are the rows of A / W one tile covers.
+static inline void choose_raster(long long M, long long N, long long K, int tile_m, int tile_n, int num_m_blocks,
+                                 int num_n_blocks, int* group, int* band_n, uint64_t* policy_a, uint64_t* policy_b) {
+  const double l2_keep = 40e6;  // bytes of one operand we try to keep resident (the output stream shares the L2)
+  const double a_bytes = static_cast<double>(M) * K, w_bytes = static_cast<double>(N) * K;
+  int gm = static_cast<int>(l2_keep / (static_cast<double>(tile_m) * K));
+  int gn = static_cast<int>(l2_keep / (static_cast<double>(tile_n) * K));
+  gm = gm < 1 ? 1 : (gm > num_m_blocks ? num_m_blocks : gm);
+  gn = gn < 1 ? 1 : (gn > num_n_blocks ? num_n_blocks : gn);
+  const double cost_m = a_bytes + w_bytes * ((num_m_blocks + gm - 1) / gm);  // bands over M: W re-streamed per band
+  const double cost_n = w_bytes + a_bytes * ((num_n_blocks + gn - 1) / gn);
+  bool along_m = cost_m <= cost_n;
+  {  // developer override for raster experiments: B2_GEMM_RASTER="<band_n>,<group>"
+    static const char* e = getenv("B2_GEMM_RASTER");
+    int bn_ = 0, g_ = 0;
+    if (e && sscanf(e, "%d,%d", &bn_, &g_) == 2 && g_ >= 1) {
+      along_m = bn_ == 0;
+      gm = g_ > num_m_blocks ? num_m_blocks : g_;
+      gn = g_ > num_n_blocks ? num_n_blocks : g_;
+    }
+  }
+  if (along_m) {
+    *band_n = 0;
+    *group = gm;
+    *policy_a = kEvictLast;
+    *policy_b = kEvictNormal;
+  } else {
+    *band_n = 1;
+    *group = gn;
+    *policy_a = kEvictNormal;
+    *policy_b = kEvictLast;
+  }
 }
 
 B2_DEVICE float load_bias(const void* bias, int dtype, int col) {
@@ -85,18 +129,31 @@ B2_DEVICE void load_bias8(const void* bias, int dtype, int col, float (&v)[8]) {
   }
 }
 
+// One output element.  `bias` is the bias value or -0.0f when the op has no bias: fma(t, bs, -0) and t + (-0)
+// round exactly like the bias-free forms (t * bs, t) including the sign of zero, so one code path serves both
+// and stays bit-identical to the reference's two.
 template <MmaKind KIND>
-B2_DEVICE float epilogue_value(uint32_t raw, float as, float bs, float bias, bool has_bias) {
+B2_DEVICE float epilogue_value(uint32_t raw, float as, float bs, float bias) {
   if constexpr (KIND == MmaKind::I8) {
     // gemm_int8.cpp:40-46: fmadd(mul(cvtepi32_ps(acc), As), Bs, bias)  |  mul(mul(.., As), Bs)
     const float c = __int2float_rn(static_cast<int32_t>(raw));
-    const float t = __fmul_rn(c, as);
-    return has_bias ? __fmaf_rn(t, bs, bias) : __fmul_rn(t, bs);
+    return __fmaf_rn(__fmul_rn(c, as), bs, bias);
   } else {
     // fp8_gemm_kernel.cu sm100 EVT: As * (Bs * acc) [+ bias]
     const float c = __uint_as_float(raw);
-    const float t = __fmul_rn(as, __fmul_rn(bs, c));
-    return has_bias ? __fadd_rn(t, bias) : t;
+    return __fadd_rn(__fmul_rn(as, __fmul_rn(bs, c)), bias);
+  }
+}
+
+// OUT_KIND 0 = bf16, 1 = f16 (compile-time: a run-time dtype doubles every pack in the epilogue's hot loop)
+template <int OUT_KIND>
+B2_DEVICE uint32_t pack16(float lo, float hi) {
+  if constexpr (OUT_KIND == 0) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
+  } else {
+    const __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&v);
   }
 }
 

@@ -33,10 +33,12 @@
 
 namespace b2 {
 
-template <MmaKind KIND, int OUT_BYTES, int BN, int CG>
+// OUT_KIND: 0 = bf16, 1 = f16, 2 = 32-bit (f32, or the raw s32 accumulators)
+template <MmaKind KIND, int OUT_KIND, int BN, int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_w8a8_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                      const __grid_constant__ CUtensorMap tmap_d, const KernelParams p) {
+  constexpr int OUT_BYTES = OUT_KIND == 2 ? 4 : 2;
   constexpr int B_ROWS = BN / CG;  // rows of the W tile this CTA stages
   constexpr uint32_t A_STAGE_BYTES = BM * BK;
   constexpr uint32_t B_STAGE_BYTES = B_ROWS * BK;
@@ -122,16 +124,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           } else if constexpr (CG == 1) {
             if (elect_one()) {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kb * BK, m_row, kEvictNormal);
-              tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * BK, n_row, kEvictNormal);
+              tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kb * BK, m_row, p.policy_a);
+              tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * BK, n_row, p.policy_b);
             }
           } else {
             // both CTAs' bytes are expected on (and complete on) the leader CTA's barrier
             if (elect_one()) {
               if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
               const uint32_t bar0 = smem_u32(&full_bar[stage]) & kPeerBitMask;
-              tma_load_2d_cg2(smem_u32(a_dst), &tmap_a, bar0, kb * BK, m_row, kEvictNormal);
-              tma_load_2d_cg2(smem_u32(b_dst), &tmap_b, bar0, kb * BK, n_row, kEvictNormal);
+              tma_load_2d_cg2(smem_u32(a_dst), &tmap_a, bar0, kb * BK, m_row, p.policy_a);
+              tma_load_2d_cg2(smem_u32(b_dst), &tmap_b, bar0, kb * BK, n_row, p.policy_b);
             }
           }
           __syncwarp();
@@ -209,7 +211,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     int acc = 0;
     uint32_t acc_phase = 0;
     int buf = 0;
-    long long prof_epi = 0;
+    long long prof_epi = 0, prof_wr = 0, prof_ld = 0, prof_body = 0;
     constexpr int BOX_COLS = COLS_PER_BOX < BN ? COLS_PER_BOX : BN;
     constexpr int BOX_BYTES = BOX_COLS * OUT_BYTES;  // 128 (SW128 box) or 64 (SW64 box, BN = 32 @ 16 bit)
     static_assert(BOX_BYTES == 128 || BOX_BYTES == 64, "store box is 128 or 64 bytes wide");
@@ -232,7 +234,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         for (int c = epi_tid; c < BN; c += 128) {
           const int col = col_tile + c;
           smem_bs[c] = col < p.N ? __ldg(p.Bs + col) : 0.f;
-          smem_bias[c] = (has_bias && col < p.N) ? load_bias(p.bias, p.bias_dtype, col) : 0.f;
+          smem_bias[c] = (has_bias && col < p.N) ? load_bias(p.bias, p.bias_dtype, col) : -0.f;  // x + (-0) == x bit for bit
         }
       }
       epi_bar_sync();
@@ -245,85 +247,102 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       tc_fence_after_sync();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
 
+      const long long body0 = p.prof ? clock64() : 0;
       if (!(p.debug_flags & 2)) {
-        // 32-column TMEM loads, software-pipelined over two register sets: the load of chunk c+1 is in
-        // flight while chunk c is scaled, cast and staged
+        // 32-column TMEM loads, software-pipelined over two register sets: the load of chunk c+1 is in flight
+        // while chunk c is scaled, cast and staged.  The loop over PAIRS of chunks stays rolled -- fully unrolled
+        // the body is ~40 KB of SASS and the four epilogue warps stall on instruction fetch.
         uint32_t r[2][32];
+        constexpr int NPAIR = NCH >= 2 ? NCH / 2 : 1;
+        constexpr int CH_PER_PAIR = NCH >= 2 ? 2 : 1;
         tmem_ld_32x32b_x32(t_row, r[0]);
+#pragma unroll 1
+        for (int pr = 0; pr < NPAIR; ++pr) {
 #pragma unroll
-        for (int c = 0; c < NCH; ++c) {
-          const int h = c % CH_PER_BOX;
-          uint8_t* stage_buf = my_epi + buf * EPI_BUF_BYTES;
-          tmem_ld_wait();
-          if (c + 1 < NCH) {
-            tmem_ld_32x32b_x32(t_row + static_cast<uint32_t>((c + 1) * 32), r[(c + 1) & 1]);
-          } else {
-            // accumulator fully read: hand the TMEM buffer back to the MMA warp before the last chunk's math
-            tc_fence_before_sync();
-            __syncwarp();
-            if (lane == 0) {
-              if constexpr (CG == 1) mbar_arrive(&acc_empty[acc]);
-              else mbar_arrive_cluster(&acc_empty[acc], 0);
+          for (int hh = 0; hh < CH_PER_PAIR; ++hh) {
+            const int c = pr * CH_PER_PAIR + hh;      // chunk index inside the tile
+            const int h = CH_PER_BOX == 2 ? hh : 0;   // chunk index inside its store box
+            uint8_t* stage_buf = my_epi + buf * EPI_BUF_BYTES;
+            {
+              const long long l0 = p.prof ? clock64() : 0;
+              tmem_ld_wait();
+              if (p.prof) prof_ld += clock64() - l0;
             }
-          }
-          if (h == 0) {
-            // the TMA store that last read this staging buffer must have drained it
-            tma_store_wait_read<1>();  // a no-op for the lanes that never committed a store group
-            __syncwarp();
-          }
-          const uint32_t(&rc)[32] = r[c & 1];
-          const float4* bs4 = reinterpret_cast<const float4*>(smem_bs + c * 32);
-          const float4* bi4 = reinterpret_cast<const float4*>(smem_bias + c * 32);
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {  // 8 columns per group
-            float v[8];
-            if (raw_out) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rc[g * 8 + j]);
+            if (c + 1 < NCH) {
+              tmem_ld_32x32b_x32(t_row + static_cast<uint32_t>((c + 1) * 32), r[(hh + 1) & 1]);
             } else {
-              const float4 b0 = bs4[2 * g], b1 = bs4[2 * g + 1];
-              const float bs[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-              float bi[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-              if (has_bias) {
-                const float4 c0 = bi4[2 * g], c1 = bi4[2 * g + 1];
-                bi[0] = c0.x; bi[1] = c0.y; bi[2] = c0.z; bi[3] = c0.w;
-                bi[4] = c1.x; bi[5] = c1.y; bi[6] = c1.z; bi[7] = c1.w;
+              // accumulator fully read: hand the TMEM buffer back to the MMA warp before the last chunk's math
+              tc_fence_before_sync();
+              __syncwarp();
+              if (lane == 0) {
+                if constexpr (CG == 1) mbar_arrive(&acc_empty[acc]);
+                else mbar_arrive_cluster(&acc_empty[acc], 0);
               }
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = epilogue_value<KIND>(rc[g * 8 + j], as, bs[j], bi[j], has_bias);
             }
-            if constexpr (OUT_BYTES == 2) {
-              // 8 columns -> one 16-byte chunk; chunk index inside the box row = h*4 + g
-              uint4 o;
-              o.x = pack16(v[0], v[1], p.out_dtype);
-              o.y = pack16(v[2], v[3], p.out_dtype);
-              o.z = pack16(v[4], v[5], p.out_dtype);
-              o.w = pack16(v[6], v[7], p.out_dtype);
-              const int chunk = (h * 4 + g) ^ swz;
-              *reinterpret_cast<uint4*>(stage_buf + lane * BOX_BYTES + chunk * 16) = o;
-            } else {
-              // 8 columns -> two 16-byte chunks 2g, 2g+1
+            if (h == 0) {
+              // the TMA store that last read this staging buffer must have drained it
+              const long long r0 = p.prof ? clock64() : 0;
+              tma_store_wait_read<1>();  // a no-op for the lanes that never committed a store group
+              __syncwarp();
+              if (p.prof) prof_wr += clock64() - r0;
+            }
+            const uint32_t(&rc)[32] = r[hh & 1];
+            const float4* bs4 = reinterpret_cast<const float4*>(smem_bs + c * 32);
+            const float4* bi4 = reinterpret_cast<const float4*>(smem_bias + c * 32);
+            // per-column scale / bias of the next 8 columns are fetched before the current 8 are stored, so the
+            // shared-memory load latency hides behind the math instead of following every STS
+            float4 nb[4];
+            if (!raw_out) {
+              nb[0] = bs4[0]; nb[1] = bs4[1]; nb[2] = bi4[0]; nb[3] = bi4[1];
+            }
 #pragma unroll
-              for (int cc = 0; cc < 2; ++cc) {
+            for (int g = 0; g < 4; ++g) {  // 8 columns per group
+              float v[8];
+              if (raw_out) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(rc[g * 8 + j]);
+              } else {
+                const float bs[8] = {nb[0].x, nb[0].y, nb[0].z, nb[0].w, nb[1].x, nb[1].y, nb[1].z, nb[1].w};
+                const float bi[8] = {nb[2].x, nb[2].y, nb[2].z, nb[2].w, nb[3].x, nb[3].y, nb[3].z, nb[3].w};
+                if (g < 3) {
+                  nb[0] = bs4[2 * g + 2]; nb[1] = bs4[2 * g + 3]; nb[2] = bi4[2 * g + 2]; nb[3] = bi4[2 * g + 3];
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = epilogue_value<KIND>(rc[g * 8 + j], as, bs[j], bi[j]);
+              }
+              if constexpr (OUT_BYTES == 2) {
+                // 8 columns -> one 16-byte chunk; chunk index inside the box row = h*4 + g
                 uint4 o;
-                o.x = __float_as_uint(v[4 * cc + 0]);
-                o.y = __float_as_uint(v[4 * cc + 1]);
-                o.z = __float_as_uint(v[4 * cc + 2]);
-                o.w = __float_as_uint(v[4 * cc + 3]);
-                const int chunk = (g * 2 + cc) ^ swz;
+                o.x = pack16<OUT_KIND>(v[0], v[1]);
+                o.y = pack16<OUT_KIND>(v[2], v[3]);
+                o.z = pack16<OUT_KIND>(v[4], v[5]);
+                o.w = pack16<OUT_KIND>(v[6], v[7]);
+                const int chunk = (h * 4 + g) ^ swz;
                 *reinterpret_cast<uint4*>(stage_buf + lane * BOX_BYTES + chunk * 16) = o;
+              } else {
+                // 8 columns -> two 16-byte chunks 2g, 2g+1
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc) {
+                  uint4 o;
+                  o.x = __float_as_uint(v[4 * cc + 0]);
+                  o.y = __float_as_uint(v[4 * cc + 1]);
+                  o.z = __float_as_uint(v[4 * cc + 2]);
+                  o.w = __float_as_uint(v[4 * cc + 3]);
+                  const int chunk = (g * 2 + cc) ^ swz;
+                  *reinterpret_cast<uint4*>(stage_buf + lane * BOX_BYTES + chunk * 16) = o;
+                }
               }
             }
-          }
-          if (h == CH_PER_BOX - 1) {
-            const int col_box = col_tile + (c / CH_PER_BOX) * BOX_COLS;
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (row0 < p.M && col_box < p.N && elect_one()) {  // the same lane every time
-              tma_store_2d(&tmap_d, stage_buf, col_box, row0);
-              tma_store_commit();
+            if (h == CH_PER_BOX - 1) {
+              const int col_box = col_tile + (c / CH_PER_BOX) * BOX_COLS;
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (row0 < p.M && col_box < p.N && elect_one()) {  // the same lane every time
+                tma_store_2d(&tmap_d, stage_buf, col_box, row0);
+                tma_store_commit();
+              }
+              buf ^= 1;
             }
-            buf ^= 1;
           }
         }
       } else {
@@ -334,13 +353,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           else mbar_arrive_cluster(&acc_empty[acc], 0);
         }
       }
+      if (p.prof) prof_body += clock64() - body0;
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
       }
     }
     tma_store_wait_all<0>();
-    if (p.prof && warp == EPI_WARP0 && lane == 0) p.prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(prof_epi);
+    if (p.prof && warp == EPI_WARP0 && lane == 0) {
+      p.prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(prof_epi);
+      p.prof[blockIdx.x * 8 + 5] = static_cast<unsigned long long>(prof_wr);
+      p.prof[blockIdx.x * 8 + 6] = static_cast<unsigned long long>(prof_ld);
+      p.prof[blockIdx.x * 8 + 7] = static_cast<unsigned long long>(prof_body);
+    }
   }
   if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);
 
@@ -403,10 +428,10 @@ static const TileConfig& pick_config(int M, int N, int sms) {
   return kConfigs[best];
 }
 
-template <MmaKind KIND, int OUT_BYTES, int BN, int CG>
+template <MmaKind KIND, int OUT_KIND, int BN, int CG>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const KernelParams& p,
                       int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
-  auto kern = gemm_w8a8_kernel<KIND, OUT_BYTES, BN, CG>;
+  auto kern = gemm_w8a8_kernel<KIND, OUT_KIND, BN, CG>;
   static int attr_dev = -1;  // per instantiation; the attribute is per-function, per-device context
   int dev = 0;
   cudaGetDevice(&dev);
@@ -439,16 +464,16 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
   return B2_OK;
 }
 
-template <MmaKind KIND, int OUT_BYTES>
+template <MmaKind KIND, int OUT_KIND>
 static int launch_cfg(const TileConfig& c, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td,
                       const KernelParams& p, int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
   switch (c.id) {
-    case 1: return launch_one<KIND, OUT_BYTES, 32, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
-    case 2: return launch_one<KIND, OUT_BYTES, 64, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
-    case 3: return launch_one<KIND, OUT_BYTES, 128, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
-    case 4: return launch_one<KIND, OUT_BYTES, 256, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
-    case 5: return launch_one<KIND, OUT_BYTES, 256, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
-    default: return launch_one<KIND, OUT_BYTES, 128, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 1: return launch_one<KIND, OUT_KIND, 32, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 2: return launch_one<KIND, OUT_KIND, 64, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 3: return launch_one<KIND, OUT_KIND, 128, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 4: return launch_one<KIND, OUT_KIND, 256, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+    case 5: return launch_one<KIND, OUT_KIND, 256, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
+    default: return launch_one<KIND, OUT_KIND, 128, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
   }
 }
 
@@ -498,7 +523,8 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
     }();
     p.debug_flags = dbg | forced_debug;
   }
-  p.group_m = 16 / cg;
+  choose_raster(a.M, a.N, a.K, BM * cg, bn, p.num_m_blocks, p.num_n_blocks, &p.group_m, &p.band_n, &p.policy_a,
+                &p.policy_b);
   p.prof = static_cast<unsigned long long*>(profile_buffer());
   // decode shapes: fetch only the rows that exist (rounded to the 8-row swizzle atom);
   // the untouched tail of the smem tile feeds MMA rows whose outputs are clipped by the store.
@@ -517,12 +543,15 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   const int units = sms / cg;
   const int grid = (tiles < units ? tiles : units) * cg;
   const size_t smem = smem_bytes_for(bn, b_rows, p.stages);
+  const int out_kind = a.out_dtype == B2_DTYPE_BF16 ? 0 : (a.out_dtype == B2_DTYPE_F16 ? 1 : 2);
   if (flavor == GEMM_S8) {
-    if (out_bytes == 2) return launch_cfg<MmaKind::I8, 2>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
-    return launch_cfg<MmaKind::I8, 4>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
+    if (out_kind == 0) return launch_cfg<MmaKind::I8, 0>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
+    if (out_kind == 1) return launch_cfg<MmaKind::I8, 1>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
+    return launch_cfg<MmaKind::I8, 2>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
   }
-  if (out_bytes == 2) return launch_cfg<MmaKind::F8, 2>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
-  return launch_cfg<MmaKind::F8, 4>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
+  if (out_kind == 0) return launch_cfg<MmaKind::F8, 0>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
+  if (out_kind == 1) return launch_cfg<MmaKind::F8, 1>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
+  return launch_cfg<MmaKind::F8, 2>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
 }
 
 }  // namespace b2

@@ -75,7 +75,7 @@ B2_DEVICE void mbar_arrive_cluster(uint64_t* bar, uint32_t cta) {
   asm volatile(
       "{\n\t.reg .b32 ra;\n\t"
       "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
       "r"(cta)
       : "memory");
 }
@@ -153,10 +153,12 @@ B2_DEVICE void tma_load_2d_cg2(uint32_t smem_dst, const CUtensorMap* m, uint32_t
       : "memory");
 }
 
+// the output is written once and never read back by this kernel: evict-first keeps it from pushing the
+// operands out of L2
 B2_DEVICE void tma_store_2d(const CUtensorMap* m, const void* smem_src, int32_t c0, int32_t c1) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(
                    reinterpret_cast<uint64_t>(m)),
-               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "l"(kEvictFirst)
                : "memory");
 }
 

@@ -41,10 +41,16 @@ for cfg in cfgs:
     torch.cuda.synchronize()
     b2.capi.lib.b2_set_profile_buffer(None)
     p = prof.view(148, 8).double().cpu()
+    cfgname = b2.capi.last_gemm_config()
+    tm = 256 if cfgname.startswith('2cta') else 128
+    tn = int(cfgname.split('x')[-1])
+    tiles_total = (-(-M // tm)) * (-(-N // tn)) * (2 if tm == 256 else 1)
     life = p[:, 4].clamp_min(1)
     lead = p[p[:, 0] > 0] if (p[:, 0] > 0).any() else p
     print(f"{kind} M={M} N={N} K={K} cfg={cfg}:{b2.capi.last_gemm_config()}  {t*1e6:8.1f} us {2.0*M*N*K/t/1e12:7.1f} TOPS | "
           f"CTA life {life.mean():.0f} clk (max {life.max():.0f}) | MMA waits operands {100*(lead[:,0]/lead[:,4]).mean():.1f}% "
           f"accum {100*(lead[:,1]/lead[:,4]).mean():.1f}% | producer waits stage {100*(p[:,2]/life).mean():.1f}% | "
-          f"epilogue waits accum {100*(p[:,3]/life).mean():.1f}%", flush=True)
+          f"epilogue waits accum {100*(p[:,3]/life).mean():.1f}% body {100*(p[:,7]/life).mean():.1f}% "
+          f"(store-buffer wait {100*(p[:,5]/life).mean():.1f}%, tmem-ld wait {100*(p[:,6]/life).mean():.1f}%) "
+          f"body clk/tile {(p[:,7].sum()/ (tiles_total)):.0f}", flush=True)
 b2.capi.set_gemm_config(0)

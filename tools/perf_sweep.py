@@ -1,0 +1,165 @@
+"""Per-shape throughput of every kernel family on the BASELINE.json configs (developer tool; feeds profiles/).
+
+    python tools/perf_sweep.py [int8] [fp8] [block] [quant] [--quick]
+
+Method: CUDA events around back-to-back launches for >= 40 ms after warm-up; operands rotate through
+enough distinct buffers that the bytes touched between two uses of the same buffer exceed the 126 MB L2, so the
+memory-bound shapes (M <= 64, quantizers) see HBM and not a warm cache.  Ops = 2*M*N*K; bytes = the ALGORITHMIC
+bytes of SURVEY 8(d) (every operand once, output once).  Peaks: tensor = 2 x the measured cuBLAS bf16 rate of
+MEASURED_PEAKS.json (burst, these are short runs), HBM = its measured copy bandwidth.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import sglang_diffusion_b200 as b2  # noqa: E402
+
+dev = torch.device("cuda:0")
+QUICK = "--quick" in sys.argv
+want = [a for a in sys.argv[1:] if not a.startswith("--")] or ["int8", "fp8", "block", "quant"]
+try:
+    PK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+except Exception:
+    PK = {}
+HBM = PK.get("hbm_gbs", 6650.0)
+TENSOR = 2.0 * PK.get("bf16_tflops", 1590.0)
+L2_BYTES = 160e6
+
+
+def timed(fns, min_ms=40.0):
+    """fns: list of closures (one per rotating buffer set).  Returns seconds per call."""
+    for f in fns[: min(len(fns), 3)]:
+        f()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = len(fns)
+    reps = 1
+    while True:
+        e0.record()
+        for _ in range(reps):
+            for f in fns:
+                f()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if ms >= min_ms or reps >= 4096:
+            return ms * 1e-3 / (reps * n)
+        reps = max(reps * 2, int(reps * min_ms / max(ms, 1e-3)) + 1)
+
+
+def copies_for(bytes_per_set):
+    return max(1, min(64, int(L2_BYTES // max(bytes_per_set, 1)) + 1))
+
+
+def line(name, M, N, K, t, ops, byts, cfg=""):
+    tops = ops / t / 1e12
+    gbs = byts / t / 1e9
+    print(f"{name:22s} M={M:<6d} N={N:<6d} K={K:<6d} {t*1e6:9.1f} us  {tops:8.1f} TOPS ({100*tops/TENSOR:5.1f}% of {TENSOR:.0f})  "
+          f"{gbs:8.1f} GB/s ({100*gbs/HBM:5.1f}% of {HBM:.0f})  {cfg}", flush=True)
+
+
+def gemm_int8(M, N, K, bias=False):
+    nset = copies_for(N * K + M * K + 2 * M * N)
+    sets = []
+    for _ in range(nset):
+        A = torch.randint(-127, 128, (M, K), dtype=torch.int8, device=dev)
+        W = torch.randint(-127, 128, (N, K), dtype=torch.int8, device=dev)
+        sets.append((A, W))
+    As = torch.rand(M, 1, device=dev)
+    Bs = torch.rand(N, 1, device=dev) * 1e-2
+    b = torch.randn(N, device=dev).bfloat16() if bias else None
+    fns = [(lambda A=A, W=W: b2.int8_scaled_mm(A, W.t(), As, Bs, torch.bfloat16, b)) for A, W in sets]
+    t = timed(fns)
+    line("int8_scaled_mm", M, N, K, t, 2.0 * M * N * K, M * K + N * K + 2 * M * N + 4 * M + 4 * N, b2.capi.last_gemm_config())
+
+
+def gemm_fp8(M, N, K):
+    nset = copies_for(N * K + M * K + 2 * M * N)
+    sets = []
+    for _ in range(nset):
+        A = (torch.randn(M, K, device=dev)).to(torch.float8_e4m3fn)
+        W = (torch.randn(N, K, device=dev)).to(torch.float8_e4m3fn)
+        sets.append((A, W))
+    As = torch.rand(M, 1, device=dev)
+    Bs = torch.rand(N, 1, device=dev) * 1e-2
+    fns = [(lambda A=A, W=W: b2.fp8_scaled_mm(A, W.t(), As, Bs, torch.bfloat16, None)) for A, W in sets]
+    t = timed(fns)
+    line("fp8_scaled_mm", M, N, K, t, 2.0 * M * N * K, M * K + N * K + 2 * M * N + 4 * M + 4 * N, b2.capi.last_gemm_config())
+
+
+def gemm_block(M, N, K):
+    nset = copies_for(N * K + M * K + 2 * M * N)
+    sets = []
+    for _ in range(nset):
+        A = (torch.randn(M, K, device=dev)).to(torch.float8_e4m3fn)
+        W = (torch.randn(N, K, device=dev)).to(torch.float8_e4m3fn)
+        sets.append((A, W))
+    sfa = torch.rand(K // 128, M, device=dev).t()          # [M, K/128], stride(0) == 1 (M-major)
+    sfb = torch.rand(N // 128, K // 128, device=dev).t()   # [K/128, N/128], K-major
+    fns = [(lambda A=A, W=W: b2.fp8_blockwise_scaled_mm(A, W.t(), sfa, sfb, torch.bfloat16)) for A, W in sets]
+    t = timed(fns)
+    line("fp8_blockwise_mm", M, N, K, t, 2.0 * M * N * K,
+         M * K + N * K + 2 * M * N + 4 * M * K // 128 + 4 * (N // 128) * (K // 128), b2.capi.last_gemm_config())
+
+
+def quant(kind, M, K):
+    nset = copies_for(3 * M * K)
+    xs = [(torch.randn(M, K, device=dev) / 10).bfloat16() for _ in range(nset)]
+    if kind == "int8":
+        fns = [(lambda x=x: b2.per_token_quant_int8(x)) for x in xs]
+        byts = 3 * M * K + 4 * M
+    elif kind == "fp8":
+        fns = [(lambda x=x: b2.sglang_per_token_quant_fp8(x)) for x in xs]
+        byts = 3 * M * K + 4 * M
+    else:
+        fns = [(lambda x=x: b2.sglang_per_token_group_quant_fp8(x, 128, column_major_scales=True)) for x in xs]
+        byts = 3 * M * K + 4 * M * K // 128
+    t = timed(fns)
+    line(f"quant_{kind}", M, 0, K, t, 0.0, byts)
+
+
+def linear_int8(M, N, K):
+    nset = copies_for(N * K + 2 * M * K + 2 * M * N)
+    sets = []
+    for _ in range(nset):
+        x = (torch.randn(M, K, device=dev) / 10).bfloat16()
+        W = torch.randint(-127, 128, (N, K), dtype=torch.int8, device=dev)
+        sets.append((x, W))
+    Bs = torch.rand(N, device=dev) * 1e-2
+    fns = [(lambda x=x, W=W: b2.int8_scaled_mm_with_quant(x, W, Bs, None, torch.bfloat16, False)) for x, W in sets]
+    t = timed(fns)
+    line("int8 linear (q+mm)", M, N, K, t, 2.0 * M * N * K, 2 * M * K + N * K + 2 * M * N + 4 * N)
+
+
+if "int8" in want:
+    print("# C1 + C2: Llama-3-8B int8 shapes"); gemm_int8(128, 4096, 4096, bias=True)
+    Ms = [1, 16, 64, 256, 1024, 4096, 8192] if not QUICK else [16, 8192]
+    for K, N in ((4096, 6144), (4096, 28672), (14336, 4096)):
+        for M in Ms:
+            gemm_int8(M, N, K)
+    print("# C4: Wan2.1-14B / FLUX.1 DiT shapes, M = 32768 and the 8-way shard 4096")
+    for K, N in ((5120, 5120), (5120, 13824), (13824, 5120), (3072, 9216), (3072, 12288), (12288, 3072)):
+        for M in ([32768, 4096] if not QUICK else [4096]):
+            gemm_int8(M, N, K)
+    print("# fused linear"); linear_int8(8192, 28672, 4096); linear_int8(16, 28672, 4096)
+if "fp8" in want:
+    print("# C5: Llama-3-70B TP=8 fp8 shards")
+    for K, N in ((8192, 1280), (8192, 7168), (1024, 8192), (3584, 8192)):
+        for M in (64, 8192):
+            gemm_fp8(M, N, K)
+    gemm_fp8(8192, 28672, 4096)
+if "block" in want:
+    print("# C3: DeepSeek-V3 block-wise fp8, M = 4096")
+    for N, K in ((24576, 1536), (32768, 512), (7168, 16384), (36864, 7168), (7168, 18432), (4096, 7168), (7168, 2048)):
+        gemm_block(4096, N, K)
+if "quant" in want:
+    print("# quantizers")
+    for M, K in ((8192, 4096), (8192, 14336), (32768, 5120), (64, 8192), (16, 4096)):
+        for kind in ("int8", "fp8", "group"):
+            quant(kind, M, K)

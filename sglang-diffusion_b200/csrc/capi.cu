@@ -229,9 +229,9 @@ int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64
                           int64_t sfb_k_stride, const void* bias, int bias_dtype, void* D, int64_t ldd,
                           int out_dtype, int M, int N, int K, b2_stream_t stream) {
   if (int r = check_arch()) return r;
-  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16 && out_dtype != B2_DTYPE_F32)
+  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16)  // fp8_blockwise_gemm_kernel.cu:405-406
     return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: out_dtype must be Half or BFloat16");
-  const int ob = out_dtype == B2_DTYPE_F32 ? 4 : 2;
+  const int ob = 2;
   if (int r = check_gemm_common(A, lda, W, ldw, D, ldd, ob, M, N, K)) return r;
   if (K % 128 != 0) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: K=%d must be a multiple of 128", K);
   if (!sfa || !sfb) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: scales must not be null");

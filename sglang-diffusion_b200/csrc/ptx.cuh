@@ -51,6 +51,8 @@ B2_DEVICE void cluster_sync_all() {
 
 // named barrier 1 over the four epilogue warps (128 threads); barrier 0 stays __syncthreads
 B2_DEVICE void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// named barrier 1 over the eight promotion warps of the block-wise kernel (256 threads)
+B2_DEVICE void promo_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 B2_DEVICE uint64_t globaltimer_ns() {
   uint64_t t;
@@ -116,6 +118,25 @@ B2_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
 #endif
 }
 
+// Whole-warp wait on up to 32 DIFFERENT barriers with one instruction stream: lane i waits for (bar, parity) when
+// `active`.  mbarrier.try_wait blocks its warp for ~150-200 clocks even when the phase is already complete, so a
+// role that needs k barriers per step pays that once instead of k times.
+B2_DEVICE void mbar_wait_lanes(uint64_t* bar, uint32_t parity, bool active) {
+  bool done = !active || mbar_try_wait(bar, parity);
+  uint32_t spins = 0;
+  uint64_t t0 = 0;
+  while (!__all_sync(0xffffffffu, done)) {
+    if (!done) done = mbar_try_wait(bar, parity);
+#if B2_WAIT_WATCHDOG
+    if (++spins >= 0x10000u && (spins & 0x3ffu) == 0) {
+      const uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ull) __trap();
+    }
+#endif
+  }
+}
+
 // ------------------------------------------------------------------ TMA ----
 
 B2_DEVICE void tma_prefetch_desc(const CUtensorMap* m) {
@@ -172,6 +193,16 @@ B2_DEVICE void tma_store_wait_read() {
 template <int N>
 B2_DEVICE void tma_store_wait_all() {
   asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// 4-byte asynchronous global -> shared copy (LDGSTS): no register is tied up while the load is in flight
+B2_DEVICE void cp_async_4(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+B2_DEVICE void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+B2_DEVICE void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
 // generic-proxy smem writes -> visible to the async proxy (TMA store, tcgen05 reads)

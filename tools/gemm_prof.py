@@ -20,10 +20,16 @@ if kind == "s8":
 else:
     A = torch.randn(M, K, device=dev).to(torch.float8_e4m3fn)
     W = torch.randn(N, K, device=dev).to(torch.float8_e4m3fn)
+    if zeros:
+        A = torch.zeros(M, K, device=dev).to(torch.float8_e4m3fn); W = torch.zeros(N, K, device=dev).to(torch.float8_e4m3fn)
     op = b2.fp8_scaled_mm
 As = torch.rand(M, 1, device=dev)
 Bs = torch.rand(N, 1, device=dev)
-prof = torch.zeros(148 * 8, dtype=torch.int64, device=dev)
+if kind == "bw":  # block-wise: SFA [M, K/128] M-major, SFB [K/128, N/128] K-major; cfg 1 = 1-CTA, 2 = 2-CTA
+    As = torch.rand(K // 128, M, device=dev).t()
+    Bs = torch.rand(N // 128, K // 128, device=dev).t()
+    op = lambda a, w, sa, sb, dt, bias: b2.fp8_blockwise_scaled_mm(a, w, sa, sb, dt)
+prof = torch.zeros(148 * 8 + 64 * 8, dtype=torch.int64, device=dev)
 for cfg in cfgs:
     b2.capi.set_gemm_config(cfg)
     for _ in range(3):
@@ -40,10 +46,11 @@ for cfg in cfgs:
     op(A, W.t(), As, Bs, torch.bfloat16, None)
     torch.cuda.synchronize()
     b2.capi.lib.b2_set_profile_buffer(None)
-    p = prof.view(148, 8).double().cpu()
+    tl = prof[148 * 8:].view(64, 8).cpu()
+    p = prof[:148 * 8].view(148, 8).double().cpu()
     cfgname = b2.capi.last_gemm_config()
     tm = 256 if cfgname.startswith('2cta') else 128
-    tn = int(cfgname.split('x')[-1])
+    tn = int(cfgname.split('x')[1].split('_')[0])
     tiles_total = (-(-M // tm)) * (-(-N // tn)) * (2 if tm == 256 else 1)
     life = p[:, 4].clamp_min(1)
     lead = p[p[:, 0] > 0] if (p[:, 0] > 0).any() else p
@@ -53,4 +60,10 @@ for cfg in cfgs:
           f"epilogue waits accum {100*(p[:,3]/life).mean():.1f}% body {100*(p[:,7]/life).mean():.1f}% "
           f"(store-buffer wait {100*(p[:,5]/life).mean():.1f}%, tmem-ld wait {100*(p[:,6]/life).mean():.1f}%) "
           f"body clk/tile {(p[:,7].sum()/ (tiles_total)):.0f}", flush=True)
+    if kind == "bw":
+        nkb = K // 128
+        kbs = tiles_total / 148 * nkb  # K blocks per CTA
+        print(f"   block-wise, clk per K block: loop {life.mean()/kbs:.0f} | promotion warp waits: partial {p[:,3].mean()/kbs:.0f} "
+              f"scales+barrier {p[:,5].mean()/kbs:.0f} | MMA warp waits (stage + slot) {lead[:,0].mean()/kbs:.0f} | "
+              f"producer waits {p[:,2].mean()/kbs:.0f}", flush=True)
 b2.capi.set_gemm_config(0)

@@ -52,6 +52,18 @@ DATASHEET_INT8_TOPS = 4500.0
 CPU_SAMPLE_ROWS = 1024
 
 
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum per GEMM launch (average over the workload's layers) from the
+    committed `ncu --set full` capture, or None when no capture of this workload is on file."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return d["avg_bytes_per_launch"] if d.get("workload") == workload else None
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -309,7 +321,7 @@ def main():
     peak_tops = 2.0 * peaks["bf16_sustained"]
     roofline = {"bound": "tensor", "kernel": f"gemm_w8a8_kernel<kind::i8> ({gemm_cfg})",
                 "achieved": round(gemm_tops, 1), "peak": round(peak_tops, 1), "unit": "TFLOP/s",
-                "frac": round(gemm_tops / peak_tops, 4), "traffic": None,
+                "frac": round(gemm_tops / peak_tops, 4), "traffic": ncu_traffic(args.workload),
                 "peak_source": f"2 x bf16_tflops_sustained of MEASURED_PEAKS.json ({peaks['source']}); int8 MMA rate = 2 x bf16",
                 "frac_of_datasheet_4500": round(gemm_tops / DATASHEET_INT8_TOPS, 4),
                 "frac_of_2x_bf16_burst": round(gemm_tops / (2.0 * peaks["bf16_burst"]), 4),

@@ -137,6 +137,16 @@ void b2_set_gemm_config(int config_id);
 /* Name of the tile configuration the last GEMM call on this thread used. */
 const char* b2_last_gemm_config(void);
 
+/* Static-weight declaration (calling thread; default 0).  When non-zero the caller promises that the W operand of
+ * the following GEMM calls is NOT written by the kernel that precedes the GEMM in its stream (inference weights:
+ * loaded once).  Decode-shape GEMMs (M <= 128) are then launched with programmatic dependent launch: their CTAs
+ * start while the preceding kernel (normally this library's quantizer, which releases its dependents at once) is
+ * still running, request their first ring of WEIGHT tiles, and only then wait for that kernel before touching the
+ * activations, the scales or the output.  Results are identical; only the launch overlap changes.  The linear
+ * methods of the host package (weights are module parameters) turn it on around their calls. */
+void b2_set_weight_prefetch(int enabled);
+int b2_get_weight_prefetch(void);
+
 /* Developer hook: when non-NULL, the per-token GEMM kernels write per-CTA wait-cycle counters
  * (8 x uint64 per CTA: MMA-waits-for-operands, MMA-waits-for-accumulator, producer-waits-for-stage,
  * epilogue-waits-for-accumulator, CTA lifetime, 3 reserved) into this device buffer

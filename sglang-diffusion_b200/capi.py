@@ -24,7 +24,7 @@ SYMBOLS = [
     "b2_linear_w8a8_int8_workspace", "b2_linear_w8a8_int8",
     "b2_linear_w8a8_fp8_workspace", "b2_linear_w8a8_fp8",
     "b2_launch_count", "b2_launch_count_reset", "b2_set_gemm_config", "b2_last_gemm_config",
-    "b2_set_profile_buffer",
+    "b2_set_profile_buffer", "b2_set_weight_prefetch", "b2_get_weight_prefetch",
 ]
 
 if not os.path.isfile(LIB_PATH):
@@ -66,6 +66,9 @@ lib.b2_set_gemm_config.restype = None
 lib.b2_last_gemm_config.restype = ctypes.c_char_p
 lib.b2_set_profile_buffer.argtypes = [_vp]
 lib.b2_set_profile_buffer.restype = None
+lib.b2_set_weight_prefetch.argtypes = [_i]
+lib.b2_set_weight_prefetch.restype = None
+lib.b2_get_weight_prefetch.restype = _i
 
 
 class B2Error(RuntimeError):
@@ -103,3 +106,22 @@ def set_gemm_config(config_id: int) -> None:
 
 def last_gemm_config() -> str:
     return lib.b2_last_gemm_config().decode()
+
+
+def set_weight_prefetch(enabled: bool) -> None:
+    """b2_set_weight_prefetch: promise that W operands are static (not written by the preceding kernel), so that
+    decode-shape GEMMs launch programmatically and fetch weights under the tail of the preceding kernel."""
+    lib.b2_set_weight_prefetch(1 if enabled else 0)
+
+
+class static_weights:
+    """`with capi.static_weights(): ...` -- scope of the promise above (restores the previous setting)."""
+
+    def __enter__(self):
+        self._prev = int(lib.b2_get_weight_prefetch())
+        lib.b2_set_weight_prefetch(1)
+        return self
+
+    def __exit__(self, *exc):
+        lib.b2_set_weight_prefetch(self._prev)
+        return False

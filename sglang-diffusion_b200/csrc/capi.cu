@@ -20,9 +20,11 @@ static thread_local int g_forced_config = 0;
 static thread_local const char* g_last_config = "";
 
 static thread_local void* g_prof = nullptr;
+static thread_local int g_weight_prefetch = 0;
 
 void count_launch(int n) { g_launches += static_cast<uint64_t>(n); }
 void* profile_buffer() { return g_prof; }
+bool weight_prefetch_enabled() { return g_weight_prefetch != 0; }
 
 static int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -128,6 +130,8 @@ void b2_launch_count_reset(void) { g_launches = 0; }
 void b2_set_gemm_config(int config_id) { g_forced_config = config_id; }
 const char* b2_last_gemm_config(void) { return g_last_config; }
 void b2_set_profile_buffer(void* device_buffer) { g_prof = device_buffer; }
+void b2_set_weight_prefetch(int enabled) { g_weight_prefetch = enabled; }
+int b2_get_weight_prefetch(void) { return g_weight_prefetch; }
 
 int b2_quant_int8_rows(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s, int M, int K,
                        b2_stream_t stream) {

@@ -479,11 +479,19 @@ static int launch_cfg(const TileConfig& c, const CUtensorMap& ta, const CUtensor
 
 int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** used_config, cudaStream_t st,
                           char* err, size_t err_len);
+int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const char** used_config, cudaStream_t st,
+                       char* err, size_t err_len);
 
 int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const char** used_config,
                 cudaStream_t st, char* err, size_t err_len) {
   if (flavor == GEMM_E4M3_BLOCK128) return gemm_launch_blockwise(a, forced_config, used_config, st, err, err_len);
   const int sms = device_sm_count();
+  // decode shapes (HBM-bound on the weight bytes): cluster split-K kernel of gemm_splitk_sm100.cu
+  // (measured, profiles/r01c_sweep_splitk.log: it wins whenever the activation box is small, and for any M <= 128
+  // when N is too narrow to give the persistent kernel one tile per SM)
+  const bool decode_shape = a.M <= 32 || (a.M <= BM && a.N < 32 * sms);
+  if ((forced_config & 0x40) ? a.M <= BM : ((forced_config & 0xff) == 0 && decode_shape))
+    return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);
   const TileConfig* cfg = &pick_config(a.M, a.N, sms);
   const int forced_debug = forced_config >> 8;  // developer experiments ride in the upper bits of the forced id
   forced_config &= 0xff;

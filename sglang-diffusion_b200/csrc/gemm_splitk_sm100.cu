@@ -1,0 +1,462 @@
+// Decode-shape (M <= 128) W8A8 GEMM for sm_100a: the weight matrix is streamed from HBM exactly once by
+// MANY small CTAs, K split across the CTAs of a thread-block cluster and reduced through distributed
+// shared memory.
+//
+//   D[M,N] = epilogue( A[M,K] x W[N,K]^T ),  M <= 128  -- HBM-bound on the N*K weight bytes
+//
+// Same arithmetic contract as gemm_sm100.cu (int8_scaled_mm / fp8_scaled_mm; reference
+// sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:663-747, fp8_gemm_kernel.cu:1450-1532, epilogue order of
+// sgl-kernel/csrc/cpu/gemm_int8.cpp:20-60).  What differs is the schedule.  The persistent kernel gives one
+// 128 x BN tile with the whole K extent to one SM: at M <= 128 there are fewer tiles than SMs (or a ragged
+// second wave) and each SM has at most a dozen 4-32 KB boxes in flight, a third of what HBM3e needs.  Here
+//
+//   * a work unit is BN weight rows x (K / S) bytes; S CTAs of one cluster (cluster dims {S,1,1}, S <= 8) share a
+//     tile, each running the usual TMA -> tcgen05.mma pipeline over its own K range into its own TMEM;
+//   * only the `a_box_rows` (M rounded up to 8) activation rows are fetched per stage -- the MMA still reads 128
+//     rows of shared memory, the rows past the box are whatever the ring holds and land in TMEM lanes nobody reads;
+//   * units are small (tens of KB) so several CTAs are resident per SM and the block scheduler balances them;
+//   * reduction: every CTA spills its raw 32-bit partial accumulators (rows < M only) to its own shared memory,
+//     one cluster barrier, then CTA r sums columns [r*BN/S, (r+1)*BN/S) over all S peers IN RANK ORDER through
+//     ld.shared::cluster (DSMEM), applies scale / bias / cast and stores to global.  No workspace, no atomics, no
+//     second launch; int32 partial sums are exact so the int8 result is bit-identical to the unsplit kernel, and
+//     the fp32 sums of the fp8 path are deterministic.
+#include <cstdlib>
+
+#include "gemm_common.cuh"
+
+namespace b2 {
+
+struct SplitParams {
+  const float* As;
+  const float* Bs;
+  const void* bias;
+  int bias_dtype;
+  int out_dtype;
+  void* D;
+  long long ldd;  // elements
+  int M, N, K;
+  int num_kb;      // 128-byte K blocks in total
+  int split;       // S = cluster size
+  int stages;
+  int a_box_rows;  // activation rows fetched per stage (multiple of 8, >= M)
+  uint32_t bar_offset;  // byte offset of the barrier block inside the dynamic shared-memory window
+};
+
+B2_DEVICE uint32_t ld_dsmem_u32(uint32_t local_addr, uint32_t cta) {
+  uint32_t v;
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %1, %2;\n\t"
+      "ld.shared::cluster.u32 %0, [ra];\n\t}"
+      : "=r"(v)
+      : "r"(local_addr), "r"(cta)
+      : "memory");
+  return v;
+}
+
+// Programmatic dependent launch: no-ops unless the launch carries cudaLaunchAttributeProgrammaticStreamSerialization
+B2_DEVICE void pdl_wait_prior_grids() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+B2_DEVICE void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+B2_DEVICE uint4 ld_dsmem_v4(uint32_t local_addr, uint32_t cta) {
+  uint4 v;
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %4, %5;\n\t"
+      "ld.shared::cluster.v4.u32 {%0, %1, %2, %3}, [ra];\n\t}"
+      : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+      : "r"(local_addr), "r"(cta)
+      : "memory");
+  return v;
+}
+
+// partial accumulators in shared memory: [row][BN] words, 16-byte chunk index XORed with (row & 7) -- the
+// row-per-lane 16-byte stores of the spill and the chunk-per-lane 16-byte loads of the reduction are both
+// bank-conflict free
+template <int BN>
+B2_DEVICE uint32_t part_offset(int row, int chunk) {
+  return static_cast<uint32_t>(row * BN * 4 + ((chunk ^ (row & 7)) << 4));
+}
+
+template <MmaKind KIND, int BN>
+__global__ void __launch_bounds__(NUM_THREADS)
+    gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                       const SplitParams p) {
+  constexpr uint32_t B_STAGE_BYTES = BN * BK;
+  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  const int stages = p.stages;
+  const uint32_t a_stage_bytes = static_cast<uint32_t>(p.a_box_rows) * BK;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + static_cast<size_t>(stages) * a_stage_bytes;
+  uint32_t* part = reinterpret_cast<uint32_t*>(smem);  // aliases the operand ring once every MMA has retired
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const int S = p.split;
+  const int rank = S > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+  const int tile = static_cast<int>(blockIdx.x) / S;
+  const int kb0 = static_cast<int>(static_cast<long long>(rank) * p.num_kb / S);
+  const int kb1 = static_cast<int>(static_cast<long long>(rank + 1) * p.num_kb / S);
+
+  // dynamic window layout: [ data region (host computes its size) | full[stages] empty[stages] acc_full tmem_ptr ]
+  // -- the barriers live above everything the ring, the MMA's 128-row reads and the partials can touch
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.bar_offset);
+  uint64_t* empty_bar = full_bar + stages;
+  uint64_t* acc_full = empty_bar + stages;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_full + 1);
+  float* smem_as = reinterpret_cast<float*>(smem + p.bar_offset + 512);  // As[0..M) staged by the epilogue warps
+
+  // Warp 0 initialises the barriers and puts the first ring of loads in flight BEFORE the block-wide sync: the
+  // TMEM allocation and the sync are off the critical path of the first HBM round trip.
+  const uint32_t tx_bytes = a_stage_bytes + B_STAGE_BYTES;
+  const int first_pass = min(stages, kb1 - kb0);
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmap_a);
+      tma_prefetch_desc(&tmap_b);
+      for (int i = 0; i < stages; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      mbar_init(acc_full, 1);
+      fence_mbar_init();
+      // The weights are touched exactly once (evict-first) and -- when the caller has declared them static
+      // (b2_set_weight_prefetch) -- are requested before the preceding kernel of the stream has finished; the
+      // activations come from that kernel, so their loads sit behind griddepcontrol.wait.  They are re-read by
+      // every tile: keep them in L2.
+      for (int i = 0; i < first_pass; ++i) {
+        mbar_arrive_expect_tx(&full_bar[i], tx_bytes);
+        tma_load_2d(smem_b + static_cast<size_t>(i) * B_STAGE_BYTES, &tmap_b, &full_bar[i], (kb0 + i) * BK, tile * BN,
+                    kEvictFirst);
+      }
+      pdl_wait_prior_grids();
+      for (int i = 0; i < first_pass; ++i)
+        tma_load_2d(smem_a + static_cast<size_t>(i) * a_stage_bytes, &tmap_a, &full_bar[i], (kb0 + i) * BK, 0,
+                    kEvictLast);
+      pdl_launch_dependents();
+    }
+    __syncwarp();
+  }
+  if (warp == 1) tmem_alloc<1>(tmem_ptr, TMEM_COLS);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ========================================== TMA producer (ring reuse) ====
+    int stage = 0;
+    uint32_t phase = 1;  // the first pass over the ring is already in flight
+    for (int kb = kb0 + first_pass; kb < kb1; ++kb) {
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+        tma_load_2d(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES, &tmap_b, &full_bar[stage], kb * BK,
+                    tile * BN, kEvictFirst);
+        tma_load_2d(smem_a + static_cast<size_t>(stage) * a_stage_bytes, &tmap_a, &full_bar[stage], kb * BK, 0,
+                    kEvictLast);
+      }
+      __syncwarp();
+      if (++stage == stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================================= MMA issuer ====
+    constexpr uint32_t idesc = make_idesc<KIND>(BM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after_sync();
+      const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * a_stage_bytes));
+      const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
+      if (elect_one()) {
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k)
+          umma<KIND, 1>(tmem_base, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
+                        db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, (kb > kb0 || k != 0) ? 1u : 0u);
+        umma_commit(&empty_bar[stage]);
+      }
+      __syncwarp();
+      if (++stage == stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+    if (elect_one()) umma_commit(acc_full);
+    __syncwarp();
+  } else {
+    // ============================== accumulators: TMEM -> own shared memory ====
+    const int quarter = warp & 3;
+    pdl_wait_prior_grids();  // As below and D at the end belong to / may still be read by the preceding kernels
+    {
+      const int t = (warp - EPI_WARP0) * 32 + lane;
+      if (t < p.M && p.As != nullptr) smem_as[t] = __ldg(p.As + t);
+    }
+    if (quarter * 32 < p.a_box_rows) {
+      mbar_wait(acc_full, 0);
+      tc_fence_after_sync();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+      const int row = quarter * 32 + lane;
+      uint8_t* part_bytes = reinterpret_cast<uint8_t*>(part);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(t_row + static_cast<uint32_t>(c * 32), r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(part_bytes + part_offset<BN>(row, c * 8 + j)) =
+              make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+      }
+    }
+  }
+
+  // every CTA's partials are in its shared memory and visible cluster-wide after this barrier
+  tc_fence_before_sync();
+  __syncwarp();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc<1>(tmem_base, TMEM_COLS);
+  }
+
+  if (warp >= EPI_WARP0) {
+    // ===================== reduce my column slice over the cluster, epilogue ====
+    // work item = (row, group of 4 columns); consecutive threads take consecutive groups of one row, so the DSMEM
+    // loads are conflict free and the global stores of a warp cover whole contiguous row segments
+    const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
+    const int cols_per = (((BN + S - 1) / S) + 3) & ~3;
+    const int c0 = rank * cols_per;
+    const int width = min(cols_per, BN - c0);
+    const int gpr = width > 0 ? width >> 2 : 0;  // groups per row
+    const bool has_bias = p.bias != nullptr;
+    const bool raw_out = (KIND == MmaKind::I8) && p.out_dtype == B2_DTYPE_S32;
+    const uint32_t part_base = smem_u32(part);
+    const int items = p.M * gpr;
+    const bool fixed_group = gpr > 0 && (128 % gpr) == 0;  // then a thread keeps its column group for every row
+    float bs[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {-0.f, -0.f, -0.f, -0.f};
+    int cached_col = -1;
+    for (int idx = epi_tid; idx < items; idx += 128) {
+      const int row = idx / gpr;
+      const int g = idx - row * gpr;
+      const int c = c0 + g * 4;
+      const int col = tile * BN + c;
+      if (col >= p.N) continue;  // N % 8 == 0: a group of 4 columns is inside or outside as a whole
+      const uint32_t addr = part_base + part_offset<BN>(row, c >> 2);
+      uint4 acc = ld_dsmem_v4(addr, 0);
+      for (int pr = 1; pr < S; ++pr) {
+        const uint4 o = ld_dsmem_v4(addr, pr);
+        if constexpr (KIND == MmaKind::I8) {
+          acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;  // two's complement: exact int32 sums
+        } else {
+          acc.x = __float_as_uint(__fadd_rn(__uint_as_float(acc.x), __uint_as_float(o.x)));
+          acc.y = __float_as_uint(__fadd_rn(__uint_as_float(acc.y), __uint_as_float(o.y)));
+          acc.z = __float_as_uint(__fadd_rn(__uint_as_float(acc.z), __uint_as_float(o.z)));
+          acc.w = __float_as_uint(__fadd_rn(__uint_as_float(acc.w), __uint_as_float(o.w)));
+        }
+      }
+      const size_t o = static_cast<size_t>(row) * static_cast<size_t>(p.ldd) + static_cast<size_t>(col);
+      if (raw_out) {
+        *reinterpret_cast<uint4*>(static_cast<uint32_t*>(p.D) + o) = acc;
+        continue;
+      }
+      if (!fixed_group || cached_col != col) {
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.Bs + col));
+        bs[0] = b4.x; bs[1] = b4.y; bs[2] = b4.z; bs[3] = b4.w;
+        if (has_bias) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bi[j] = load_bias(p.bias, p.bias_dtype, col + j);
+        }
+        cached_col = col;
+      }
+      const float as = smem_as[row];
+      const uint32_t a4[4] = {acc.x, acc.y, acc.z, acc.w};
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = epilogue_value<KIND>(a4[j], as, bs[j], bi[j]);
+      if (p.out_dtype == B2_DTYPE_F32) {
+        *reinterpret_cast<float4*>(static_cast<float*>(p.D) + o) = make_float4(v[0], v[1], v[2], v[3]);
+      } else {
+        uint2 w;
+        w.x = pack16(v[0], v[1], p.out_dtype);
+        w.y = pack16(v[2], v[3], p.out_dtype);
+        *reinterpret_cast<uint2*>(static_cast<uint16_t*>(p.D) + o) = w;
+      }
+    }
+  }
+  // nobody leaves while a peer may still be reading its partials
+  __syncwarp();
+  cluster_sync_all();
+}
+
+// ------------------------------------------------------------------ host ----
+
+static const int kSplitBN[4] = {32, 64, 128, 256};
+
+struct SplitPlan {
+  int bn_idx, split, stages;
+  size_t smem;
+  double cost;
+};
+
+static size_t splitk_smem(int bn, int a_rows, int stages) {
+  const size_t a_stage = static_cast<size_t>(a_rows) * BK, b_stage = static_cast<size_t>(bn) * BK;
+  size_t data = stages * (a_stage + b_stage);
+  const size_t mma_reach = stages * a_stage + static_cast<size_t>(BM) * BK;  // 128-row reads of the last A stage
+  if (mma_reach > data) data = mma_reach;
+  const size_t rows_p = static_cast<size_t>((a_rows + 31) / 32) * 32;
+  const size_t partial = rows_p * bn * 4;
+  if (partial > data) data = partial;
+  data = (data + 1023) / 1024 * 1024;
+  return data + 1024;  // 512 B of barriers + TMEM pointer (2 * 24 + 2 slots of 8 bytes max), 512 B of staged As
+}
+
+// Schedule heuristic, fitted to tools/perf_sweep.py splitk --all (profiles/r01c_sweep_splitk.log):
+//   * tile width 128 while the activation box is small (<= 32 rows), 64 above (the 16 KB activation stage then
+//     dominates the ring);
+//   * the smallest power-of-two split that puts >= ~0.85 x #SMs CTAs in the grid with >= 4 K-blocks each;
+//   * the deepest ring (<= 12 stages) that still lets EVERY CTA of the grid be resident at once -- one wave, the
+//     block scheduler balances SMs that hold 1 vs 2 CTAs -- and 4 stages when the grid needs more than 3 per SM.
+static SplitPlan plan_splitk(int M, int N, int K, int a_rows, int sms) {
+  (void)M;
+  const int num_kb = (K + BK - 1) / BK;
+  const int bi = a_rows <= 32 ? 2 : 1;
+  const int bn = kSplitBN[bi];
+  const int tiles = (N + bn - 1) / bn;
+  int s = 1;
+  while (s < 8 && tiles * s < (sms * 85) / 100 && num_kb / (2 * s) >= 4) s *= 2;
+  const int kb_per = (num_kb + s - 1) / s;
+  const long ctas = static_cast<long>(tiles) * s;
+  const int need_occ = static_cast<int>((ctas + sms - 1) / sms);
+  int stages = 4;
+  if (need_occ <= 3) {
+    const size_t budget = (228u * 1024u) / need_occ - 1024u;
+    stages = 12;
+    while (stages > 2 && splitk_smem(bn, a_rows, stages) > budget) --stages;
+  }
+  if (stages > kb_per) stages = kb_per;
+  while (stages > 1 && splitk_smem(bn, a_rows, stages) > static_cast<size_t>(SMEM_LIMIT)) --stages;
+  return SplitPlan{bi, s, stages, splitk_smem(bn, a_rows, stages), 0.0};
+}
+
+template <MmaKind KIND, int BN>
+static int launch_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const SplitParams& p, int grid, size_t smem,
+                         bool pdl, cudaStream_t st, char* err, size_t err_len) {
+  auto kern = gemm_splitk_kernel<KIND, BN>;
+  static int attr_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr_dev != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+    if (e != cudaSuccess) {
+      snprintf(err, err_len, "cudaFuncSetAttribute(max dynamic smem): %s", cudaGetErrorString(e));
+      return B2_ERR_CUDA;
+    }
+    attr_dev = dev;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[2];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = static_cast<unsigned>(p.split);
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = pdl ? 2 : 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+  if (e != cudaSuccess) {
+    snprintf(err, err_len, "split-K gemm kernel launch (cluster %d, smem %zu): %s", p.split, smem,
+             cudaGetErrorString(e));
+    return B2_ERR_CUDA;
+  }
+  count_launch();
+  return B2_OK;
+}
+
+// forced: 0 = plan; otherwise 0x40 | bn_idx << 3 | (S - 1), optionally | ring depth cap << 8
+int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const char** used_config, cudaStream_t st,
+                       char* err, size_t err_len) {
+  const int sms = device_sm_count();
+  const int a_rows = ((a.M + 7) / 8) * 8;
+  SplitPlan plan = plan_splitk(a.M, a.N, a.K, a_rows, sms);
+  const int num_kb = (a.K + BK - 1) / BK;
+  if (forced & 0x40) {
+    plan.bn_idx = (forced >> 3) & 3;
+    plan.split = (forced & 7) + 1;
+    if (plan.split > num_kb) plan.split = num_kb;
+    const int bn = kSplitBN[plan.bn_idx];
+    const int kb_per = (num_kb + plan.split - 1) / plan.split;
+    int stages = kb_per < 24 ? kb_per : 24;
+    while (stages > 1 && splitk_smem(bn, a_rows, stages) > static_cast<size_t>(SMEM_LIMIT)) --stages;
+    const int forced_stages = (forced >> 8) & 31;  // developer sweeps: ring depth cap in bits 8-12
+    if (forced_stages >= 1 && forced_stages < stages) stages = forced_stages;
+    plan.stages = stages;
+    plan.smem = splitk_smem(bn, a_rows, stages);
+  }
+  const int bn = kSplitBN[plan.bn_idx];
+  if (plan.smem > static_cast<size_t>(SMEM_LIMIT)) {
+    snprintf(err, err_len, "split-K plan does not fit shared memory (bn=%d rows=%d)", bn, a_rows);
+    return B2_ERR_ARG;
+  }
+  static thread_local char name[48];
+  snprintf(name, sizeof(name), "splitk_%dx%d_s%d_st%d", a_rows, bn, plan.split, plan.stages);
+  if (used_config) *used_config = name;
+
+  SplitParams p;
+  p.As = a.As;
+  p.Bs = a.Bs;
+  p.bias = a.bias;
+  p.bias_dtype = a.bias_dtype;
+  p.out_dtype = a.out_dtype;
+  p.D = a.D;
+  p.ldd = a.ldd;
+  p.M = a.M;
+  p.N = a.N;
+  p.K = a.K;
+  p.num_kb = num_kb;
+  p.split = plan.split;
+  p.stages = plan.stages;
+  p.a_box_rows = a_rows;
+  p.bar_offset = static_cast<uint32_t>(plan.smem - 1024);
+
+  CUtensorMap ta, tb;
+  if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, a_rows, BK) ||
+      !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, bn, BK)) {
+    snprintf(err, err_len, "cuTensorMapEncodeTiled failed (M=%d N=%d K=%d lda=%lld ldw=%lld)", a.M, a.N, a.K,
+             (long long)a.lda, (long long)a.ldw);
+    return B2_ERR_CUDA;
+  }
+  const int tiles = (a.N + bn - 1) / bn;
+  const int grid = tiles * plan.split;
+#define B2_SPLITK_CASE(KIND_, BN_) \
+  return launch_splitk<KIND_, BN_>(ta, tb, p, grid, plan.smem, weight_prefetch_enabled(), st, err, err_len)
+  if (flavor == GEMM_S8) {
+    switch (bn) {
+      case 32: B2_SPLITK_CASE(MmaKind::I8, 32);
+      case 64: B2_SPLITK_CASE(MmaKind::I8, 64);
+      case 128: B2_SPLITK_CASE(MmaKind::I8, 128);
+      default: B2_SPLITK_CASE(MmaKind::I8, 256);
+    }
+  }
+  switch (bn) {
+    case 32: B2_SPLITK_CASE(MmaKind::F8, 32);
+    case 64: B2_SPLITK_CASE(MmaKind::F8, 64);
+    case 128: B2_SPLITK_CASE(MmaKind::F8, 128);
+    default: B2_SPLITK_CASE(MmaKind::F8, 256);
+  }
+#undef B2_SPLITK_CASE
+}
+
+}  // namespace b2

@@ -110,6 +110,11 @@ __global__ void __launch_bounds__(BLOCK) quant_rows_kernel(const T* __restrict__
   constexpr int WARPS_PER_ROW = (TPR + 31) / 32;
   __shared__ float s_red[ROWS][WARPS_PER_ROW > 1 ? WARPS_PER_ROW : 1];
 
+  // Release programmatically-launched dependents at once (a no-op for ordinary successors): the decode GEMM that
+  // follows starts fetching its weights while these rows are quantized, and waits for this grid's completion
+  // (griddepcontrol.wait) before it reads the codes or the scales.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
   const int r_in_cta = threadIdx.x / TPR;
   const int t = threadIdx.x % TPR;
   const int row = blockIdx.x * ROWS + r_in_cta;

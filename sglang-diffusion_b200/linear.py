@@ -22,7 +22,7 @@ from typing import List, Optional
 import torch
 import torch.distributed as dist
 
-from . import ops
+from . import capi, ops
 
 
 # --------------------------------------------------------------- int8 W8A8 ----
@@ -50,17 +50,20 @@ class W8A8Int8LinearMethod:
         layer.weight_scale = torch.nn.Parameter(layer.weight_scale.data, requires_grad=False)
 
     def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None):
-        if self.fused:
-            x2d = x.view(-1, x.shape[-1])
-            out = ops.int8_scaled_mm_with_quant(x2d, layer.weight.t(), layer.weight_scale, bias, x.dtype, False)
-            return out.view(*x.shape[:-1], layer.weight.shape[1])
-        x_q, x_scale = ops.per_token_quant_int8(x)
-        x_q_2d = x_q.view(-1, x_q.shape[-1])
-        x_scale_2d = x_scale.view(-1, x_scale.shape[-1])
-        output_shape = [*x_q.shape[:-1], layer.weight.shape[1]]
-        output = ops.int8_scaled_mm(x_q_2d, layer.weight, x_scale_2d, layer.weight_scale, out_dtype=x.dtype,
-                                    bias=bias)
-        return output.view(output_shape)
+        # layer.weight is a loaded parameter, never the output of the kernel before the GEMM: decode-shape GEMMs
+        # may fetch it under the quantizer's tail (b2_set_weight_prefetch, include/b200_w8a8.h)
+        with capi.static_weights():
+            if self.fused:
+                x2d = x.view(-1, x.shape[-1])
+                out = ops.int8_scaled_mm_with_quant(x2d, layer.weight.t(), layer.weight_scale, bias, x.dtype, False)
+                return out.view(*x.shape[:-1], layer.weight.shape[1])
+            x_q, x_scale = ops.per_token_quant_int8(x)
+            x_q_2d = x_q.view(-1, x_q.shape[-1])
+            x_scale_2d = x_scale.view(-1, x_scale.shape[-1])
+            output_shape = [*x_q.shape[:-1], layer.weight.shape[1]]
+            output = ops.int8_scaled_mm(x_q_2d, layer.weight, x_scale_2d, layer.weight_scale, out_dtype=x.dtype,
+                                        bias=bias)
+            return output.view(output_shape)
 
 
 # ---------------------------------------------------------------- fp8 W8A8 ----
@@ -96,7 +99,8 @@ class W8A8Fp8LinearMethod:
         layer.weight_scale = torch.nn.Parameter(layer.weight_scale.data, requires_grad=False)
 
     def apply(self, layer, x: torch.Tensor, bias: Optional[torch.Tensor] = None):
-        return apply_fp8_linear(x, layer.weight, layer.weight_scale, bias=bias)
+        with capi.static_weights():  # see W8A8Int8LinearMethod.apply
+            return apply_fp8_linear(x, layer.weight, layer.weight_scale, bias=bias)
 
 
 def cutlass_w8a8_block_fp8_linear_with_fallback(input: torch.Tensor, weight: torch.Tensor, block_size: List[int],

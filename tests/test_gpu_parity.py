@@ -133,6 +133,84 @@ def test_gemm_s8_raw_accumulators_exact_every_tile_config(cfg, M, N, K):
     assert torch.equal(D, exact_acc(A, W))
 
 
+def splitk_cfg(bn_idx: int, split: int) -> int:
+    """forced id of the decode kernel (gemm_splitk_sm100.cu): 0x40 | bn_idx << 3 | (S - 1); bn = 32 << bn_idx"""
+    return 0x40 | (bn_idx << 3) | (split - 1)
+
+
+@pytest.mark.parametrize("bn_idx", [0, 1, 2, 3])
+@pytest.mark.parametrize("split", [1, 2, 3, 4, 5, 8])
+@pytest.mark.parametrize("M,N,K", [(1, 264, 2048), (16, 1000, 4096), (33, 384, 1168), (100, 520, 1024), (128, 256, 8192)])
+def test_gemm_s8_splitk_cluster_accumulators_exact(bn_idx, split, M, N, K):
+    """Decode kernel: every tile width x cluster size, K tails (1168 = 9.125 stages), N tails, M up to 128.
+    int32 partial sums over the cluster are exact, so the result equals the unsplit dot bit for bit."""
+    g = torch.Generator().manual_seed(M * 7 + N * 3 + K + bn_idx * 11 + split)
+    A = torch.randint(-128, 128, (M, K), dtype=torch.int8, generator=g).to(DEV)
+    W = torch.randint(-128, 128, (N, K), dtype=torch.int8, generator=g).to(DEV)
+    D = c_gemm_s8(A, W, None, None, None, torch.int32, splitk_cfg(bn_idx, split))
+    assert capi.last_gemm_config().startswith("splitk_")
+    assert torch.equal(D, exact_acc(A, W))
+
+
+@pytest.mark.parametrize("M", [1, 16, 64, 128])
+@pytest.mark.parametrize("K,N", [(4096, 6144), (4096, 28672), (14336, 4096)])
+def test_decode_shapes_auto_plan_bitwise_vs_persistent_kernel(M, K, N):
+    """BASELINE C2 decode shapes: the planned split-K launch equals the persistent kernel (forced config 1) bit for
+    bit, bias and scales included."""
+    x, W, Bs, bias = mk_int8_problem(M, N, K, seed=M + N)
+    x, W, Bs, bias = x.to(DEV), W.to(DEV), Bs.to(DEV), bias.to(DEV)
+    q, s = c_quant_int8(x)
+    a = c_gemm_s8(q, W, s, Bs, bias)
+    assert capi.last_gemm_config().startswith("splitk_") == (M <= 32 or N < 32 * 148)
+    if not capi.last_gemm_config().startswith("splitk_"):
+        a = c_gemm_s8(q, W, s, Bs, bias, cfg=splitk_cfg(1, 2))
+    b = c_gemm_s8(q, W, s, Bs, bias, cfg=1)
+    assert capi.last_gemm_config() == "1cta_128x32"
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_static_weight_prefetch_chain_is_bit_identical(graph):
+    """b2_set_weight_prefetch: quantizer -> decode GEMM launched programmatically (weights requested under the
+    quantizer's tail, activations behind griddepcontrol.wait), 24 layers back to back, eager and graph-replayed:
+    the outputs equal the plainly-launched chain bit for bit."""
+    M, K, N = 16, 4096, 6144
+    layers = []
+    for i in range(6):
+        x, W, Bs, bias = mk_int8_problem(M, N, K, seed=100 + i)
+        layers.append((x.to(DEV), W.to(DEV), Bs.to(DEV), bias.to(DEV)))
+
+    def chain():
+        outs = []
+        for rep in range(4):
+            for x, W, Bs, bias in layers:
+                q, s = b2.per_token_quant_int8(x)
+                outs.append(b2.int8_scaled_mm(q, W.t(), s, Bs.view(-1, 1), torch.bfloat16, bias))
+        return outs
+
+    want = chain()
+    torch.cuda.synchronize()
+    with capi.static_weights():
+        assert capi.lib.b2_get_weight_prefetch() == 1
+        if graph:
+            st = torch.cuda.Stream()
+            st.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(st):
+                chain()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=st):
+                    got = chain()
+            torch.cuda.current_stream().wait_stream(st)
+            for _ in range(3):
+                g.replay()
+        else:
+            got = chain()
+    assert capi.lib.b2_get_weight_prefetch() == 0
+    torch.cuda.synchronize()
+    for a, b in zip(want, got):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+
+
 def test_gemm_s8_extreme_codes_do_not_saturate():
     """K = 16384 of (-128)*(-128) = 2.7e8 < 2^31: the accumulator must be exact, not saturated."""
     M, N, K = 130, 136, 16384
@@ -353,6 +431,30 @@ def test_fp8_scaled_mm_vs_restatement(M, N, K, has_bias):
     assert ((o - ref).abs().max() / ref.abs().max()).item() < 1e-2
     assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 1e-6 * ref.abs().max())
     assert (o == ref.bfloat16().float()).float().mean().item() > 0.99
+
+
+@pytest.mark.parametrize("bn_idx,split", [(0, 1), (0, 8), (1, 3), (2, 4), (3, 2), (3, 7)])
+@pytest.mark.parametrize("M", [1, 64, 128])
+def test_fp8_splitk_cluster_vs_restatement(bn_idx, split, M):
+    """fp8 decode kernel: fp32 partials summed in rank order; within the reference tolerance and deterministic."""
+    N, K = 1288, 3584
+    g = torch.Generator(device=DEV).manual_seed(bn_idx * 8 + split + M)
+    a = (torch.randn(M, K, generator=g, device=DEV)).clamp(-448, 448).to(torch.float8_e4m3fn)
+    b = (torch.randn(N, K, generator=g, device=DEV)).clamp(-448, 448).to(torch.float8_e4m3fn)
+    sa = torch.rand(M, generator=g, device=DEV) * 1e-2 + 1e-3
+    sb = torch.rand(N, generator=g, device=DEV) * 1e-2 + 1e-3
+    bias = torch.randn(N, generator=g, device=DEV).bfloat16()
+    outs = []
+    for _ in range(2):
+        capi.set_gemm_config(splitk_cfg(bn_idx, split))
+        try:
+            outs.append(b2.fp8_scaled_mm(a, b.t(), sa.view(-1, 1), sb.view(-1, 1), torch.bfloat16, bias))
+            assert capi.last_gemm_config().startswith("splitk_")
+        finally:
+            capi.set_gemm_config(0)
+    assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))
+    o = (a.double() @ b.double().t()) * sa.double()[:, None] * sb.double()[None, :] + bias.double()
+    torch.testing.assert_close(outs[0].double(), o, rtol=1e-2, atol=1e-2 * o.abs().max().item())
 
 
 @pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5, 6])

@@ -32,6 +32,8 @@ TENSOR = 2.0 * PK.get("bf16_tflops", 1590.0)
 L2_BYTES = 160e6
 
 
+PDL = "--pdl" in sys.argv  # declare the weights static: decode GEMMs launch programmatically (b2_set_weight_prefetch)
+b2.capi.set_weight_prefetch(PDL)
 GRAPH = "--graph" in sys.argv  # replay the launches from a CUDA graph: kernel time without the Python/dispatcher cost
 
 
@@ -84,7 +86,7 @@ def line(name, M, N, K, t, ops, byts, cfg=""):
           f"{gbs:8.1f} GB/s ({100*gbs/HBM:5.1f}% of {HBM:.0f})  {cfg}", flush=True)
 
 
-def gemm_int8(M, N, K, bias=False):
+def gemm_int8(M, N, K, bias=False, cfg=0):
     nset = copies_for(N * K + M * K + 2 * M * N)
     sets = []
     for _ in range(nset):
@@ -95,7 +97,11 @@ def gemm_int8(M, N, K, bias=False):
     Bs = torch.rand(N, 1, device=dev) * 1e-2
     b = torch.randn(N, device=dev).bfloat16() if bias else None
     fns = [(lambda A=A, W=W: b2.int8_scaled_mm(A, W.t(), As, Bs, torch.bfloat16, b)) for A, W in sets]
-    t = timed(fns)
+    b2.capi.set_gemm_config(cfg)
+    try:
+        t = timed(fns)
+    finally:
+        b2.capi.set_gemm_config(0)
     line("int8_scaled_mm", M, N, K, t, 2.0 * M * N * K, M * K + N * K + 2 * M * N + 4 * M + 4 * N, b2.capi.last_gemm_config())
 
 
@@ -145,6 +151,7 @@ def quant(kind, M, K):
 
 
 def linear_int8(M, N, K):
+    # quantizer + GEMM per call, as W8A8Int8LinearMethod.apply issues them
     nset = copies_for(N * K + 2 * M * K + 2 * M * N)
     sets = []
     for _ in range(nset):
@@ -157,6 +164,22 @@ def linear_int8(M, N, K):
     line("int8 linear (q+mm)", M, N, K, t, 2.0 * M * N * K, 2 * M * K + N * K + 2 * M * N + 4 * N)
 
 
+if "splitk" in want:
+    # decode kernel (gemm_splitk_sm100.cu): the planner's pick, then every forced (BN, S), per C2 decode shape
+    for K, N in ((4096, 6144), (4096, 28672), (14336, 4096), (8192, 1280), (1024, 8192)):
+        for M in ((16, 128) if not QUICK else (16,)):
+            print(f"# M={M} N={N} K={K}")
+            gemm_int8(M, N, K)
+            gemm_int8(M, N, K, cfg=1 if N <= 6144 else 4)
+            if "--all" in sys.argv:
+                for bn_idx in range(4):
+                    for S in (1, 2, 4, 8):
+                        for cap in (4, 8, 16):
+                            kb_per = -(-(K // 128) // S)
+                            if cap > 4 and cap // 2 >= kb_per:
+                                continue  # same launch as the previous cap
+                            gemm_int8(M, N, K, cfg=0x40 | (bn_idx << 3) | (S - 1) | (cap << 8))
+    sys.exit(0)
 if "int8" in want:
     print("# C1 + C2: Llama-3-8B int8 shapes"); gemm_int8(128, 4096, 4096, bias=True)
     Ms = [1, 16, 64, 256, 1024, 4096, 8192] if not QUICK else [16, 8192]

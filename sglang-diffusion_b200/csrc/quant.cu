@@ -20,6 +20,8 @@
 #include <cuda_fp16.h>
 #include <cuda_fp8.h>
 
+#include <cstdlib>
+
 #include "b200_w8a8_internal.h"
 #include "ptx.cuh"
 
@@ -180,8 +182,20 @@ __global__ void __launch_bounds__(BLOCK) quant_rows_kernel(const T* __restrict__
       const T* e = reinterpret_cast<const T*>(&cache[i]);
       QV out;
       uint8_t* o = reinterpret_cast<uint8_t*>(&out);
+      if constexpr (MODE == QMode::FP8 && VEC % 2 == 0) {
+        // paired conversion: one cvt.rn.satfinite.e4m3x2 per two elements (the clamp keeps the reference's
+        // fminf/fmaxf semantics for non-finite inputs)
+        uint16_t* o2 = reinterpret_cast<uint16_t*>(&out);
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) o[j] = quant_one<MODE>(to_f32(e[j]), inv);
+        for (int j = 0; j < VEC; j += 2) {
+          const float a = fmaxf(fminf(__fmul_rn(to_f32(e[j]), inv), 448.f), -448.f);
+          const float b = fmaxf(fminf(__fmul_rn(to_f32(e[j + 1]), inv), 448.f), -448.f);
+          o2[j >> 1] = f32x2_to_e4m3x2(a, b);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) o[j] = quant_one<MODE>(to_f32(e[j]), inv);
+      }
       qr[v] = out;
     }
   }
@@ -256,65 +270,134 @@ cudaError_t quant_rows_fp8(const void* x, int x_dtype, int64_t ldx, uint8_t* q, 
 }
 
 // ------------------------------------------------------------ 1xG groups ----
-// G = 128: one group = 16 threads x 8 elements (one 16-byte load each).  A warp
-// covers two groups; amax is reduced with 4 xor-shuffles inside each half-warp.
-// Grid-stride over (row, group) pairs so the grid is sized to the machine.
+// G = 128: one group = 16 threads x 8 elements (one 16-byte load each).  A CTA covers a tile of 16 rows x 4
+// adjacent groups (four independent 16-byte loads in flight per thread); amax is reduced with 4 xor-shuffles
+// inside each half-warp.  The reference divides every element by the group scale
+// (per_token_group_quant_8bit.cu:110); eight IEEE divisions per thread made the first version of this kernel
+// ALU-bound (44 % of HBM).  Here the correctly rounded reciprocal r = RN(1/ys) is computed once and each
+// quotient is q0 = RN(x r), q = RN(q0 + r (x - q0 ys)) -- Markstein's sequence, which returns RN(x / ys) whenever
+// the significand of ys is not all ones (that case, group-uniform, takes the division).  tests/test_gpu_parity.py
+// checks every (bf16 x significand, bf16 amax significand, exponent gap) combination against the oracle.
+// Scales are staged in shared memory so that the M-major (column-major) scale matrix the block-wise GEMM wants is
+// written as 64-byte runs of 16 consecutive rows instead of one 4-byte store per sector.
 template <typename T>
+B2_DEVICE float group128_quantize(const uint4& v, float eps, float fmin, float fmax, uint2& out) {
+  const T* e = reinterpret_cast<const T*>(&v);
+  float f[8];
+  float amax = eps;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    f[j] = to_f32(e[j]);
+    amax = fmaxf(amax, fabsf(f[j]));
+  }
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  const float ys = __fdiv_rn(amax, fmax);
+  const float r = __frcp_rn(ys);
+  float qv[8];
+  // ONE group-uniform branch (not one per element): the all-ones significand is the only case the reciprocal
+  // sequence does not cover
+  if ((__float_as_uint(ys) & 0x7fffffu) != 0x7fffffu) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float q0 = __fmul_rn(f[j], r);
+      qv[j] = __fmaf_rn(__fmaf_rn(-q0, ys, f[j]), r, q0);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) qv[j] = __fdiv_rn(f[j], ys);
+  }
+  // reference: fmaxf(fmin, fminf(q, fmax)) then a saturating cast.  The upper fminf also maps NaN to fmax as the
+  // reference does; the lower bound is what cvt.satfinite does by itself when fmin is the format's own minimum.
+  const bool lower = fmin > -448.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    qv[j] = fminf(qv[j], fmax);
+    if (lower) qv[j] = fmaxf(qv[j], fmin);
+  }
+  out.x = static_cast<uint32_t>(f32x2_to_e4m3x2(qv[0], qv[1])) | (static_cast<uint32_t>(f32x2_to_e4m3x2(qv[2], qv[3])) << 16);
+  out.y = static_cast<uint32_t>(f32x2_to_e4m3x2(qv[4], qv[5])) | (static_cast<uint32_t>(f32x2_to_e4m3x2(qv[6], qv[7])) << 16);
+  return ys;
+}
+
+// GQ_GROUPS adjacent groups per CTA tile = independent 16-byte loads in flight per thread
+template <typename T, int GQ_GROUPS>
 __global__ void __launch_bounds__(256) quant_group128_kernel(const T* __restrict__ x, int64_t ldx,
                                                              uint8_t* __restrict__ q, int64_t ldq,
                                                              float* __restrict__ s, int64_t s_row_stride,
                                                              int64_t s_grp_stride, int M, int groups_per_row,
                                                              float eps, float fmin, float fmax) {
-  const int64_t total = static_cast<int64_t>(M) * groups_per_row;
+  // one CTA = one tile of 16 rows x GQ_GROUPS groups; the grid covers every tile (no grid-stride loop: with eight
+  // CTAs resident per SM the block scheduler keeps ~128 KB of loads in flight per SM without software pipelining)
+  __shared__ float s_scale[GQ_GROUPS][16];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // see quant_rows_kernel
   const int sub = threadIdx.x & 15;
-  for (int64_t g = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 4; g < ((total + 1) & ~1ll);
-       g += (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 4) {
-    const bool active = g < total;
-    const int64_t row = active ? g / groups_per_row : 0;
-    const int grp = active ? static_cast<int>(g % groups_per_row) : 0;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (active) v = ld_stream(reinterpret_cast<const uint4*>(x + row * ldx + grp * 128) + sub);
-    const T* e = reinterpret_cast<const T*>(&v);
-    float f[8];
-    float amax = eps;
+  const int r_in = threadIdx.x >> 4;
+  const int gtiles = (groups_per_row + GQ_GROUPS - 1) / GQ_GROUPS;
+  const int64_t t = blockIdx.x;
+  const int64_t rb = t / gtiles;
+  const int g0 = static_cast<int>(t - rb * gtiles) * GQ_GROUPS;
+  const int64_t row = rb * 16 + r_in;
+  const T* xr = x + row * ldx + static_cast<int64_t>(g0) * 128;
+  uint4 v[GQ_GROUPS];
+  bool act[GQ_GROUPS];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      f[j] = to_f32(e[j]);
-      amax = fmaxf(amax, fabsf(f[j]));
-    }
-#pragma unroll
-    for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-    const float ys = __fdiv_rn(amax, fmax);
-    if (active) {
-      uint2 out;
-      uint8_t* o8 = reinterpret_cast<uint8_t*>(&out);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float qv = fminf(fmaxf(__fdiv_rn(f[j], ys), fmin), fmax);
-        o8[j] = f32_to_e4m3_sat(qv);
-      }
-      reinterpret_cast<uint2*>(q + row * ldq + grp * 128)[sub] = out;
-      if (sub == 0) s[row * s_row_stride + grp * s_grp_stride] = ys;
-    }
+  for (int i = 0; i < GQ_GROUPS; ++i) {
+    act[i] = row < M && (g0 + i) < groups_per_row;
+    v[i] = make_uint4(0, 0, 0, 0);
+    if (act[i]) v[i] = ld_stream(reinterpret_cast<const uint4*>(xr + i * 128) + sub);
   }
+  uint8_t* qr = q + row * ldq + static_cast<int64_t>(g0) * 128;
+#pragma unroll
+  for (int i = 0; i < GQ_GROUPS; ++i) {
+    uint2 o;
+    const float ys = group128_quantize<T>(v[i], eps, fmin, fmax, o);
+    if (act[i]) reinterpret_cast<uint2*>(qr + i * 128)[sub] = o;
+    if (sub == 0) s_scale[i][r_in] = ys;
+  }
+  __syncthreads();
+  if (threadIdx.x < 16 * GQ_GROUPS) {
+    const int gi = threadIdx.x >> 4, rr = threadIdx.x & 15;
+    const int64_t row2 = rb * 16 + rr;
+    if (row2 < M && g0 + gi < groups_per_row)
+      s[row2 * s_row_stride + static_cast<int64_t>(g0 + gi) * s_grp_stride] = s_scale[gi][rr];
+  }
+}
+
+template <typename T, int GQ>
+static cudaError_t launch_group128(const void* x, int64_t ldx, uint8_t* q, int64_t ldq, float* s, int64_t s_row_stride,
+                                   int64_t s_grp_stride, int M, int gpr, float eps, float fmin, float fmax,
+                                   cudaStream_t st) {
+  const int64_t blocks = static_cast<int64_t>((M + 15) / 16) * ((gpr + GQ - 1) / GQ);
+  if (blocks > 0x7fffffffll) return cudaErrorInvalidValue;
+  quant_group128_kernel<T, GQ><<<static_cast<int>(blocks), 256, 0, st>>>(static_cast<const T*>(x), ldx, q, ldq, s,
+                                                                         s_row_stride, s_grp_stride, M, gpr, eps,
+                                                                         fmin, fmax);
+  return cudaGetLastError();
 }
 
 cudaError_t quant_fp8_group128(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s,
                                int64_t s_row_stride, int64_t s_grp_stride, int M, int K, float eps, float fmin,
                                float fmax, cudaStream_t st) {
   const int gpr = K / 128;
-  const int64_t total = static_cast<int64_t>(M) * gpr;
-  if (total == 0) return cudaSuccess;
-  const int64_t blocks_needed = (total * 16 + 255) / 256;
-  const int grid = static_cast<int>(blocks_needed < 148 * 16 ? blocks_needed : 148 * 16);
-  if (x_dtype == B2_DTYPE_BF16)
-    quant_group128_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ldx, q, ldq,
-                                                               s, s_row_stride, s_grp_stride, M, gpr, eps, fmin,
-                                                               fmax);
-  else
-    quant_group128_kernel<__half><<<grid, 256, 0, st>>>(static_cast<const __half*>(x), ldx, q, ldq, s,
-                                                        s_row_stride, s_grp_stride, M, gpr, eps, fmin, fmax);
-  return cudaGetLastError();
+  if (static_cast<int64_t>(M) * gpr == 0) return cudaSuccess;
+  static const int forced = [] {
+    const char* e = getenv("B2_GQ_GROUPS");
+    return e ? atoi(e) : 0;
+  }();
+  int gq = (gpr >= 4 && static_cast<int64_t>((M + 15) / 16) * (gpr / 4) >= 2 * 148) ? 4 : 2;  // measured (profiles/r01c_group_quant.md): 8 costs registers and occupancy
+  if (forced == 2 || forced == 4 || forced == 8) gq = forced;
+#define B2_GQ_CASE(T_)                                                                                             \
+  switch (gq) {                                                                                                    \
+    case 8: return launch_group128<T_, 8>(x, ldx, q, ldq, s, s_row_stride, s_grp_stride, M, gpr, eps, fmin, fmax, st); \
+    case 4: return launch_group128<T_, 4>(x, ldx, q, ldq, s, s_row_stride, s_grp_stride, M, gpr, eps, fmin, fmax, st); \
+    default: return launch_group128<T_, 2>(x, ldx, q, ldq, s, s_row_stride, s_grp_stride, M, gpr, eps, fmin, fmax, st); \
+  }
+  if (x_dtype == B2_DTYPE_BF16) {
+    B2_GQ_CASE(__nv_bfloat16)
+  }
+  B2_GQ_CASE(__half)
+#undef B2_GQ_CASE
 }
 
 }  // namespace b2

@@ -408,6 +408,39 @@ def test_group_quant_fp8_128_bit_exact(M, K, colmajor):
     assert torch.equal(s.cpu().contiguous().view(torch.int32), s_ref.contiguous().view(torch.int32))
 
 
+def test_group_quant_fp8_shared_reciprocal_division_is_exact_for_every_significand_pair():
+    """The group quantizer replaces x / ys by Markstein's reciprocal sequence (csrc/quant.cu).  Every bf16
+    significand of x (128) x sign x exponent gap (0..15) against every bf16 significand of the group maximum (128)
+    at four magnitudes: codes and scales must equal the oracle's true division bit for bit."""
+    sig = (128 + torch.arange(128, dtype=torch.float64)) / 128.0  # 1.0000000b .. 1.1111111b
+    xs = []
+    for gap in range(16):
+        for sign in (1.0, -1.0):
+            xs.append(sign * sig * 2.0 ** (-gap))
+    xs = torch.cat(xs)  # 4096 values relative to 2^ea
+    per_group = 127
+    ngroups = (xs.numel() + per_group - 1) // per_group
+    pad = ngroups * per_group - xs.numel()
+    xs = torch.cat([xs, xs[:pad]]).view(ngroups, per_group)
+    rows = []
+    for ea in (-20, 0, 7, 60):
+        for a in sig.tolist():
+            blk = torch.empty(ngroups, 128, dtype=torch.float64)
+            blk[:, 0] = a * 2.0 ** ea
+            blk[:, 1:] = xs * 2.0 ** ea
+            rows.append(blk)
+    x = torch.cat(rows).to(torch.bfloat16)  # every value is exactly representable in bf16
+    assert x.shape[0] == 4 * 128 * ngroups
+    q_ref, s_ref = restate.per_token_group_quant_fp8(x, 128, 1e-10, True)
+    q, s = b2.per_token_group_quant_fp8(x.to(DEV), 128, column_major_scales=True)
+    assert torch.equal(s.cpu().contiguous().view(torch.int32), s_ref.contiguous().view(torch.int32))
+    assert torch.equal(q.cpu().view(torch.uint8), q_ref)
+    # independent of the oracle: torch's own fp32 division and e4m3 cast on the device
+    xf = x.to(DEV).float()
+    want = (xf / s.reshape(-1, 1)).clamp(-448, 448).to(torch.float8_e4m3fn)
+    assert torch.equal(q.view(torch.uint8), want.view(torch.uint8))
+
+
 # ===================================================================== fp8 GEMMs ====
 
 def _ulp_bf16(t: torch.Tensor) -> torch.Tensor:

@@ -1,0 +1,99 @@
+"""BASELINE.json configs[4]: Llama-3-70B W8A8-fp8 tensor-parallel shards, decode M=64 and prefill M=8192.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
+        tools/tp_bench.py [--int8] [--check]
+
+One process per GPU (TP = N).  Column-parallel layers (QKV 8192 -> 10240, gate_up 8192 -> 57344) split W on N and
+need no collective; row-parallel layers (o_proj 8192 -> 8192, down 28672 -> 8192) split W on K, quantize the local
+K shard per token, and sum the partial outputs with ONE NCCL all-reduce on the compute stream
+(python/sglang/srt/layers/linear.py:1467-1496 through sglang_diffusion_b200.linear.QuantLinear).
+Every number is device time (CUDA events) per call, MAX over ranks; ops = 2*M*N*K of the WHOLE layer, so TOPS is
+the job aggregate.  Prints one JSON line per (layer, M) on rank 0.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import sglang_diffusion_b200 as b2  # noqa: E402
+from sglang_diffusion_b200.linear import QuantLinear, W8A8Fp8LinearMethod, W8A8Int8LinearMethod  # noqa: E402
+
+LAYERS = [  # name, parallel, K (full), N (full)
+    ("qkv_proj", "column", 8192, 10240),
+    ("o_proj", "row", 8192, 8192),
+    ("gate_up_proj", "column", 8192, 57344),
+    ("down_proj", "row", 28672, 8192),
+]
+
+
+def timed(fn, iters, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()) * 1e-3
+
+
+def main():
+    int8 = "--int8" in sys.argv
+    check = "--check" in sys.argv
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    method = W8A8Int8LinearMethod() if int8 else W8A8Fp8LinearMethod()
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    for name, par, K, N in LAYERS:
+        layer = QuantLinear(K, N, method, bias=False, parallel=par, tp_rank=rank, tp_size=world, device=dev)
+        n_loc, k_loc = (N // world, K) if par == "column" else (N, K // world)
+        w = torch.randn(n_loc, k_loc, generator=g, device=dev) * 0.05
+        ws = w.abs().amax(dim=1, keepdim=True) / (127.0 if int8 else 448.0)
+        wq = torch.round(w / ws).clamp(-127, 127).to(torch.int8) if int8 else (w / ws).to(torch.float8_e4m3fn)
+        layer.weight.data.copy_(wq)
+        layer.weight_scale.data.copy_(ws)
+        method.process_weights_after_loading(layer)
+        del w
+        for M in (64, 8192):
+            x = (torch.randn(M, k_loc, generator=g, device=dev) / 10).bfloat16()
+            out = layer(x)
+            if check:
+                part = (x.double() @ (wq.double() * ws.double()).t())
+                if par == "row":
+                    dist.all_reduce(part)
+                err = ((out.double() - part).abs().max() / part.abs().max()).item()
+                assert err < 3e-2, (name, M, err)  # dynamic 8-bit activations: ~1 % of the output range
+            iters = 200 if M == 64 else 30
+            t_all = timed(lambda: layer(x), iters)
+            t_mm = timed(lambda: method.apply(layer, x, None), iters)
+            if rank == 0:
+                ops = 2.0 * M * N * K
+                print(json.dumps({
+                    "layer": name, "parallel": par, "tp": world, "dtype": "int8" if int8 else "fp8_e4m3", "M": M,
+                    "K_full": K, "N_full": N, "us_linear_incl_allreduce": round(t_all * 1e6, 1),
+                    "us_quant_plus_gemm": round(t_mm * 1e6, 1),
+                    "us_allreduce": round((t_all - t_mm) * 1e6, 1) if par == "row" else 0.0,
+                    "allreduce_bytes": M * N * 2 if par == "row" and world > 1 else 0,
+                    "tops_aggregate": round(ops / t_all / 1e12, 1),
+                    "gemm_config": b2.capi.last_gemm_config()}), flush=True)
+        del layer
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -184,7 +184,26 @@ def cpu_reference_run(layers, has_bias, sample_rows, warmup, steps, min_seconds=
 
 # ------------------------------------------------------------------- main ----
 
+_RESULT_FD = None
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line of the run, written to the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    # Libraries chat on stdout (NCCL prints "NCCL version ..." there at init): keep the original stdout for the
+    # result line only and send everything else to stderr, so that stdout carries exactly one JSON line.
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -223,7 +242,7 @@ def main():
                 "cpu_baseline": {"value": round(tops, 4), "unit": "TOPS", "cores": cores, "kind": kind, "sample": sample},
                 "e2e": {"value": round(tops, 4), "unit": "TOPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line), flush=True)
+        emit(line)
         return
 
     # ------------------------------------------------------------ our arm ----
@@ -383,7 +402,7 @@ def main():
                 "data": "synthetic", "config": config, "tokens_per_s": round(world * M / (ms_per_step * 1e-3), 1),
                 "frac_of_datasheet_int8_4500_tops": round(value / world / DATASHEET_INT8_TOPS, 4),
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

@@ -32,18 +32,39 @@ LAYERS = [  # name, parallel, K (full), N (full)
 ]
 
 
-def timed(fn, iters, warm=5):
+def timed(fn, iters, warm=5, inner=10):
+    """Device time per call, max over ranks.  The calls are replayed from a CUDA graph (`inner` calls per graph,
+    NCCL all-reduce included) so that decode shapes are not timed through the Python dispatcher; falls back to
+    eager launches if the capture fails."""
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
+    run, per = fn, 1
+    if "--eager" not in sys.argv:
+        try:
+            st = torch.cuda.Stream()
+            st.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(st):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=st):
+                    for _ in range(inner):
+                        fn()
+            torch.cuda.current_stream().wait_stream(st)
+            g.replay()
+            torch.cuda.synchronize()
+            run, per = g.replay, inner
+        except Exception as e:  # noqa: BLE001
+            print(f"[tp_bench] graph capture failed ({type(e).__name__}: {e}); timing eager launches", file=sys.stderr)
+            torch.cuda.synchronize()
+    reps = max(1, iters // per)
     dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(iters):
-        fn()
+    for _ in range(reps):
+        run()
     e1.record()
     torch.cuda.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
+    t = torch.tensor([e0.elapsed_time(e1) / (reps * per)], dtype=torch.float64, device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item()) * 1e-3
 
@@ -57,11 +78,17 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
+    # --as-tp N: use the shard shapes of TP = N on however many ranks are present (shape debugging on one GPU;
+    # the all-reduce then only spans the ranks that exist)
+    shard = world
+    if "--as-tp" in sys.argv:
+        shard = int(sys.argv[sys.argv.index("--as-tp") + 1])
     method = W8A8Int8LinearMethod() if int8 else W8A8Fp8LinearMethod()
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     for name, par, K, N in LAYERS:
-        layer = QuantLinear(K, N, method, bias=False, parallel=par, tp_rank=rank, tp_size=world, device=dev)
-        n_loc, k_loc = (N // world, K) if par == "column" else (N, K // world)
+        layer = QuantLinear(K, N, method, bias=False, parallel=par, tp_rank=rank, tp_size=shard, device=dev)
+        layer.tp_size = world  # the collective spans the ranks that exist
+        n_loc, k_loc = (N // shard, K) if par == "column" else (N, K // shard)
         w = torch.randn(n_loc, k_loc, generator=g, device=dev) * 0.05
         ws = w.abs().amax(dim=1, keepdim=True) / (127.0 if int8 else 448.0)
         wq = torch.round(w / ws).clamp(-127, 127).to(torch.int8) if int8 else (w / ws).to(torch.float8_e4m3fn)
@@ -74,7 +101,7 @@ def main():
             out = layer(x)
             if check:
                 part = (x.double() @ (wq.double() * ws.double()).t())
-                if par == "row":
+                if par == "row" and world > 1:
                     dist.all_reduce(part)
                 err = ((out.double() - part).abs().max() / part.abs().max()).item()
                 assert err < 3e-2, (name, M, err)  # dynamic 8-bit activations: ~1 % of the output range

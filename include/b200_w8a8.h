@@ -137,6 +137,25 @@ void b2_set_gemm_config(int config_id);
 /* Name of the tile configuration the last GEMM call on this thread used. */
 const char* b2_last_gemm_config(void);
 
+/* Sum of the row-parallel partial outputs over the tensor-parallel ranks of one NVSwitch domain, through peer memory
+ * (replaces the NCCL all-reduce of python/sglang/srt/layers/linear.py:1486-1490 for decode-sized messages; the
+ * reference's own small-message path is sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:204-260).
+ *   peer_bufs_dev    device array of `world` pointers: the SAME symmetric buffer as mapped on every rank (entry
+ *                    `rank` is the local one).  Every rank's GEMM has written its [numel] partials there, earlier in
+ *                    `stream`.  The two-shot path leaves the sums in the buffer as well.
+ *   signal_pads_dev  device array of `world` pointers to u32 signal pads of >= 8 KiB each, zeroed once at allocation
+ *                    and mapped like the buffers.  Words [0, world * max_blocks) hold the barrier numbers the peers
+ *                    post, words [1024, 1024 + max_blocks) this rank's per-CTA barrier counters (device-resident so
+ *                    that CUDA-graph replays advance them); nothing is reset between calls.
+ *   multicast_ptr    NVSwitch multicast mapping of the buffer, or NULL (then only the one-shot path is available)
+ *   out              private [numel] output of this rank (16-byte aligned), dtype bf16 / f16 like the buffers
+ *   algo             0 auto (two-shot when multicast_ptr), 1 one-shot peer loads (fp32 sum in rank order, bit-identical
+ *                    on every rank), 2 two-shot multimem.ld_reduce / multimem.st (the switch adds in fp32)
+ * The host side only has to allocate and exchange the mappings (torch.distributed._symmetric_memory in
+ * sglang_diffusion_b200/comm.py); every rank must make the same call.  No NCCL on this path. */
+int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* signal_pads_dev, void* multicast_ptr, void* out,
+                      int64_t numel, int dtype, int rank, int world, int algo, int max_blocks, b2_stream_t stream);
+
 /* Static-weight declaration (calling thread; default 0).  When non-zero the caller promises that the W operand of
  * the following GEMM calls is NOT written by the kernel that precedes the GEMM in its stream (inference weights:
  * loaded once).  Decode-shape GEMMs (M <= 128) are then launched with programmatic dependent launch: their CTAs

@@ -25,6 +25,7 @@ SYMBOLS = [
     "b2_linear_w8a8_fp8_workspace", "b2_linear_w8a8_fp8",
     "b2_launch_count", "b2_launch_count_reset", "b2_set_gemm_config", "b2_last_gemm_config",
     "b2_set_profile_buffer", "b2_set_weight_prefetch", "b2_get_weight_prefetch",
+    "b2_allreduce_symm",
 ]
 
 if not os.path.isfile(LIB_PATH):
@@ -69,6 +70,8 @@ lib.b2_set_profile_buffer.restype = None
 lib.b2_set_weight_prefetch.argtypes = [_i]
 lib.b2_set_weight_prefetch.restype = None
 lib.b2_get_weight_prefetch.restype = _i
+lib.b2_allreduce_symm.argtypes = [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp]
+lib.b2_allreduce_symm.restype = _i
 
 
 class B2Error(RuntimeError):

@@ -1,0 +1,66 @@
+"""Peer-memory all-reduce for the row-parallel W8A8 linear layers (decode-sized messages).
+
+The reference sums the partial outputs of a RowParallelLinear with `tensor_model_parallel_all_reduce`
+(python/sglang/srt/layers/linear.py:1486-1490), which picks its custom all-reduce kernel for small messages
+(sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:204-260, python/sglang/srt/distributed/device_communicators/
+custom_all_reduce.py:328-346) and NCCL otherwise.  Here the small-message path is `b2_allreduce_symm`
+(csrc/allreduce_symm.cu): the GEMM writes its partial output into a symmetric buffer and one kernel reduces it
+through the NVSwitch (multimem.ld_reduce / multimem.st) or, without a multicast mapping, with ordered peer loads.
+
+PyTorch is plumbing only: `torch.distributed._symmetric_memory` allocates the buffer and exchanges the peer /
+multicast mappings; the data path is this library's kernel.  Larger messages keep NCCL.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import capi
+
+_DT = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16}
+
+
+class SymmAllReduce:
+    """One symmetric buffer of `max_bytes` per rank of `group`; every rank must construct it collectively."""
+
+    def __init__(self, group=None, max_bytes: int = 8 << 20, device: Optional[torch.device] = None):
+        import torch.distributed._symmetric_memory as symm_mem  # raises where the build has no symmetric memory
+
+        group = group if group is not None else dist.group.WORLD
+        self.group = group
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.max_bytes = int(max_bytes)
+        self.buf = symm_mem.empty(self.max_bytes, dtype=torch.uint8, device=self.device)
+        self.handle = symm_mem.rendezvous(self.buf, group.group_name)
+        self.rank, self.world = int(self.handle.rank), int(self.handle.world_size)
+        if not 2 <= self.world <= 8:
+            raise ValueError("SymmAllReduce serves 2..8 ranks of one NVSwitch domain")
+        self.multicast_ptr = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        self.bufs_dev = int(self.handle.buffer_ptrs_dev)
+        self.pads_dev = int(self.handle.signal_pad_ptrs_dev)
+        # signal pad layout of csrc/allreduce_symm.cu: words [0, world * blocks) flags, [1024, 1024 + blocks) counters
+        if int(self.handle.signal_pad_size) < 8192:
+            raise ValueError("signal pad smaller than the 8 KiB b2_allreduce_symm needs")
+        self.max_blocks = min(64, 1024 // self.world)
+
+    def partial(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
+        """[M,N] view of the local symmetric buffer: the GEMM's output operand."""
+        nbytes = M * N * dtype.itemsize
+        if nbytes > self.max_bytes:
+            raise ValueError(f"message of {nbytes} bytes exceeds the symmetric buffer ({self.max_bytes})")
+        return self.buf[:nbytes].view(dtype).view(M, N)
+
+    def fits(self, M: int, N: int, dtype: torch.dtype) -> bool:
+        return dtype in _DT and M * N * dtype.itemsize <= self.max_bytes and (M * N) % 8 == 0 and M * N > 0
+
+    def all_reduce(self, partial: torch.Tensor, algo: int = 0) -> torch.Tensor:
+        """Sum of `partial` (a tensor returned by .partial(), already written by this rank's GEMM on the current
+        stream) over the ranks; returns a fresh private tensor.  Collective: every rank calls it."""
+        out = torch.empty(partial.shape, dtype=partial.dtype, device=partial.device)
+        stream = torch.cuda.current_stream(partial.device).cuda_stream
+        capi.check(capi.lib.b2_allreduce_symm(self.bufs_dev, self.pads_dev, self.multicast_ptr or None, out.data_ptr(),
+                                              partial.numel(), _DT[partial.dtype], self.rank, self.world, algo,
+                                              self.max_blocks, stream))
+        return out

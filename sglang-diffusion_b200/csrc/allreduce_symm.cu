@@ -1,0 +1,222 @@
+// Row-parallel partial-output all-reduce over NVLink 5 / NVSwitch peer memory (sm_100a), for the decode-shape
+// W8A8 linear layers whose [M,N] bf16 partial products are summed across tensor-parallel ranks
+// (reference: python/sglang/srt/layers/linear.py:1486-1490 -> tensor_model_parallel_all_reduce; the reference's own
+// small-message path is sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:204-260).
+//
+// The GEMM of every rank writes its partial output straight into a SYMMETRIC buffer (same size on every rank, mapped
+// into every peer's address space and into one NVSwitch multicast address; the mapping is set up by the host --
+// torch.distributed._symmetric_memory -- and handed over as plain device pointers).  One kernel then does
+//
+//   two-shot / NVLS  (multicast pointer available):
+//     barrier | rank r:  multimem.ld_reduce (the SWITCH adds the 8 partials in fp32) over slice r
+//             |          multimem.st of the bf16 sums to slice r of every rank's buffer
+//     barrier | every rank copies the reduced buffer to its private output tensor
+//   one-shot / P2P   (no multicast, or tiny messages):
+//     barrier | every rank loads all peers' partials (16-byte peer loads), adds them in fp32 IN RANK ORDER and
+//             | writes its private output  (bit-identical on every rank)
+//     barrier | (buffers may be overwritten by the next layer)
+//
+// Cross-GPU barriers are per CTA (CTA b of every rank handles the same elements): thread t < world posts the
+// barrier number to peer t's signal pad with st.release.sys and polls its own pad with ld.acquire.sys; barrier
+// numbers only grow (the per-CTA counter lives in the pad, so graph replays advance it), nothing is reset.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cstdio>
+
+#include "b200_w8a8_internal.h"
+
+namespace b2 {
+
+#define AR_DEVICE __device__ __forceinline__
+
+AR_DEVICE void st_release_sys(uint32_t* addr, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+AR_DEVICE void st_relaxed_sys(uint32_t* addr, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+AR_DEVICE uint32_t ld_acquire_sys(const uint32_t* addr) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+
+// Signal pad of a rank (u32 words): [0, world * blocks) flags, flag (b, r) = last barrier number rank r announced to
+// this rank for CTA b;  [kEpochWord + b] = barrier number CTA b of THIS rank has completed (kept on the device so
+// that a CUDA-graph replay, whose kernel arguments are frozen, still advances).
+constexpr int kEpochWord = 1024;
+
+// Barrier number `seq` between CTA `blockIdx.x` of all ranks.  A posted release-store to every peer (no NVLink round
+// trip), then an acquire-poll of the local pad.  Barrier numbers only grow and a peer can be at most one barrier
+// ahead, so "flag - seq >= 0" is the arrival test and nothing is ever reset.  Everything this CTA wrote before the
+// barrier (bar.sync makes the release cumulative over the whole CTA) is visible to the peers after it.
+// RELEASE = false when this CTA has written nothing a peer will read since the last barrier (the partials of the
+// preceding GEMM kernel are already visible at its completion; "I have finished READING" needs no release either:
+// the loads have returned before the dependent stores that precede the bar.sync were issued).
+template <bool RELEASE>
+AR_DEVICE void xgpu_barrier(uint32_t* const* pads, int rank, int world, uint32_t seq) {
+  __syncthreads();
+  if (static_cast<int>(threadIdx.x) < world) {
+    const int peer = static_cast<int>(threadIdx.x);
+    uint32_t* send = pads[peer] + static_cast<size_t>(blockIdx.x) * world + rank;
+    if constexpr (RELEASE) st_release_sys(send, seq);
+    else st_relaxed_sys(send, seq);
+    const uint32_t* recv = pads[rank] + static_cast<size_t>(blockIdx.x) * world + peer;
+    unsigned long long spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(recv) - seq) < 0) {
+      if (++spins > (1ull << 28)) __trap();  // a peer that never arrives must not hang the box
+    }
+  }
+  __syncthreads();
+}
+
+template <bool BF16>
+AR_DEVICE uint4 multimem_ld_reduce_add(const void* mc) {
+  uint4 v;
+  if constexpr (BF16) {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc)
+                 : "memory");
+  } else {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc)
+                 : "memory");
+  }
+  return v;
+}
+
+AR_DEVICE void multimem_st(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
+template <bool BF16>
+AR_DEVICE void unpack8(const uint4& v, float (&f)[8]) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if constexpr (BF16) {
+      f[2 * i] = __uint_as_float(w[i] << 16);
+      f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    } else {
+      const __half2 h = *reinterpret_cast<const __half2*>(&w[i]);
+      f[2 * i] = __low2float(h);
+      f[2 * i + 1] = __high2float(h);
+    }
+  }
+}
+
+template <bool BF16>
+AR_DEVICE uint4 pack8(const float (&f)[8]) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if constexpr (BF16) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    } else {
+      const __half2 h = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// nvec = number of 16-byte vectors of the message.  Vector v belongs to CTA (v / blockDim.x) % gridDim.x on every
+// rank -- the per-CTA barriers rely on that -- and, in the two-shot path, to the slice of rank
+// (v / (blockDim.x * gridDim.x)) % world.
+template <bool BF16>
+__global__ void __launch_bounds__(512) allreduce_two_shot_kernel(uint4* const* bufs, uint32_t* const* pads,
+                                                                  uint4* mc, uint4* out, long long nvec, int rank,
+                                                                  int world) {
+  const uint32_t epoch = pads[rank][kEpochWord + blockIdx.x];
+  xgpu_barrier<false>(pads, rank, world, epoch + 1);  // every rank's GEMM has written its partials (stream order)
+  const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
+  const long long lane0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (long long v = lane0 + stride * rank; v < nvec; v += stride * world) {
+    const uint4 sum = multimem_ld_reduce_add<BF16>(mc + v);
+    multimem_st(mc + v, sum);
+  }
+  xgpu_barrier<true>(pads, rank, world, epoch + 2);  // the sums of every slice have landed in this rank's buffer
+  if (threadIdx.x == 0) pads[rank][kEpochWord + blockIdx.x] = epoch + 2;
+  const uint4* mine = bufs[rank];
+  for (long long v = lane0; v < nvec; v += stride) out[v] = mine[v];
+  // no trailing barrier: a peer can only overwrite this rank's buffer through a later multimem.st, which sits
+  // behind the first barrier of the NEXT call, and that barrier needs this CTA to have left this kernel
+}
+
+template <bool BF16>
+__global__ void __launch_bounds__(512) allreduce_one_shot_kernel(uint4* const* bufs, uint32_t* const* pads, uint4* out,
+                                                                  long long nvec, int rank, int world) {
+  const uint32_t epoch = pads[rank][kEpochWord + blockIdx.x];
+  xgpu_barrier<false>(pads, rank, world, epoch + 1);
+  const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
+  for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += stride) {
+    float acc[8];
+    unpack8<BF16>(bufs[0][v], acc);
+    for (int r = 1; r < world; ++r) {  // rank order: the same fp32 sum, bit for bit, on every rank
+      float f[8];
+      unpack8<BF16>(bufs[r][v], f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
+    }
+    out[v] = pack8<BF16>(acc);
+  }
+  xgpu_barrier<false>(pads, rank, world, epoch + 2);  // every peer has read this rank's partials: the buffer may be reused
+  if (threadIdx.x == 0) pads[rank][kEpochWord + blockIdx.x] = epoch + 2;
+}
+
+}  // namespace b2
+
+using namespace b2;
+
+extern "C" int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* signal_pads_dev, void* multicast_ptr,
+                                 void* out, int64_t numel, int dtype, int rank, int world, int algo,
+                                 int max_blocks, b2_stream_t stream) {
+  if (!peer_bufs_dev || !signal_pads_dev || !out) return fail_msg(B2_ERR_ARG, "allreduce_symm: null pointer");
+  if (dtype != B2_DTYPE_BF16 && dtype != B2_DTYPE_F16)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm: dtype must be bfloat16 or float16");
+  if (world < 2 || world > 8 || rank < 0 || rank >= world)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm: world size must be 2..8 (one NVSwitch domain), rank inside it");
+  if (numel <= 0 || numel % 8 != 0) return fail_msg(B2_ERR_ARG, "allreduce_symm: numel must be a positive multiple of 8");
+  if (reinterpret_cast<uintptr_t>(out) % 16 != 0) return fail_msg(B2_ERR_ARG, "allreduce_symm: out must be 16-byte aligned");
+  if (algo == 2 && !multicast_ptr) return fail_msg(B2_ERR_ARG, "allreduce_symm: two-shot needs a multicast pointer");
+  const long long nvec = numel / 8;
+  // auto: ordered peer loads while the traffic they cost (every rank pulls the whole message from every peer) stays
+  // small, the switch reduction above that (measured crossover, profiles/r01d_symm_allreduce_*.log)
+  const bool two_shot =
+      algo == 2 || (algo == 0 && multicast_ptr != nullptr && numel * 2 * static_cast<int64_t>(world) > (4ll << 20));
+  const int threads = 512;
+  // per-CTA flags: world u32 per block in every rank's signal pad; the host says how many blocks the pad can take
+  long long blocks = (nvec + threads - 1) / threads;
+  if (two_shot) blocks = (blocks + world - 1) / world;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks > kEpochWord / world) blocks = kEpochWord / world;  // the flag words must stay below the epoch words
+  if (blocks < 1) blocks = 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint4* const* bufs = reinterpret_cast<uint4* const*>(peer_bufs_dev);
+  if (two_shot) {
+    if (dtype == B2_DTYPE_BF16)
+      allreduce_two_shot_kernel<true><<<static_cast<int>(blocks), threads, 0, st>>>(
+          bufs, signal_pads_dev, static_cast<uint4*>(multicast_ptr), static_cast<uint4*>(out), nvec, rank, world);
+    else
+      allreduce_two_shot_kernel<false><<<static_cast<int>(blocks), threads, 0, st>>>(
+          bufs, signal_pads_dev, static_cast<uint4*>(multicast_ptr), static_cast<uint4*>(out), nvec, rank, world);
+  } else {
+    if (dtype == B2_DTYPE_BF16)
+      allreduce_one_shot_kernel<true><<<static_cast<int>(blocks), threads, 0, st>>>(
+          bufs, signal_pads_dev, static_cast<uint4*>(out), nvec, rank, world);
+    else
+      allreduce_one_shot_kernel<false><<<static_cast<int>(blocks), threads, 0, st>>>(
+          bufs, signal_pads_dev, static_cast<uint4*>(out), nvec, rank, world);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm launch: %s", cudaGetErrorString(e));
+  count_launch();
+  return B2_OK;
+}

@@ -44,6 +44,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
 void count_launch(int n = 1);
 void* profile_buffer();  // device buffer set by b2_set_profile_buffer (nullptr = profiling off)
 int device_sm_count();
+int fail_msg(int code, const char* fmt, ...);  // sets b2_last_error() of the calling thread, returns `code`
 bool weight_prefetch_enabled();  // b2_set_weight_prefetch: W operands are static, GEMMs may launch programmatically
 
 }  // namespace b2

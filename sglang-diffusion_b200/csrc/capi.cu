@@ -34,6 +34,15 @@ static int fail(int code, const char* fmt, ...) {
   return code;
 }
 
+// the same, for the other translation units of the library
+int fail_msg(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
 struct DevInfo {
   int sms = 0, major = 0, minor = 0;
   bool valid = false;

@@ -490,7 +490,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   // (measured, profiles/r01c_sweep_splitk.log: it wins whenever the activation box is small, and for any M <= 128
   // when N is too narrow to give the persistent kernel one tile per SM)
   const bool decode_shape = a.M <= 32 || (a.M <= BM && a.N < 32 * sms);
-  if ((forced_config & 0x40) ? a.M <= BM : ((forced_config & 0xff) == 0 && decode_shape))
+  if ((forced_config & 0x80000) ? a.M <= BM : ((forced_config & 0xff) == 0 && decode_shape))
     return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);
   const TileConfig* cfg = &pick_config(a.M, a.N, sms);
   const int forced_debug = forced_config >> 8;  // developer experiments ride in the upper bits of the forced id

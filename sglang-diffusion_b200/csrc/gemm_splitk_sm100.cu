@@ -39,6 +39,10 @@ struct SplitParams {
   int split;       // S = cluster size
   int stages;
   int a_box_rows;  // activation rows fetched per stage (multiple of 8, >= M)
+  int bn;          // weight rows per tile = UMMA N (multiple of 16, 16..256): chosen at run time so that the grid is
+                   // ONE balanced wave (e.g. N = 28672 -> 138 tiles of 208 rows on 148 SMs)
+  uint32_t tmem_cols;   // power of two >= max(32, bn)
+  uint32_t part_pitch;  // bytes per row of the partial buffer: bn rounded up to 32 words (the XOR swizzle's span)
   uint32_t bar_offset;  // byte offset of the barrier block inside the dynamic shared-memory window
 };
 
@@ -73,17 +77,28 @@ B2_DEVICE uint4 ld_dsmem_v4(uint32_t local_addr, uint32_t cta) {
 // partial accumulators in shared memory: [row][BN] words, 16-byte chunk index XORed with (row & 7) -- the
 // row-per-lane 16-byte stores of the spill and the chunk-per-lane 16-byte loads of the reduction are both
 // bank-conflict free
-template <int BN>
-B2_DEVICE uint32_t part_offset(int row, int chunk) {
-  return static_cast<uint32_t>(row * BN * 4 + ((chunk ^ (row & 7)) << 4));
+B2_DEVICE uint32_t part_offset(int row, int chunk, uint32_t pitch_bytes) {
+  return static_cast<uint32_t>(row) * pitch_bytes + static_cast<uint32_t>((chunk ^ (row & 7)) << 4);
 }
 
-template <MmaKind KIND, int BN>
+// 32 lanes x 16 consecutive 32-bit columns -> 16 registers per thread
+B2_DEVICE void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+template <MmaKind KIND>
 __global__ void __launch_bounds__(NUM_THREADS)
     gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                        const SplitParams p) {
-  constexpr uint32_t B_STAGE_BYTES = BN * BK;
-  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  const int BN = p.bn;
+  const uint32_t B_STAGE_BYTES = static_cast<uint32_t>(BN) * BK;
+  const uint32_t TMEM_COLS = p.tmem_cols;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
@@ -147,6 +162,18 @@ __global__ void __launch_bounds__(NUM_THREADS)
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
 
+  // column slice of the tile this CTA reduces and writes (work item = row x group of 4 columns)
+  const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
+  const int cols_per = (((BN + S - 1) / S) + 3) & ~3;
+  const int c0 = rank * cols_per;
+  const int width = max(0, min(cols_per, BN - c0));
+  const int gpr = width >> 2;  // groups per row
+  const bool has_bias = p.bias != nullptr;
+  const bool raw_out = (KIND == MmaKind::I8) && p.out_dtype == B2_DTYPE_S32;
+  const bool fixed_group = gpr > 0 && (128 % gpr) == 0;  // then a thread keeps its column group for every row
+  float bs[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {-0.f, -0.f, -0.f, -0.f};
+  int cached_col = -1;
+
   if (warp == 0) {
     // ========================================== TMA producer (ring reuse) ====
     int stage = 0;
@@ -168,7 +195,7 @@ __global__ void __launch_bounds__(NUM_THREADS)
     }
   } else if (warp == 1) {
     // ======================================================= MMA issuer ====
-    constexpr uint32_t idesc = make_idesc<KIND>(BM, BN);
+    const uint32_t idesc = make_idesc<KIND>(BM, static_cast<uint32_t>(BN));
     int stage = 0;
     uint32_t phase = 0;
     for (int kb = kb0; kb < kb1; ++kb) {
@@ -199,6 +226,19 @@ __global__ void __launch_bounds__(NUM_THREADS)
       const int t = (warp - EPI_WARP0) * 32 + lane;
       if (t < p.M && p.As != nullptr) smem_as[t] = __ldg(p.As + t);
     }
+    // per-column scale / bias of this thread's column group: fetched while the main loop runs
+    if (fixed_group && !raw_out && epi_tid < p.M * gpr) {
+      const int col = tile * BN + c0 + (epi_tid % gpr) * 4;
+      if (col < p.N) {
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.Bs + col));
+        bs[0] = b4.x; bs[1] = b4.y; bs[2] = b4.z; bs[3] = b4.w;
+        if (has_bias) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bi[j] = load_bias(p.bias, p.bias_dtype, col + j);
+        }
+        cached_col = col;
+      }
+    }
     if (quarter * 32 < p.a_box_rows) {
       mbar_wait(acc_full, 0);
       tc_fence_after_sync();
@@ -206,13 +246,13 @@ __global__ void __launch_bounds__(NUM_THREADS)
       const int row = quarter * 32 + lane;
       uint8_t* part_bytes = reinterpret_cast<uint8_t*>(part);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(t_row + static_cast<uint32_t>(c * 32), r);
+      for (int c = 0; c < BN / 16; ++c) {
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(t_row + static_cast<uint32_t>(c * 16), r);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<uint4*>(part_bytes + part_offset<BN>(row, c * 8 + j)) =
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4*>(part_bytes + part_offset(row, c * 4 + j, p.part_pitch)) =
               make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
       }
     }
@@ -231,25 +271,15 @@ __global__ void __launch_bounds__(NUM_THREADS)
     // ===================== reduce my column slice over the cluster, epilogue ====
     // work item = (row, group of 4 columns); consecutive threads take consecutive groups of one row, so the DSMEM
     // loads are conflict free and the global stores of a warp cover whole contiguous row segments
-    const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
-    const int cols_per = (((BN + S - 1) / S) + 3) & ~3;
-    const int c0 = rank * cols_per;
-    const int width = min(cols_per, BN - c0);
-    const int gpr = width > 0 ? width >> 2 : 0;  // groups per row
-    const bool has_bias = p.bias != nullptr;
-    const bool raw_out = (KIND == MmaKind::I8) && p.out_dtype == B2_DTYPE_S32;
     const uint32_t part_base = smem_u32(part);
     const int items = p.M * gpr;
-    const bool fixed_group = gpr > 0 && (128 % gpr) == 0;  // then a thread keeps its column group for every row
-    float bs[4] = {0.f, 0.f, 0.f, 0.f}, bi[4] = {-0.f, -0.f, -0.f, -0.f};
-    int cached_col = -1;
     for (int idx = epi_tid; idx < items; idx += 128) {
       const int row = idx / gpr;
       const int g = idx - row * gpr;
       const int c = c0 + g * 4;
       const int col = tile * BN + c;
       if (col >= p.N) continue;  // N % 8 == 0: a group of 4 columns is inside or outside as a whole
-      const uint32_t addr = part_base + part_offset<BN>(row, c >> 2);
+      const uint32_t addr = part_base + part_offset(row, c >> 2, p.part_pitch);
       uint4 acc = ld_dsmem_v4(addr, 0);
       for (int pr = 1; pr < S; ++pr) {
         const uint4 o = ld_dsmem_v4(addr, pr);
@@ -298,12 +328,9 @@ __global__ void __launch_bounds__(NUM_THREADS)
 
 // ------------------------------------------------------------------ host ----
 
-static const int kSplitBN[4] = {32, 64, 128, 256};
-
 struct SplitPlan {
-  int bn_idx, split, stages;
+  int bn, split, stages;
   size_t smem;
-  double cost;
 };
 
 static size_t splitk_smem(int bn, int a_rows, int stages) {
@@ -312,23 +339,50 @@ static size_t splitk_smem(int bn, int a_rows, int stages) {
   const size_t mma_reach = stages * a_stage + static_cast<size_t>(BM) * BK;  // 128-row reads of the last A stage
   if (mma_reach > data) data = mma_reach;
   const size_t rows_p = static_cast<size_t>((a_rows + 31) / 32) * 32;
-  const size_t partial = rows_p * bn * 4;
+  const size_t partial = rows_p * static_cast<size_t>((bn + 31) / 32 * 32) * 4;
   if (partial > data) data = partial;
   data = (data + 1023) / 1024 * 1024;
   return data + 1024;  // 512 B of barriers + TMEM pointer (2 * 24 + 2 slots of 8 bytes max), 512 B of staged As
 }
 
-// Schedule heuristic, fitted to tools/perf_sweep.py splitk --all (profiles/r01c_sweep_splitk.log):
+static int deepest_ring(int bn, int a_rows, int kb_per) {
+  int stages = kb_per < 24 ? kb_per : 24;
+  while (stages > 1 && splitk_smem(bn, a_rows, stages) > static_cast<size_t>(SMEM_LIMIT)) --stages;
+  return stages;
+}
+
+template <MmaKind KIND>
+static void configure_kernel(char* err, size_t err_len, int* status) {
+  static int attr_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr_dev == dev) return;
+  cudaError_t e =
+      cudaFuncSetAttribute(gemm_splitk_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) {
+    snprintf(err, err_len, "cudaFuncSetAttribute(max dynamic smem): %s", cudaGetErrorString(e));
+    *status = B2_ERR_CUDA;
+    return;
+  }
+  attr_dev = dev;
+}
+
+// Schedule heuristic, fitted to tools/perf_sweep.py splitk --all (profiles/r01c_sweep_splitk_all.log):
 //   * tile width 128 while the activation box is small (<= 32 rows), 64 above (the 16 KB activation stage then
 //     dominates the ring);
 //   * the smallest power-of-two split that puts >= ~0.85 x #SMs CTAs in the grid with >= 4 K-blocks each;
-//   * the deepest ring (<= 12 stages) that still lets EVERY CTA of the grid be resident at once -- one wave, the
-//     block scheduler balances SMs that hold 1 vs 2 CTAs -- and 4 stages when the grid needs more than 3 per SM.
-static SplitPlan plan_splitk(int M, int N, int K, int a_rows, int sms) {
-  (void)M;
+//   * the deepest ring (<= 12 stages) that still lets EVERY CTA of the grid be resident at once, and 4 stages when
+//     the grid needs more than 3 CTAs per SM.
+// Measured and rejected (profiles/r01d_sweep_splitk_balanced.log): one balanced wave of <= #SM CTAs with odd tile
+// widths (208 rows for N = 28672, 176 x split 4 for N = 6144) and the deepest ring that fits.  It is no faster on
+// the wide layer and 1.5x slower on the narrow ones: a CTA that owns a whole SM's shared memory leaves no room for
+// the programmatically launched successor, so nothing hides the ~4 us launch / first-round-trip / drain cost.  The
+// kernel keeps the run-time tile width (any multiple of 16) for shapes whose N is not a multiple of 128.
+static SplitPlan plan_splitk(int N, int K, int a_rows) {
+  const int sms = device_sm_count();
   const int num_kb = (K + BK - 1) / BK;
-  const int bi = a_rows <= 32 ? 2 : 1;
-  const int bn = kSplitBN[bi];
+  int bn = a_rows <= 32 ? 128 : 64;
+  if (N < bn) bn = (N + 15) / 16 * 16;
   const int tiles = (N + bn - 1) / bn;
   int s = 1;
   while (s < 8 && tiles * s < (sms * 85) / 100 && num_kb / (2 * s) >= 4) s *= 2;
@@ -343,24 +397,15 @@ static SplitPlan plan_splitk(int M, int N, int K, int a_rows, int sms) {
   }
   if (stages > kb_per) stages = kb_per;
   while (stages > 1 && splitk_smem(bn, a_rows, stages) > static_cast<size_t>(SMEM_LIMIT)) --stages;
-  return SplitPlan{bi, s, stages, splitk_smem(bn, a_rows, stages), 0.0};
+  return SplitPlan{bn, s, stages, splitk_smem(bn, a_rows, stages)};
 }
 
-template <MmaKind KIND, int BN>
+template <MmaKind KIND>
 static int launch_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const SplitParams& p, int grid, size_t smem,
                          bool pdl, cudaStream_t st, char* err, size_t err_len) {
-  auto kern = gemm_splitk_kernel<KIND, BN>;
-  static int attr_dev = -1;
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (attr_dev != dev) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-    if (e != cudaSuccess) {
-      snprintf(err, err_len, "cudaFuncSetAttribute(max dynamic smem): %s", cudaGetErrorString(e));
-      return B2_ERR_CUDA;
-    }
-    attr_dev = dev;
-  }
+  int status = B2_OK;
+  configure_kernel<KIND>(err, err_len, &status);
+  if (status != B2_OK) return status;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(static_cast<unsigned>(grid));
   cfg.blockDim = dim3(NUM_THREADS);
@@ -375,7 +420,7 @@ static int launch_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const Spl
   attrs[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = pdl ? 2 : 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_splitk_kernel<KIND>, ta, tb, p);
   if (e != cudaSuccess) {
     snprintf(err, err_len, "split-K gemm kernel launch (cluster %d, smem %zu): %s", p.split, smem,
              cudaGetErrorString(e));
@@ -385,32 +430,29 @@ static int launch_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const Spl
   return B2_OK;
 }
 
-// forced: 0 = plan; otherwise 0x40 | bn_idx << 3 | (S - 1), optionally | ring depth cap << 8
+// forced: 0 = plan; otherwise 0x80000 | (bn / 16 - 1) | (S - 1) << 4, optionally | ring depth cap << 8
 int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const char** used_config, cudaStream_t st,
                        char* err, size_t err_len) {
-  const int sms = device_sm_count();
   const int a_rows = ((a.M + 7) / 8) * 8;
-  SplitPlan plan = plan_splitk(a.M, a.N, a.K, a_rows, sms);
   const int num_kb = (a.K + BK - 1) / BK;
-  if (forced & 0x40) {
-    plan.bn_idx = (forced >> 3) & 3;
-    plan.split = (forced & 7) + 1;
+  SplitPlan plan;
+  if (forced & 0x80000) {
+    plan.bn = ((forced & 15) + 1) * 16;
+    plan.split = ((forced >> 4) & 7) + 1;
     if (plan.split > num_kb) plan.split = num_kb;
-    const int bn = kSplitBN[plan.bn_idx];
-    const int kb_per = (num_kb + plan.split - 1) / plan.split;
-    int stages = kb_per < 24 ? kb_per : 24;
-    while (stages > 1 && splitk_smem(bn, a_rows, stages) > static_cast<size_t>(SMEM_LIMIT)) --stages;
-    const int forced_stages = (forced >> 8) & 31;  // developer sweeps: ring depth cap in bits 8-12
-    if (forced_stages >= 1 && forced_stages < stages) stages = forced_stages;
-    plan.stages = stages;
-    plan.smem = splitk_smem(bn, a_rows, stages);
+    plan.stages = deepest_ring(plan.bn, a_rows, (num_kb + plan.split - 1) / plan.split);
+    const int cap = (forced >> 8) & 31;  // developer sweeps: ring depth cap in bits 8-12
+    if (cap >= 1 && cap < plan.stages) plan.stages = cap;
+    plan.smem = splitk_smem(plan.bn, a_rows, plan.stages);
+  } else {
+    plan = plan_splitk(a.N, a.K, a_rows);
   }
-  const int bn = kSplitBN[plan.bn_idx];
+  const int bn = plan.bn;
   if (plan.smem > static_cast<size_t>(SMEM_LIMIT)) {
     snprintf(err, err_len, "split-K plan does not fit shared memory (bn=%d rows=%d)", bn, a_rows);
     return B2_ERR_ARG;
   }
-  static thread_local char name[48];
+  static thread_local char name[64];
   snprintf(name, sizeof(name), "splitk_%dx%d_s%d_st%d", a_rows, bn, plan.split, plan.stages);
   if (used_config) *used_config = name;
 
@@ -429,6 +471,10 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
   p.split = plan.split;
   p.stages = plan.stages;
   p.a_box_rows = a_rows;
+  p.bn = bn;
+  p.tmem_cols = 32;
+  while (p.tmem_cols < static_cast<uint32_t>(bn)) p.tmem_cols *= 2;
+  p.part_pitch = static_cast<uint32_t>((bn + 31) / 32 * 32) * 4u;
   p.bar_offset = static_cast<uint32_t>(plan.smem - 1024);
 
   CUtensorMap ta, tb;
@@ -440,23 +486,9 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
   }
   const int tiles = (a.N + bn - 1) / bn;
   const int grid = tiles * plan.split;
-#define B2_SPLITK_CASE(KIND_, BN_) \
-  return launch_splitk<KIND_, BN_>(ta, tb, p, grid, plan.smem, weight_prefetch_enabled(), st, err, err_len)
-  if (flavor == GEMM_S8) {
-    switch (bn) {
-      case 32: B2_SPLITK_CASE(MmaKind::I8, 32);
-      case 64: B2_SPLITK_CASE(MmaKind::I8, 64);
-      case 128: B2_SPLITK_CASE(MmaKind::I8, 128);
-      default: B2_SPLITK_CASE(MmaKind::I8, 256);
-    }
-  }
-  switch (bn) {
-    case 32: B2_SPLITK_CASE(MmaKind::F8, 32);
-    case 64: B2_SPLITK_CASE(MmaKind::F8, 64);
-    case 128: B2_SPLITK_CASE(MmaKind::F8, 128);
-    default: B2_SPLITK_CASE(MmaKind::F8, 256);
-  }
-#undef B2_SPLITK_CASE
+  const bool pdl = weight_prefetch_enabled();
+  if (flavor == GEMM_S8) return launch_splitk<MmaKind::I8>(ta, tb, p, grid, plan.smem, pdl, st, err, err_len);
+  return launch_splitk<MmaKind::F8>(ta, tb, p, grid, plan.smem, pdl, st, err, err_len);
 }
 
 }  // namespace b2

@@ -190,10 +190,38 @@ class QuantLinear(torch.nn.Module):
             return full.narrow(dim_k, self.tp_rank * k, k)
         return full
 
+    def use_symmetric_all_reduce(self, comm) -> None:
+        """Route decode-sized row-parallel reductions through `comm` (sglang_diffusion_b200.comm.SymmAllReduce):
+        the GEMM writes its partial output into the symmetric buffer and b2_allreduce_symm sums it over NVLink
+        peer memory; messages that do not fit keep the NCCL all-reduce.  (The reference makes the same split
+        between its custom all-reduce and NCCL, custom_all_reduce.py:328-346.)"""
+        self.symm_comm = comm
+
+    def _row_parallel_symm(self, x: torch.Tensor, bias) -> Optional[torch.Tensor]:
+        comm = getattr(self, "symm_comm", None)
+        if comm is None or not x.is_cuda or not isinstance(self.quant_method, (W8A8Int8LinearMethod, W8A8Fp8LinearMethod)):
+            return None
+        x2d = x.view(-1, x.shape[-1])
+        M, N = x2d.shape[0], self.weight.shape[1]
+        if not comm.fits(M, N, x.dtype):
+            return None
+        with capi.static_weights():
+            if isinstance(self.quant_method, W8A8Int8LinearMethod):
+                q, s = ops.per_token_quant_int8(x2d)
+            else:
+                q, s = ops.sglang_per_token_quant_fp8(x2d)
+            part = ops.scaled_mm_out(q, self.weight, s.view(-1), self.weight_scale.view(-1), comm.partial(M, N, x.dtype),
+                                     bias)
+        return comm.all_reduce(part).view(*x.shape[:-1], N)
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         bias = self.bias
         if self.parallel == "row" and self.tp_rank != 0:
             bias = None
+        if self.parallel == "row" and self.tp_size > 1:
+            out = self._row_parallel_symm(x, bias)
+            if out is not None:
+                return out
         out = self.quant_method.apply(self, x, bias)
         if self.parallel == "row" and self.tp_size > 1:
             dist.all_reduce(out, group=self.tp_group)  # in place, on the compute stream (NCCL) / gloo on CPU

@@ -38,6 +38,27 @@ def fp8_blockwise_scaled_mm(mat_a, mat_b, scales_a, scales_b, out_dtype):
     return _ops.fp8_blockwise_scaled_mm.default(mat_a, mat_b, scales_a, scales_b, out_dtype)
 
 
+def scaled_mm_out(mat_a, mat_b, scales_a, scales_b, out, bias=None):
+    """int8_scaled_mm / fp8_scaled_mm (chosen by mat_a.dtype) writing into the caller's `out` [M,N] instead of a
+    fresh tensor -- the C ABI takes the output pointer (include/b200_w8a8.h); the torch ops above cannot, their
+    schema is the reference's.  Used to place row-parallel partial outputs in the symmetric all-reduce buffer."""
+    from . import capi
+
+    M, K = mat_a.shape
+    N = mat_b.shape[1]
+    assert mat_b.shape[0] == K and mat_b.stride(0) == 1, "mat_b must be [K,N] with stride(0) == 1"
+    assert out.shape == (M, N) and out.stride(1) == 1 and mat_a.stride(1) == 1
+    assert scales_a.numel() == M and scales_b.numel() == N and scales_a.is_contiguous() and scales_b.is_contiguous()
+    dt = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16, torch.float32: capi.DTYPE_F32}
+    fn = capi.lib.b2_gemm_s8 if mat_a.dtype == torch.int8 else capi.lib.b2_gemm_e4m3
+    stream = torch.cuda.current_stream(mat_a.device).cuda_stream
+    capi.check(fn(mat_a.data_ptr(), mat_a.stride(0), mat_b.data_ptr(), mat_b.stride(1), scales_a.data_ptr(),
+                  scales_b.data_ptr(), None if bias is None else bias.data_ptr(),
+                  dt[bias.dtype] if bias is not None else capi.DTYPE_F32, out.data_ptr(), out.stride(0),
+                  dt[out.dtype], M, N, K, stream))
+    return out
+
+
 def int8_scaled_mm_with_quant(mat1, mat2, scales2, bias, out_dtype, is_vnni=False):
     """CPU-path op name (gemm_int8.cpp:481-547) on CUDA tensors: bf16/f16 in, fused
     per-token int8 quantization + int8 GEMM + scale/bias epilogue.  mat2 is [N,K] int8."""

@@ -133,9 +133,11 @@ def test_gemm_s8_raw_accumulators_exact_every_tile_config(cfg, M, N, K):
     assert torch.equal(D, exact_acc(A, W))
 
 
-def splitk_cfg(bn_idx: int, split: int) -> int:
-    """forced id of the decode kernel (gemm_splitk_sm100.cu): 0x40 | bn_idx << 3 | (S - 1); bn = 32 << bn_idx"""
-    return 0x40 | (bn_idx << 3) | (split - 1)
+def splitk_cfg(bn_idx: int, split: int, bn: int = 0) -> int:
+    """forced id of the decode kernel (gemm_splitk_sm100.cu): 0x80000 | (bn / 16 - 1) | (S - 1) << 4;
+    bn = 32 << bn_idx unless given"""
+    bn = bn or (32 << bn_idx)
+    return 0x80000 | (bn // 16 - 1) | ((split - 1) << 4)
 
 
 @pytest.mark.parametrize("bn_idx", [0, 1, 2, 3])
@@ -149,6 +151,20 @@ def test_gemm_s8_splitk_cluster_accumulators_exact(bn_idx, split, M, N, K):
     W = torch.randint(-128, 128, (N, K), dtype=torch.int8, generator=g).to(DEV)
     D = c_gemm_s8(A, W, None, None, None, torch.int32, splitk_cfg(bn_idx, split))
     assert capi.last_gemm_config().startswith("splitk_")
+    assert torch.equal(D, exact_acc(A, W))
+
+
+@pytest.mark.parametrize("bn", [16, 48, 80, 112, 176, 208, 240])
+@pytest.mark.parametrize("split", [1, 4])
+@pytest.mark.parametrize("M,N,K", [(5, 1000, 2048), (64, 1296, 1168)])
+def test_gemm_s8_splitk_odd_tile_widths_exact(bn, split, M, N, K):
+    """Tile widths that are not powers of two (the planner picks e.g. 208 rows for N = 28672): 16-column TMEM
+    reads, partial rows padded to 32 words, N tails inside a tile."""
+    g = torch.Generator().manual_seed(bn * 13 + split + M)
+    A = torch.randint(-128, 128, (M, K), dtype=torch.int8, generator=g).to(DEV)
+    W = torch.randint(-128, 128, (N, K), dtype=torch.int8, generator=g).to(DEV)
+    D = c_gemm_s8(A, W, None, None, None, torch.int32, splitk_cfg(0, split, bn))
+    assert f"x{bn}_s" in capi.last_gemm_config()
     assert torch.equal(D, exact_acc(A, W))
 
 

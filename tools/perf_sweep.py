@@ -172,13 +172,10 @@ if "splitk" in want:
             gemm_int8(M, N, K)
             gemm_int8(M, N, K, cfg=1 if N <= 6144 else 4)
             if "--all" in sys.argv:
-                for bn_idx in range(4):
+                for bn in (32, 64, 96, 112, 128, 176, 208, 256):
                     for S in (1, 2, 4, 8):
-                        for cap in (4, 8, 16):
-                            kb_per = -(-(K // 128) // S)
-                            if cap > 4 and cap // 2 >= kb_per:
-                                continue  # same launch as the previous cap
-                            gemm_int8(M, N, K, cfg=0x40 | (bn_idx << 3) | (S - 1) | (cap << 8))
+                        for cap in (4, 24):
+                            gemm_int8(M, N, K, cfg=0x80000 | (bn // 16 - 1) | ((S - 1) << 4) | (cap << 8))
     sys.exit(0)
 if "int8" in want:
     print("# C1 + C2: Llama-3-8B int8 shapes"); gemm_int8(128, 4096, 4096, bias=True)

@@ -84,10 +84,16 @@ def main():
     if "--as-tp" in sys.argv:
         shard = int(sys.argv[sys.argv.index("--as-tp") + 1])
     method = W8A8Int8LinearMethod() if int8 else W8A8Fp8LinearMethod()
+    comm = None
+    if "--symm" in sys.argv and world > 1:  # decode-sized row-parallel sums through b2_allreduce_symm (peer memory)
+        from sglang_diffusion_b200.comm import SymmAllReduce
+        comm = SymmAllReduce(max_bytes=4 << 20, device=dev)
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     for name, par, K, N in LAYERS:
         layer = QuantLinear(K, N, method, bias=False, parallel=par, tp_rank=rank, tp_size=shard, device=dev)
         layer.tp_size = world  # the collective spans the ranks that exist
+        if comm is not None and par == "row":
+            layer.use_symmetric_all_reduce(comm)
         n_loc, k_loc = (N // shard, K) if par == "column" else (N, K // shard)
         w = torch.randn(n_loc, k_loc, generator=g, device=dev) * 0.05
         ws = w.abs().amax(dim=1, keepdim=True) / (127.0 if int8 else 448.0)
@@ -117,6 +123,8 @@ def main():
                     "us_allreduce": round((t_all - t_mm) * 1e6, 1) if par == "row" else 0.0,
                     "allreduce_bytes": M * N * 2 if par == "row" and world > 1 else 0,
                     "tops_aggregate": round(ops / t_all / 1e12, 1),
+                    "allreduce": ("b2_allreduce_symm" if comm is not None and comm.fits(M, N, torch.bfloat16)
+                                  else "nccl") if par == "row" and world > 1 else None,
                     "gemm_config": b2.capi.last_gemm_config()}), flush=True)
         del layer
     dist.destroy_process_group()

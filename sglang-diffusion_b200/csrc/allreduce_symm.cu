@@ -187,10 +187,9 @@ extern "C" int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* si
   if (reinterpret_cast<uintptr_t>(out) % 16 != 0) return fail_msg(B2_ERR_ARG, "allreduce_symm: out must be 16-byte aligned");
   if (algo == 2 && !multicast_ptr) return fail_msg(B2_ERR_ARG, "allreduce_symm: two-shot needs a multicast pointer");
   const long long nvec = numel / 8;
-  // auto: ordered peer loads while the traffic they cost (every rank pulls the whole message from every peer) stays
-  // small, the switch reduction above that (measured crossover, profiles/r01d_symm_allreduce_*.log)
-  const bool two_shot =
-      algo == 2 || (algo == 0 && multicast_ptr != nullptr && numel * 2 * static_cast<int64_t>(world) > (4ll << 20));
+  // auto (measured, profiles/r01d_symm_allreduce_{2,8}gpu.log): the switch reduction wins at every size on 8 ranks
+  // (1 MB: 15 us vs 33 us one-shot vs 34 us NCCL); between two ranks the ordered peer loads are ahead up to ~2 MB
+  const bool two_shot = algo == 2 || (algo == 0 && multicast_ptr != nullptr && (world > 2 || numel * 2 > (2ll << 20)));
   const int threads = 512;
   // per-CTA flags: world u32 per block in every rank's signal pad; the host says how many blocks the pad can take
   long long blocks = (nvec + threads - 1) / threads;

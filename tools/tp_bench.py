@@ -110,7 +110,9 @@ def main():
                 if par == "row" and world > 1:
                     dist.all_reduce(part)
                 err = ((out.double() - part).abs().max() / part.abs().max()).item()
-                assert err < 3e-2, (name, M, err)  # dynamic 8-bit activations: ~1 % of the output range
+                # dynamic 8-bit activations against the exact product of the same quantized weights: e4m3 keeps 3
+                # significand bits (<= 6 % per element), int8 7 bits
+                assert err < (3e-2 if int8 else 6e-2), (name, M, err)
             iters = 200 if M == 64 else 30
             t_all = timed(lambda: layer(x), iters)
             t_mm = timed(lambda: method.apply(layer, x, None), iters)

@@ -47,6 +47,25 @@ struct BlockwiseParams {
   int debug_flags;           // 1 = no MMAs, 2 = no promotion arithmetic (handshakes only)
 };
 
+// acc[0..n) += x[0..n) * scale with the packed fp32x2 FMA of sm_100 (two IEEE fma.rn per issue slot; the result of
+// each lane is exactly that of a scalar fma.rn, so the promotion arithmetic is unchanged).  The promotion warps are
+// issue-bound -- 64 FMAs per thread per K block against a 256-clock MMA -- and this halves their FMA slots.
+template <int N>
+B2_DEVICE void promote_fma2(float (&acc)[64], int base, const uint32_t (&x)[32], float scale) {
+  uint64_t s2;
+  asm("mov.b64 %0, {%1, %1};" : "=l"(s2) : "f"(scale));
+#pragma unroll
+  for (int j = 0; j < N; j += 2) {
+    asm("{\n\t.reg .b64 xx, cc;\n\t"
+        "mov.b64 xx, {%2, %3};\n\t"
+        "mov.b64 cc, {%0, %1};\n\t"
+        "fma.rn.f32x2 cc, xx, %4, cc;\n\t"
+        "mov.b64 {%0, %1}, cc;\n\t}"
+        : "+f"(acc[base + j]), "+f"(acc[base + j + 1])
+        : "r"(x[j]), "r"(x[j + 1]), "l"(s2));
+  }
+}
+
 B2_DEVICE void bw_tile_coords(int tile, const BlockwiseParams& p, int& m_blk, int& n_blk) {
   const int fast_blocks = p.band_n ? p.num_n_blocks : p.num_m_blocks;
   const int slow_blocks = p.band_n ? p.num_m_blocks : p.num_n_blocks;
@@ -332,13 +351,11 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
             else mbar_arrive_cluster(&part_empty[ita & (BW_SLOTS - 1)], 0);
           }
           if (!(p.debug_flags & 2)) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) acc[j] = __fmaf_rn(__uint_as_float(r0[j]), scale_a, acc[j]);
+            promote_fma2<32>(acc, 0, r0, scale_a);
           }
           if (two) tmem_ld_32x32b_x32(t_lane + col_b, r0);
           if (!(p.debug_flags & 2)) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) acc[32 + j] = __fmaf_rn(__uint_as_float(r1[j]), scale_a, acc[32 + j]);
+            promote_fma2<32>(acc, 32, r1, scale_a);
           }
           if (two) {
             tmem_ld_32x32b_x32(t_lane + col_b + 32, r1);
@@ -350,10 +367,8 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
               else mbar_arrive_cluster(&part_empty[itb & (BW_SLOTS - 1)], 0);
             }
             if (!(p.debug_flags & 2)) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) acc[j] = __fmaf_rn(__uint_as_float(r0[j]), scale_b, acc[j]);
-#pragma unroll
-              for (int j = 0; j < 32; ++j) acc[32 + j] = __fmaf_rn(__uint_as_float(r1[j]), scale_b, acc[32 + j]);
+              promote_fma2<32>(acc, 0, r0, scale_b);
+              promote_fma2<32>(acc, 32, r1, scale_b);
             }
           }
           it += two ? 2 : 1;

@@ -366,8 +366,12 @@ def main():
         ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ee0.record()
         for _ in range(e2e_steps):
+            # the layers of a step are independent problems (as in the device-resident step above): enqueue all of
+            # them, then collect -- uploads of one layer run under the downloads of another
             for hl, xh, oh in host_layers:
-                hl(xh, oh)
+                hl.submit(xh, oh)
+            for hl, _, _ in host_layers:
+                hl.wait()
         ee1.record()
         barrier()
         e2e_ms = max(ee0.elapsed_time(ee1), 0.0)

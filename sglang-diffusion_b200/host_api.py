@@ -45,6 +45,20 @@ class HostW8A8Int8Linear:
     def __call__(self, x_host: torch.Tensor, out_host: torch.Tensor) -> torch.Tensor:
         """x_host [M,K] and out_host [M,N]: CPU tensors (pinned for full PCIe speed).  Returns out_host
         after everything has landed (the call synchronises its own streams, nothing else)."""
+        self.submit(x_host, out_host)
+        return self.wait()
+
+    def wait(self) -> torch.Tensor:
+        """Block until the outputs of the last submit() are in host memory."""
+        self.s_out.synchronize()
+        return self._last_out
+
+    def submit(self, x_host: torch.Tensor, out_host: torch.Tensor) -> None:
+        """Enqueue the whole call (copies in, quantize + GEMM, copies out) on this layer's own streams and return
+        at once.  Independent layers submitted back to back share the link in both directions -- one layer's
+        uploads run under another's downloads -- which a caller with several linears over host-resident
+        activations (QKV / gate_up of one token batch) gets for free; wait() then collects each.  One submit may be
+        in flight per layer object (the staging buffers are per layer): wait() before the next submit()."""
         assert x_host.device.type == "cpu" and out_host.device.type == "cpu"
         assert x_host.dtype == self.act_dtype and out_host.dtype == self.act_dtype
         M = x_host.shape[0]
@@ -84,7 +98,6 @@ class HostW8A8Int8Linear:
                 ev = torch.cuda.Event()
                 ev.record(self.s_out)
                 out_done.append(ev)
-        self.s_out.synchronize()
         self.h2d_bytes += x_host.numel() * x_host.element_size()
         self.d2h_bytes += out_host.numel() * out_host.element_size()
-        return out_host
+        self._last_out = out_host

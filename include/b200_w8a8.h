@@ -148,7 +148,9 @@ const char* b2_last_gemm_config(void);
  *                    post, words [1024, 1024 + max_blocks) this rank's per-CTA barrier counters (device-resident so
  *                    that CUDA-graph replays advance them); nothing is reset between calls.
  *   multicast_ptr    NVSwitch multicast mapping of the buffer, or NULL (then only the one-shot path is available)
- *   out              private [numel] output of this rank (16-byte aligned), dtype bf16 / f16 like the buffers
+ *   out              private [numel] output of this rank (16-byte aligned), dtype bf16 / f16 like the buffers; NULL =
+ *                    in place: the sums stay in the symmetric buffer only (two-shot path; saves the copy for
+ *                    prefill-sized messages when the consumer is the next kernel of the same stream)
  *   algo             0 auto (two-shot when multicast_ptr), 1 one-shot peer loads (fp32 sum in rank order, bit-identical
  *                    on every rank), 2 two-shot multimem.ld_reduce / multimem.st (the switch adds in fp32)
  * The host side only has to allocate and exchange the mappings (torch.distributed._symmetric_memory in

@@ -43,7 +43,7 @@ class SymmAllReduce:
         # signal pad layout of csrc/allreduce_symm.cu: words [0, world * blocks) flags, [1024, 1024 + blocks) counters
         if int(self.handle.signal_pad_size) < 8192:
             raise ValueError("signal pad smaller than the 8 KiB b2_allreduce_symm needs")
-        self.max_blocks = min(64, 1024 // self.world)
+        self.max_blocks = min(128, 1024 // self.world)
 
     def partial(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
         """[M,N] view of the local symmetric buffer: the GEMM's output operand."""
@@ -55,12 +55,13 @@ class SymmAllReduce:
     def fits(self, M: int, N: int, dtype: torch.dtype) -> bool:
         return dtype in _DT and M * N * dtype.itemsize <= self.max_bytes and (M * N) % 8 == 0 and M * N > 0
 
-    def all_reduce(self, partial: torch.Tensor, algo: int = 0) -> torch.Tensor:
+    def all_reduce(self, partial: torch.Tensor, algo: int = 0, inplace: bool = False) -> torch.Tensor:
         """Sum of `partial` (a tensor returned by .partial(), already written by this rank's GEMM on the current
-        stream) over the ranks; returns a fresh private tensor.  Collective: every rank calls it."""
-        out = torch.empty(partial.shape, dtype=partial.dtype, device=partial.device)
+        stream) over the ranks; returns a fresh private tensor, or -- inplace=True, multicast only -- `partial`
+        itself holding the sums (valid until the next call that uses this buffer).  Collective: every rank calls it."""
+        out = None if inplace else torch.empty(partial.shape, dtype=partial.dtype, device=partial.device)
         stream = torch.cuda.current_stream(partial.device).cuda_stream
-        capi.check(capi.lib.b2_allreduce_symm(self.bufs_dev, self.pads_dev, self.multicast_ptr or None, out.data_ptr(),
-                                              partial.numel(), _DT[partial.dtype], self.rank, self.world, algo,
-                                              self.max_blocks, stream))
-        return out
+        capi.check(capi.lib.b2_allreduce_symm(self.bufs_dev, self.pads_dev, self.multicast_ptr or None,
+                                              None if inplace else out.data_ptr(), partial.numel(),
+                                              _DT[partial.dtype], self.rank, self.world, algo, self.max_blocks, stream))
+        return partial if inplace else out

@@ -138,14 +138,31 @@ __global__ void __launch_bounds__(512) allreduce_two_shot_kernel(uint4* const* b
   xgpu_barrier<false>(pads, rank, world, epoch + 1);  // every rank's GEMM has written its partials (stream order)
   const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
   const long long lane0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  for (long long v = lane0 + stride * rank; v < nvec; v += stride * world) {
-    const uint4 sum = multimem_ld_reduce_add<BF16>(mc + v);
-    multimem_st(mc + v, sum);
+  // four independent switch reductions in flight per thread: large (prefill) messages are NVLink-latency x
+  // bytes-in-flight bound, not issue bound
+  const long long step = stride * world;
+  for (long long v = lane0 + stride * rank; v < nvec; v += 4 * step) {
+    uint4 sum[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (v + u * step < nvec) sum[u] = multimem_ld_reduce_add<BF16>(mc + v + u * step);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (v + u * step < nvec) multimem_st(mc + v + u * step, sum[u]);
   }
   xgpu_barrier<true>(pads, rank, world, epoch + 2);  // the sums of every slice have landed in this rank's buffer
   if (threadIdx.x == 0) pads[rank][kEpochWord + blockIdx.x] = epoch + 2;
+  if (out == nullptr) return;  // in place: the caller consumes the sums from its symmetric buffer
   const uint4* mine = bufs[rank];
-  for (long long v = lane0; v < nvec; v += stride) out[v] = mine[v];
+  for (long long v = lane0; v < nvec; v += 4 * stride) {
+    uint4 t[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (v + u * stride < nvec) t[u] = mine[v + u * stride];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (v + u * stride < nvec) out[v + u * stride] = t[u];
+  }
   // no trailing barrier: a peer can only overwrite this rank's buffer through a later multimem.st, which sits
   // behind the first barrier of the NEXT call, and that barrier needs this CTA to have left this kernel
 }
@@ -178,18 +195,21 @@ using namespace b2;
 extern "C" int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* signal_pads_dev, void* multicast_ptr,
                                  void* out, int64_t numel, int dtype, int rank, int world, int algo,
                                  int max_blocks, b2_stream_t stream) {
-  if (!peer_bufs_dev || !signal_pads_dev || !out) return fail_msg(B2_ERR_ARG, "allreduce_symm: null pointer");
+  if (!peer_bufs_dev || !signal_pads_dev) return fail_msg(B2_ERR_ARG, "allreduce_symm: null pointer");
   if (dtype != B2_DTYPE_BF16 && dtype != B2_DTYPE_F16)
     return fail_msg(B2_ERR_ARG, "allreduce_symm: dtype must be bfloat16 or float16");
   if (world < 2 || world > 8 || rank < 0 || rank >= world)
     return fail_msg(B2_ERR_ARG, "allreduce_symm: world size must be 2..8 (one NVSwitch domain), rank inside it");
   if (numel <= 0 || numel % 8 != 0) return fail_msg(B2_ERR_ARG, "allreduce_symm: numel must be a positive multiple of 8");
   if (reinterpret_cast<uintptr_t>(out) % 16 != 0) return fail_msg(B2_ERR_ARG, "allreduce_symm: out must be 16-byte aligned");
+  if (!out && (algo == 1 || !multicast_ptr))
+    return fail_msg(B2_ERR_ARG, "allreduce_symm: in-place (out == NULL) needs the two-shot multicast path");
   if (algo == 2 && !multicast_ptr) return fail_msg(B2_ERR_ARG, "allreduce_symm: two-shot needs a multicast pointer");
   const long long nvec = numel / 8;
   // auto (measured, profiles/r01d_symm_allreduce_{2,8}gpu.log): the switch reduction wins at every size on 8 ranks
-  // (1 MB: 15 us vs 33 us one-shot vs 34 us NCCL); between two ranks the ordered peer loads are ahead up to ~2 MB
-  const bool two_shot = algo == 2 || (algo == 0 && multicast_ptr != nullptr && (world > 2 || numel * 2 > (2ll << 20)));
+  // (1 MB: 15 us vs 33 us one-shot vs 34 us NCCL); between two ranks the ordered peer loads are ahead up to 4 MB+
+  const bool two_shot =
+      algo == 2 || !out || (algo == 0 && multicast_ptr != nullptr && (world > 2 || numel * 2 > (8ll << 20)));
   const int threads = 512;
   // per-CTA flags: world u32 per block in every rank's signal pad; the host says how many blocks the pad can take
   long long blocks = (nvec + threads - 1) / threads;

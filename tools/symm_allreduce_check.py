@@ -23,7 +23,8 @@ local = int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
-comm = SymmAllReduce(max_bytes=4 << 20, device=dev)
+BIG = "--big" in sys.argv  # also time prefill-sized messages (needs a 128 MiB symmetric buffer)
+comm = SymmAllReduce(max_bytes=(128 << 20) if BIG else (4 << 20), device=dev)
 algos = [1] + ([2] if comm.multicast_ptr else [])
 fails = 0
 
@@ -58,6 +59,16 @@ for dtype in (torch.bfloat16, torch.float16):
             if not (ok and same):
                 fails += 1
                 print(f"[rank {rank}] FAIL dtype={dtype} M={M} N={N} algo={algo} ok={ok} same_on_all_ranks={same}", flush=True)
+
+if comm.multicast_ptr:  # in place: the sums are left in the symmetric buffer itself
+    part = comm.partial(64, 8192, torch.bfloat16)
+    part.copy_(torch.randn(64, 8192, device=dev).bfloat16())
+    acc32, _ = exact_sum(part)
+    got = comm.all_reduce(part, 2, inplace=True)
+    torch.cuda.synchronize()
+    if got.data_ptr() != part.data_ptr() or not bool(((got.float() - acc32).abs() <= torch.finfo(torch.bfloat16).eps * acc32.abs().clamp_min(1e-3)).all()):
+        fails += 1
+        print(f"[rank {rank}] FAIL in-place two-shot", flush=True)
 
 # flag reuse: many calls back to back, new data every time, checked at the end through a running checksum
 for algo in algos:
@@ -104,13 +115,15 @@ def timed(fn, inner=20, reps=20):
     return float(t.item()) * 1e3
 
 
-for M, N in ((1, 4096), (16, 8192), (64, 8192), (256, 8192)):
+for M, N in ((1, 4096), (16, 8192), (64, 8192), (256, 8192)) + (((2048, 8192), (8192, 8192)) if BIG else ()):
     part = comm.partial(M, N, torch.bfloat16)
     part.normal_()
     nccl_buf = part.clone()
     row = {"world": world, "bytes": M * N * 2, "us_nccl": round(timed(lambda: dist.all_reduce(nccl_buf)), 2)}
-    for algo in algos:
+    for algo in (algos if M <= 256 else [a for a in algos if a == 2]):
         row["us_one_shot_p2p" if algo == 1 else "us_two_shot_multimem"] = round(timed(lambda: comm.all_reduce(part, algo)), 2)
+    if comm.multicast_ptr:
+        row["us_two_shot_multimem_inplace"] = round(timed(lambda: comm.all_reduce(part, 2, inplace=True)), 2)
     if rank == 0:
         print(json.dumps(row), flush=True)
 

@@ -163,7 +163,9 @@ int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* signal_pads_d
  * loaded once).  Decode-shape GEMMs (M <= 128) are then launched with programmatic dependent launch: their CTAs
  * start while the preceding kernel (normally this library's quantizer, which releases its dependents at once) is
  * still running, request their first ring of WEIGHT tiles, and only then wait for that kernel before touching the
- * activations, the scales or the output.  Results are identical; only the launch overlap changes.  The linear
+ * activations, the scales or the output.  The row quantizers (M <= 128) are launched programmatically as well and wait
+ * for their own predecessor before they touch memory, so a whole quantizer -> GEMM -> quantizer -> GEMM chain overlaps.
+ * Results are identical; only the launch overlap changes.  The linear
  * methods of the host package (weights are module parameters) turn it on around their calls. */
 void b2_set_weight_prefetch(int enabled);
 int b2_get_weight_prefetch(void);

@@ -116,6 +116,9 @@ __global__ void __launch_bounds__(BLOCK) quant_rows_kernel(const T* __restrict__
   // follows starts fetching its weights while these rows are quantized, and waits for this grid's completion
   // (griddepcontrol.wait) before it reads the codes or the scales.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  // ... and, when this kernel was itself launched programmatically, wait for its own predecessor before reading x or
+  // writing q / s (a no-op under an ordinary launch)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   const int r_in_cta = threadIdx.x / TPR;
   const int t = threadIdx.x % TPR;
@@ -217,9 +220,20 @@ static cudaError_t launch_rows(const void* x, int64_t ldx, uint8_t* q, int64_t l
   constexpr int NCACHE = 8;
   constexpr int ROWS = BLOCK / TPR;
   const int grid = (M + ROWS - 1) / ROWS;
-  quant_rows_kernel<T, MODE, VEC, TPR, BLOCK, NCACHE>
-      <<<grid, BLOCK, 0, st>>>(static_cast<const T*>(x), ldx, q, ldq, s, M, K);
-  return cudaGetLastError();
+  // Decode chains (b2_set_weight_prefetch): the quantizer itself is launched programmatically, so its launch latency
+  // overlaps the tail of the kernel before it; it waits for that kernel (griddepcontrol.wait) before it touches memory.
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(BLOCK);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (weight_prefetch_enabled() && M <= 128) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, quant_rows_kernel<T, MODE, VEC, TPR, BLOCK, NCACHE>, static_cast<const T*>(x), ldx,
+                            q, ldq, s, M, K);
 }
 
 template <typename T, QMode MODE, int VEC>

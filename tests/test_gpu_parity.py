@@ -227,6 +227,47 @@ def test_static_weight_prefetch_chain_is_bit_identical(graph):
         assert torch.equal(a.view(torch.int16), b.view(torch.int16))
 
 
+@pytest.mark.parametrize("graph", [False, True])
+def test_static_weight_chain_with_data_dependent_layers(graph):
+    """Each layer's activations are the previous layer's output: the programmatically launched quantizer must wait
+    for the GEMM before it (griddepcontrol.wait) and the GEMM for its quantizer; any early read shows up as a
+    different bit pattern after 12 dependent layers."""
+    M, K = 16, 4096
+    g = torch.Generator().manual_seed(5)
+    x0 = (torch.randn(M, K, generator=g) / 10).bfloat16().to(DEV)
+    Ws = [torch.randint(-127, 128, (K, K), dtype=torch.int8, generator=g).to(DEV) for _ in range(4)]
+    Bs = [(torch.rand(K, generator=g) * 2e-4).to(DEV) for _ in range(4)]
+
+    def chain():
+        x = x0
+        for rep in range(3):
+            for W, b in zip(Ws, Bs):
+                q, s = b2.per_token_quant_int8(x)
+                x = b2.int8_scaled_mm(q, W.t(), s, b.view(-1, 1), torch.bfloat16, None)
+        return x
+
+    want = chain()
+    torch.cuda.synchronize()
+    assert torch.isfinite(want.float()).all() and want.float().abs().max() > 0
+    with capi.static_weights():
+        if graph:
+            st = torch.cuda.Stream()
+            st.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(st):
+                chain()
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr, stream=st):
+                    got = chain()
+            torch.cuda.current_stream().wait_stream(st)
+            for _ in range(3):
+                gr.replay()
+        else:
+            for _ in range(3):
+                got = chain()
+    torch.cuda.synchronize()
+    assert torch.equal(want.view(torch.int16), got.view(torch.int16))
+
+
 def test_gemm_s8_extreme_codes_do_not_saturate():
     """K = 16384 of (-128)*(-128) = 2.7e8 < 2^31: the accumulator must be exact, not saturated."""
     M, N, K = 130, 136, 16384

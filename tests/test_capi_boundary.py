@@ -98,3 +98,43 @@ def test_product_package_never_touches_the_oracle():
                 assert "restate" not in txt and "sgl_cpu_oracle" not in txt and "orc_" not in txt, f
     out = subprocess.check_output(["ldd", b2.capi.LIB_PATH], text=True)
     assert "oracle" not in out
+
+
+def test_static_weight_flag_is_scoped_and_thread_local():
+    """b2_set_weight_prefetch / capi.static_weights(): default off, restored on exit, nested scopes keep it on."""
+    from sglang_diffusion_b200 import capi
+
+    assert capi.lib.b2_get_weight_prefetch() == 0
+    with capi.static_weights():
+        assert capi.lib.b2_get_weight_prefetch() == 1
+        with capi.static_weights():
+            assert capi.lib.b2_get_weight_prefetch() == 1
+        assert capi.lib.b2_get_weight_prefetch() == 1
+    assert capi.lib.b2_get_weight_prefetch() == 0
+    import threading
+
+    seen = []
+    with capi.static_weights():
+        t = threading.Thread(target=lambda: seen.append(capi.lib.b2_get_weight_prefetch()))
+        t.start()
+        t.join()
+    assert seen == [0]
+
+
+def test_allreduce_symm_rejects_bad_arguments_without_touching_the_gpu():
+    """Argument validation of b2_allreduce_symm happens before any CUDA call (status code + b2_last_error)."""
+    import ctypes
+
+    from sglang_diffusion_b200 import capi
+
+    buf = (ctypes.c_void_p * 8)()
+    p = ctypes.cast(buf, ctypes.c_void_p)
+    f = capi.lib.b2_allreduce_symm
+    assert f(None, p, None, p, 1024, capi.DTYPE_BF16, 0, 2, 0, 64, None) == -1  # B2_ERR_ARG
+    assert "null pointer" in capi.last_error()
+    assert f(p, p, None, p, 1024, capi.DTYPE_F32, 0, 2, 0, 64, None) != 0 and "bfloat16 or float16" in capi.last_error()
+    assert f(p, p, None, p, 1024, capi.DTYPE_BF16, 0, 1, 0, 64, None) != 0 and "world size" in capi.last_error()
+    assert f(p, p, None, p, 1024, capi.DTYPE_BF16, 9, 8, 0, 64, None) != 0
+    assert f(p, p, None, p, 1001, capi.DTYPE_BF16, 0, 2, 0, 64, None) != 0 and "multiple of 8" in capi.last_error()
+    assert f(p, p, None, p, 1024, capi.DTYPE_BF16, 0, 2, 2, 64, None) != 0 and "multicast" in capi.last_error()
+    assert f(p, p, None, None, 1024, capi.DTYPE_BF16, 0, 2, 0, 64, None) != 0 and "in-place" in capi.last_error()

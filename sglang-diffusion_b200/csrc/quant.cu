@@ -231,7 +231,11 @@ static cudaError_t launch_rows(const void* x, int64_t ldx, uint8_t* q, int64_t l
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = (weight_prefetch_enabled() && M <= 128) ? 1 : 0;
+  static const bool chain_quantizer = [] {  // developer A/B switch: B2_QUANT_PDL=0 launches the quantizer plainly
+    const char* e = getenv("B2_QUANT_PDL");
+    return !(e && e[0] == '0');
+  }();
+  cfg.numAttrs = (chain_quantizer && weight_prefetch_enabled() && M <= 128) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, quant_rows_kernel<T, MODE, VEC, TPR, BLOCK, NCACHE>, static_cast<const T*>(x), ldx,
                             q, ldq, s, M, K);
 }

@@ -669,3 +669,28 @@ def test_launch_counter_counts_our_kernels():
     capi.reset_launch_count()
     b2.int8_scaled_mm_with_quant(x.to(DEV), W.to(DEV), Bs.to(DEV), None, torch.bfloat16, False)
     assert capi.launch_count() == 2  # quantizer + GEMM
+
+
+# ====================================================== host-buffer pipeline ====
+
+@pytest.mark.parametrize("M,chunk", [(1, 64), (130, 64), (1000, 256), (2048, 1024)])
+def test_host_buffer_pipeline_matches_device_path_bitwise(M, chunk):
+    """HostW8A8Int8Linear (the e2e entry bench.py times): host activations in, host outputs out, chunked through
+    three streams with double-buffered staging -- ragged last chunk, single-row batch, two layers in flight at once
+    (submit / wait) -- equals the device-resident op bit for bit."""
+    layers = []
+    for i, (K, N) in enumerate(((1024, 1536), (2048, 512))):
+        x, W, Bs, bias = mk_int8_problem(M, N, K, seed=M + i)
+        hl = b2.HostW8A8Int8Linear(W, Bs, bias, device=DEV, chunk_rows=chunk)
+        out_host = torch.empty(M, N, dtype=torch.bfloat16).pin_memory()
+        layers.append((hl, x.pin_memory(), out_host, W, Bs, bias))
+    for _ in range(2):  # second round reuses the staging buffers
+        for hl, xh, oh, *_ in layers:
+            hl.submit(xh, oh)
+        for hl, *_ in layers:
+            hl.wait()
+    for hl, xh, oh, W, Bs, bias in layers:
+        want = b2.int8_scaled_mm_with_quant(xh.to(DEV), W.to(DEV), Bs.to(DEV), bias.to(DEV), torch.bfloat16, False)
+        assert torch.equal(oh.view(torch.int16), want.cpu().view(torch.int16))
+        assert hl(xh, oh) is oh  # the blocking form
+        assert torch.equal(oh.view(torch.int16), want.cpu().view(torch.int16))

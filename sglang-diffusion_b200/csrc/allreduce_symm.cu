@@ -134,6 +134,8 @@ template <bool BF16>
 __global__ void __launch_bounds__(512) allreduce_two_shot_kernel(uint4* const* bufs, uint32_t* const* pads,
                                                                   uint4* mc, uint4* out, long long nvec, int rank,
                                                                   int world) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // the next quantizer may come up; it waits for us
+  asm volatile("griddepcontrol.wait;" ::: "memory");               // this rank's GEMM (and everything before it) is done
   const uint32_t epoch = pads[rank][kEpochWord + blockIdx.x];
   xgpu_barrier<false>(pads, rank, world, epoch + 1);  // every rank's GEMM has written its partials (stream order)
   const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
@@ -170,6 +172,8 @@ __global__ void __launch_bounds__(512) allreduce_two_shot_kernel(uint4* const* b
 template <bool BF16>
 __global__ void __launch_bounds__(512) allreduce_one_shot_kernel(uint4* const* bufs, uint32_t* const* pads, uint4* out,
                                                                   long long nvec, int rank, int world) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const uint32_t epoch = pads[rank][kEpochWord + blockIdx.x];
   xgpu_barrier<false>(pads, rank, world, epoch + 1);
   const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
@@ -219,21 +223,31 @@ extern "C" int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* si
   if (blocks < 1) blocks = 1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   uint4* const* bufs = reinterpret_cast<uint4* const*>(peer_bufs_dev);
+  // Launched programmatically: the CTAs come up under the tail of the GEMM that produces the partials and wait for it
+  // (griddepcontrol.wait, first instruction) -- the launch latency is off the critical path of the decode step.
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(blocks));
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  uint4* mc = static_cast<uint4*>(multicast_ptr);
+  uint4* o = static_cast<uint4*>(out);
+  cudaError_t le;
   if (two_shot) {
-    if (dtype == B2_DTYPE_BF16)
-      allreduce_two_shot_kernel<true><<<static_cast<int>(blocks), threads, 0, st>>>(
-          bufs, signal_pads_dev, static_cast<uint4*>(multicast_ptr), static_cast<uint4*>(out), nvec, rank, world);
-    else
-      allreduce_two_shot_kernel<false><<<static_cast<int>(blocks), threads, 0, st>>>(
-          bufs, signal_pads_dev, static_cast<uint4*>(multicast_ptr), static_cast<uint4*>(out), nvec, rank, world);
+    le = dtype == B2_DTYPE_BF16
+             ? cudaLaunchKernelEx(&cfg, allreduce_two_shot_kernel<true>, bufs, signal_pads_dev, mc, o, nvec, rank, world)
+             : cudaLaunchKernelEx(&cfg, allreduce_two_shot_kernel<false>, bufs, signal_pads_dev, mc, o, nvec, rank, world);
   } else {
-    if (dtype == B2_DTYPE_BF16)
-      allreduce_one_shot_kernel<true><<<static_cast<int>(blocks), threads, 0, st>>>(
-          bufs, signal_pads_dev, static_cast<uint4*>(out), nvec, rank, world);
-    else
-      allreduce_one_shot_kernel<false><<<static_cast<int>(blocks), threads, 0, st>>>(
-          bufs, signal_pads_dev, static_cast<uint4*>(out), nvec, rank, world);
+    le = dtype == B2_DTYPE_BF16
+             ? cudaLaunchKernelEx(&cfg, allreduce_one_shot_kernel<true>, bufs, signal_pads_dev, o, nvec, rank, world)
+             : cudaLaunchKernelEx(&cfg, allreduce_one_shot_kernel<false>, bufs, signal_pads_dev, o, nvec, rank, world);
   }
+  if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm launch: %s", cudaGetErrorString(le));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm launch: %s", cudaGetErrorString(e));
   count_launch();

@@ -491,7 +491,9 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   // when N is too narrow to give the persistent kernel one tile per SM)
   // M in (32, 64]: still ahead on layers up to ~64 rows of W per SM (profiles/r01e_m64_probe.log: 9.4 vs 12.0 us on
   // 6144 x 4096, 15.7 vs 19.9 us on 7168 x 8192), behind on the widest ones where 128 x 256 persistent tiles stream well
-  const bool decode_shape = a.M <= 32 || (a.M <= 64 && a.N <= 64 * sms) || (a.M <= BM && a.N < 32 * sms);
+  // (short K -- 8 K-blocks -- leaves the decode kernel nothing to pipeline at M > 32: 8.2 vs 6.8 us on 8192 x 1024)
+  const bool decode_shape =
+      a.M <= 32 || (a.M <= 64 && a.N <= 64 * sms && a.K >= 2048) || (a.M <= BM && a.N < 32 * sms);
   if ((forced_config & 0x80000) ? a.M <= BM : ((forced_config & 0xff) == 0 && decode_shape))
     return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);
   const TileConfig* cfg = &pick_config(a.M, a.N, sms);

@@ -177,7 +177,7 @@ def test_decode_shapes_auto_plan_bitwise_vs_persistent_kernel(M, K, N):
     x, W, Bs, bias = x.to(DEV), W.to(DEV), Bs.to(DEV), bias.to(DEV)
     q, s = c_quant_int8(x)
     a = c_gemm_s8(q, W, s, Bs, bias)
-    assert capi.last_gemm_config().startswith("splitk_") == (M <= 32 or (M <= 64 and N <= 64 * 148) or N < 32 * 148)
+    assert capi.last_gemm_config().startswith("splitk_") == (M <= 32 or (M <= 64 and N <= 64 * 148 and K >= 2048) or N < 32 * 148)
     if not capi.last_gemm_config().startswith("splitk_"):
         a = c_gemm_s8(q, W, s, Bs, bias, cfg=splitk_cfg(1, 2))
     b = c_gemm_s8(q, W, s, Bs, bias, cfg=1)

@@ -104,6 +104,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     // ===================================================== TMA producer ====
     // the whole warp walks the ring (all lanes poll the barrier); one elected lane issues
     {
+      // static-weight launches (b2_set_weight_prefetch) start this kernel under the tail of the quantizer: barrier
+      // init, TMEM allocation and the cluster handshake above are already done when its codes become readable
+      pdl_wait_prior_grids();
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t tx_bytes = (static_cast<uint32_t>(p.a_box_rows) * BK + B_STAGE_BYTES) * CG;
@@ -203,6 +206,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     }
   } else {
     // ========================================================= epilogue ====
+    pdl_wait_prior_grids();        // scales come from, and the output may still be read by, the preceding kernels
     const int quarter = warp & 3;  // TMEM lane quarter this warp may read
     const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
     uint8_t* my_epi = smem_epi + static_cast<size_t>(warp - EPI_WARP0) * 2 * EPI_BUF_BYTES;
@@ -448,13 +452,15 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attrs[1];
+  cudaLaunchAttribute attrs[2];
   attrs[0].id = cudaLaunchAttributeClusterDimension;
   attrs[0].val.clusterDim.x = CG;
   attrs[0].val.clusterDim.y = 1;
   attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attrs;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = weight_prefetch_enabled() ? 2 : 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p);
   if (e != cudaSuccess) {
     snprintf(err, err_len, "gemm kernel launch: %s", cudaGetErrorString(e));

@@ -58,10 +58,6 @@ B2_DEVICE uint32_t ld_dsmem_u32(uint32_t local_addr, uint32_t cta) {
   return v;
 }
 
-// Programmatic dependent launch: no-ops unless the launch carries cudaLaunchAttributeProgrammaticStreamSerialization
-B2_DEVICE void pdl_wait_prior_grids() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-B2_DEVICE void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-
 B2_DEVICE uint4 ld_dsmem_v4(uint32_t local_addr, uint32_t cta) {
   uint4 v;
   asm volatile(

@@ -60,6 +60,10 @@ B2_DEVICE uint64_t globaltimer_ns() {
   return t;
 }
 
+// Programmatic dependent launch: no-ops unless the launch carries cudaLaunchAttributeProgrammaticStreamSerialization
+B2_DEVICE void pdl_wait_prior_grids() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+B2_DEVICE void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ------------------------------------------------------------- mbarrier ----
 
 B2_DEVICE void mbar_init(uint64_t* bar, uint32_t count) {

@@ -227,12 +227,14 @@ def test_static_weight_prefetch_chain_is_bit_identical(graph):
         assert torch.equal(a.view(torch.int16), b.view(torch.int16))
 
 
+@pytest.mark.parametrize("M", [16, 256])
 @pytest.mark.parametrize("graph", [False, True])
-def test_static_weight_chain_with_data_dependent_layers(graph):
+def test_static_weight_chain_with_data_dependent_layers(graph, M):
     """Each layer's activations are the previous layer's output: the programmatically launched quantizer must wait
     for the GEMM before it (griddepcontrol.wait) and the GEMM for its quantizer; any early read shows up as a
-    different bit pattern after 12 dependent layers."""
-    M, K = 16, 4096
+    different bit pattern after 12 dependent layers.  M = 16 runs the decode kernel, M = 256 the persistent one (also
+    launched programmatically under the static-weight declaration)."""
+    K = 4096
     g = torch.Generator().manual_seed(5)
     x0 = (torch.randn(M, K, generator=g) / 10).bfloat16().to(DEV)
     Ws = [torch.randint(-127, 128, (K, K), dtype=torch.int8, generator=g).to(DEV) for _ in range(4)]

@@ -395,6 +395,48 @@ def test_llama8b_shapes_m8192_checksum_and_sampled_rows(K, N):
     assert torch.equal(bf16_bits(out[rows.to(DEV)].cpu()), bf16_bits(ref))
 
 
+@pytest.mark.parametrize("K,N", [(5120, 5120), (5120, 13824), (13824, 5120), (3072, 9216), (3072, 12288), (12288, 3072),
+                                 (15360, 3072)])
+def test_dit_shapes_m32768_checksum_and_sampled_rows(K, N):
+    """C4 at the full diffusion token batch M = 32768 (Wan2.1-14B 5120/13824, FLUX.1 3072/9216/12288/15360): the column
+    checksum of the raw accumulators is exact and 32 sampled rows equal the CPU oracle bit for bit, bias included."""
+    M = 32768
+    g = torch.Generator(device=DEV).manual_seed(K * 3 + N)
+    x = (torch.randn(M, K, generator=g, device=DEV) / 10).bfloat16()
+    W = torch.randint(-128, 128, (N, K), dtype=torch.int8, generator=g, device=DEV)
+    Bs = torch.rand(N, generator=g, device=DEV) * 1e-2
+    bias = torch.randn(N, generator=g, device=DEV).bfloat16()
+    q, s = c_quant_int8(x)
+    acc = c_gemm_s8(q, W, None, None, None, torch.int32)
+    want = (q.double() @ W.double().sum(dim=0)).to(torch.int64)
+    assert torch.equal(acc.to(torch.int64).sum(dim=1), want)
+    del acc
+    out = b2.int8_scaled_mm(q, W.t(), s.view(-1, 1), Bs.view(-1, 1), torch.bfloat16, bias)
+    rows = torch.randperm(M, generator=torch.Generator().manual_seed(2))[:32].sort().values
+    ref = restate.int8_scaled_mm_with_quant(x[rows.to(DEV)].cpu(), W.cpu(), Bs.cpu(), bias.float().cpu())
+    assert torch.equal(bf16_bits(out[rows.to(DEV)].cpu()), bf16_bits(ref))
+
+
+@pytest.mark.parametrize("K,N", [(8192, 1280), (8192, 7168), (1024, 8192), (3584, 8192)])
+@pytest.mark.parametrize("M", [64, 8192])
+def test_llama70b_tp8_fp8_shards_sampled_rows(K, N, M):
+    """C5: the Llama-3-70B TP = 8 shard shapes at decode (M = 64, cluster split-K kernel) and prefill (M = 8192,
+    2-CTA kernel): fp8 codes and scales bit-exact against the oracle, 32 sampled output rows within the reference's
+    tolerance of the fp64 restatement."""
+    g = torch.Generator(device=DEV).manual_seed(K + N + M)
+    x = (torch.randn(M, K, generator=g, device=DEV) / 10).bfloat16()
+    Wq, ws = mk_fp8_weight(N, K)
+    xq, xs = b2.sglang_per_token_quant_fp8(x)
+    out = b2.fp8_scaled_mm(xq, Wq.to(DEV).t(), xs, ws.to(DEV), torch.bfloat16, None)
+    rows = torch.randperm(M, generator=torch.Generator().manual_seed(3))[:32].sort().values
+    q_ref, s_ref = restate.per_token_quant_fp8(x[rows.to(DEV)].cpu())
+    assert torch.equal(xq[rows.to(DEV)].cpu().view(torch.uint8), q_ref)
+    assert torch.equal(xs[rows.to(DEV)].cpu().view(-1).view(torch.int32), s_ref.view(-1).view(torch.int32))
+    ref = restate.fp8_scaled_mm(q_ref, Wq.view(torch.uint8), s_ref, ws, None)
+    got = out[rows.to(DEV)].float().cpu()
+    torch.testing.assert_close(got, ref, rtol=1e-2, atol=1e-2 * ref.abs().max().item())
+
+
 def test_m_sharded_rows_equal_unsharded_bitwise():
     """C4 (DiT, Wan2.1 hidden 5120): splitting M over ranks changes nothing -- rows are independent."""
     M, K, N = 4096, 5120, 5120

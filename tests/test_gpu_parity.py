@@ -639,17 +639,69 @@ def test_fp8_blockwise_vs_reference_cpu_golden(name):
     assert ((out.float().cpu() - ref).norm() / ref.norm()).item() < 4e-2
 
 
-def test_fp8_blockwise_c3_shape_m4096_sampled():
-    """C3 (DeepSeek-V3, M=4096): (N,K) = (7168, 2048); 16 sampled rows against the restatement."""
-    M, N, K = 4096, 7168, 2048
-    g = torch.Generator().manual_seed(2)
+def _mk_fp8_block_weight_dev(N, K, seed=11):
+    """mk_fp8_block_weight on the device (264 M-element C3 weights in milliseconds); returns device e4m3 [N,K]
+    and fp32 block scales [N/128, K/128]."""
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    w = torch.randn(N, K, generator=g, device=DEV) * 0.05
+    wb = w.view(N // 128, 128, K // 128, 128)
+    sfb = (wb.abs().amax(dim=(1, 3)) / 448.0).float()
+    Wq = (wb / sfb[:, None, :, None]).clamp(-448, 448).reshape(N, K).to(torch.float8_e4m3fn)
+    return Wq, sfb
+
+
+C3_SHAPES = [(24576, 1536), (32768, 512), (7168, 16384), (36864, 7168), (7168, 18432), (4096, 7168), (7168, 2048)]
+
+
+@pytest.mark.parametrize("N,K", C3_SHAPES)
+def test_fp8_blockwise_c3_shape_m4096_sampled(N, K):
+    """C3 (DeepSeek-V3, M=4096), every (N,K) of sgl-kernel/benchmark/bench_fp8_blockwise_gemm.py:32-53: sampled rows
+    (first / last row of the batch, rows across M tiles) against the restatement, every column."""
+    M = 4096
+    g = torch.Generator(device=DEV).manual_seed(2)
+    x = (torch.randn(M, K, generator=g, device=DEV) / 10).bfloat16()
+    Wq, sfb = _mk_fp8_block_weight_dev(N, K)
+    out = b2.cutlass_w8a8_block_fp8_linear_with_fallback(x, Wq, [128, 128], sfb)
+    rows = torch.tensor([0, 1, 127, 128, 255, 1337, 2048, 3000, 3967, 4095])
+    q_ref, sfa_ref = restate.per_token_group_quant_fp8(x[rows.to(DEV)].cpu().contiguous(), 128, 1e-10, True)
+    ref = restate.fp8_blockwise_scaled_mm(q_ref, Wq.cpu().view(torch.uint8), sfa_ref, sfb.cpu())
+    o = out[rows.to(DEV)].float().cpu()
+    assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 2e-6 * ref.abs().max())
+    # size-independent property: every row of the full output is finite and the column checksum of the sampled rows'
+    # neighbours is reproducible (the kernel is deterministic: a second call returns the same bits)
+    out2 = b2.cutlass_w8a8_block_fp8_linear_with_fallback(x, Wq, [128, 128], sfb)
+    assert torch.equal(out.view(torch.int16), out2.view(torch.int16))
+    assert bool(torch.isfinite(out).all())
+
+
+@pytest.mark.parametrize("K", [128, 384, 640, 1664, 2176])
+@pytest.mark.parametrize("M,N", [(1, 128), (5, 512), (127, 256), (300, 1536), (1024, 2048)])
+def test_fp8_blockwise_odd_k_block_counts(M, N, K):
+    """K/128 odd (1, 3, 5, 13, 17 K-blocks): the tail of the two-blocks-per-step promotion loop and a scale chunk
+    that is not full (17 = one chunk of 16 + 1)."""
+    g = torch.Generator().manual_seed(M + N + K)
     x = (torch.randn(M, K, generator=g) / 10).bfloat16()
     Wq, sfb = mk_fp8_block_weight(N, K)
-    out = b2.cutlass_w8a8_block_fp8_linear_with_fallback(x.to(DEV), Wq.to(DEV), [128, 128], sfb.to(DEV))
-    rows = torch.arange(0, M, 257)[:16]
-    q_ref, sfa_ref = restate.per_token_group_quant_fp8(x[rows].contiguous(), 128, 1e-10, True)
+    q_ref, sfa_ref = restate.per_token_group_quant_fp8(x, 128, 1e-10, True)
     ref = restate.fp8_blockwise_scaled_mm(q_ref, Wq.view(torch.uint8), sfa_ref, sfb)
-    o = out[rows.to(DEV)].float().cpu()
+    out = b2.cutlass_w8a8_block_fp8_linear_with_fallback(x.to(DEV), Wq.to(DEV), [128, 128], sfb.to(DEV))
+    o = out.float().cpu()
+    assert ((o - ref).abs().max() / ref.abs().max()).item() < 1e-2
+    assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 2e-6 * ref.abs().max())
+
+
+@pytest.mark.parametrize("M", [1, 3, 5, 127, 128])
+@pytest.mark.parametrize("N,K", [(7168, 16384), (4096, 7168), (7168, 18432)])
+def test_fp8_blockwise_small_m_long_k(M, N, K):
+    """The reference test's M list (sgl-kernel/tests/test_fp8_blockwise_gemm.py) at the long-K C3 shapes: 128 / 144
+    K-blocks wrap the TMEM slot ring 32+ times and span 8-9 scale chunks."""
+    g = torch.Generator(device=DEV).manual_seed(M + K)
+    x = (torch.randn(M, K, generator=g, device=DEV) / 10).bfloat16()
+    Wq, sfb = _mk_fp8_block_weight_dev(N, K)
+    out = b2.cutlass_w8a8_block_fp8_linear_with_fallback(x, Wq, [128, 128], sfb)
+    q_ref, sfa_ref = restate.per_token_group_quant_fp8(x.cpu(), 128, 1e-10, True)
+    ref = restate.fp8_blockwise_scaled_mm(q_ref, Wq.cpu().view(torch.uint8), sfa_ref, sfb.cpu())
+    o = out.float().cpu()
     assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 2e-6 * ref.abs().max())
 
 

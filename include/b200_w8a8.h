@@ -78,6 +78,52 @@ int b2_quant_fp8_group128(const void* x, int x_dtype, int64_t ldx, uint8_t* q, i
                           int64_t s_row_stride, int64_t s_grp_stride, int M, int K, float eps, float fp8_min,
                           float fp8_max, b2_stream_t stream);
 
+/* per_token_quant_int8(x, cal_sum=True) of python/sglang/srt/layers/quantization/int8_kernel.py:46-89 (QoQ): the
+ * int8 row quantizer above plus row_sum[m] = sum_k x[m,k] (fp32 accumulation, stored in x's dtype).
+ * Requires K % 8 == 0 and 16-byte aligned rows. */
+int b2_quant_int8_rows_sum(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s, void* row_sum,
+                           int M, int K, b2_stream_t stream);
+
+/* sgl_per_tensor_quant_fp8 (sgl-kernel/csrc/gemm/per_tensor_quant_fp8.cu:98-123) and static_quant_fp8
+ * (python/sglang/srt/layers/quantization/fp8_kernel.py:649-700): q = e4m3(clamp(x * (1/s), +-448)) over `numel`
+ * contiguous elements.  is_static == 0: s[0] (zeroed by the caller, fp8_kernel.py:1671) first receives max|x|/448
+ * (two launches); is_static != 0: s[0] is read.  s_repeat (optional, [rows]) receives s once per token row -- the
+ * repeat_scale=True form that feeds the per-token GEMM epilogue (fp8_utils.py:1232-1239). */
+int b2_quant_fp8_tensor(const void* x, int x_dtype, uint8_t* q, float* s, float* s_repeat, int64_t numel, int64_t rows,
+                        int is_static, b2_stream_t stream);
+
+/* ---- producer-fused quantizers ---------------------------- */
+
+#define B2_QMODE_INT8_ROWS 0       /* per-token int8, arithmetic of b2_quant_int8_rows; s[m] */
+#define B2_QMODE_FP8_ROWS 1        /* per-token e4m3, arithmetic of b2_quant_fp8_rows; s[m] */
+#define B2_QMODE_FP8_GROUP128 2    /* 1x128 e4m3, arithmetic of b2_quant_fp8_group128 (s = amax/448, q = x/s) */
+#define B2_QMODE_FP8_GROUP128_V2 3 /* 1x128 e4m3, arithmetic of per_token_group_quant_8bit_v2.cu (s = amax*(1/448),
+                                      q = x*(448/amax)) */
+
+/* silu_and_mul fused into the quantizer: sgl_per_token_group_quant_8bit_v2(fuse_silu_and_mul=true)
+ * (sgl-kernel/csrc/gemm/per_token_group_quant_8bit_v2.cu:396-447; kernel :240-394).  x is [M, 2K] (gate | up);
+ * y = T(silu(gate)) * up in x's dtype T, then quantized with `qmode` (INT8_ROWS, FP8_ROWS or FP8_GROUP128_V2).
+ * Scale of (row m, group g) at s[e*s_exp_stride + t*s_row_stride + g*s_grp_stride] where (e, t) = divmod(m,
+ * tokens_per_expert) under the masked layout and (0, m) otherwise.  masked_m (optional, [E] int32): x is
+ * [E, tokens_per_expert, 2K] and only the first masked_m[e] tokens of expert e are processed.  y (optional) receives
+ * the activation rows themselves ([M, K], dtype T).  K % 8 == 0 (K % 128 == 0 for groups), K <= 32768. */
+int b2_silu_mul_quant(const void* x, int x_dtype, int64_t ldx, int qmode, uint8_t* q, int64_t ldq, float* s,
+                      int64_t s_row_stride, int64_t s_grp_stride, int64_t s_exp_stride, void* y, int64_t ldy,
+                      const int32_t* masked_m, int64_t tokens_per_expert, int64_t M, int K, b2_stream_t stream);
+
+/* (fused-add-)RMSNorm fused into the quantizer: sgl_kernel fused_add_rmsnorm / rmsnorm
+ * (sgl-kernel/csrc/elementwise/fused_add_rms_norm_kernel.cu; flashinfer norm.cuh FusedAddRMSNormKernel) followed by
+ * the activation quantizer of the next linear, in one pass.  residual (optional, in/out, [M,K]): s = x + residual is
+ * written back to it, as the reference op does; y = T((s * rsqrt(mean(s^2) + eps)) * weight) is quantized with
+ * `qmode` (INT8_ROWS, FP8_ROWS or FP8_GROUP128); y_out (optional) also receives y.  Same shape limits as above. */
+int b2_rmsnorm_quant(const void* x, int x_dtype, int64_t ldx, void* residual, int64_t ldr, const void* weight,
+                     float eps, int qmode, uint8_t* q, int64_t ldq, float* s, int64_t s_row_stride,
+                     int64_t s_grp_stride, void* y_out, int64_t ldy, int64_t M, int K, b2_stream_t stream);
+
+/* sgl_per_token_group_quant_8bit_v2 without fusion (same file, fuse_silu_and_mul = false), fp32 scales, G = 128. */
+int b2_quant_fp8_group128_v2(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s,
+                             int64_t s_row_stride, int64_t s_grp_stride, int64_t M, int K, b2_stream_t stream);
+
 /* ---- scaled GEMMs ---------------------------------------------------------- */
 
 /* int8_scaled_mm (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:663-747 -- which has NO
@@ -107,6 +153,16 @@ int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64
                           int64_t sfa_m_stride, int64_t sfa_k_stride, const float* sfb, int64_t sfb_n_stride,
                           int64_t sfb_k_stride, const void* bias, int bias_dtype, void* D, int64_t ldd,
                           int out_dtype, int M, int N, int K, b2_stream_t stream);
+
+/* bmm_fp8 (sgl-kernel/csrc/gemm/bmm_fp8.cu; flashinfer bmm_fp8_internal_cublaslt): for every batch b,
+ *     D[b] = out_t( a_scale * b_scale * f32(A[b] . W[b]^T) ),  A [batch, M, K] e4m3, W [batch, N, K] e4m3 (the
+ * reference passes B = W.transpose(-2,-1), "column major"), per-tensor fp32 device scalars a_scale / b_scale.
+ * workspace (>= b2_bmm_e4m3_workspace(M, N) bytes) holds the broadcast scale vectors of the shared epilogue. */
+size_t b2_bmm_e4m3_workspace(int M, int N);
+int b2_bmm_e4m3(const uint8_t* A, int64_t lda, int64_t a_batch_stride, const uint8_t* W, int64_t ldw,
+                int64_t w_batch_stride, const float* a_scale, const float* b_scale, void* D, int64_t ldd,
+                int64_t d_batch_stride, int out_dtype, int batch, int M, int N, int K, void* workspace,
+                size_t workspace_bytes, b2_stream_t stream);
 
 /* ---- fused linear ----------------------------------------------------------- */
 

@@ -16,6 +16,36 @@ cudaError_t quant_fp8_group128(const void* x, int x_dtype, int64_t ldx, uint8_t*
                                int64_t s_row_stride, int64_t s_grp_stride, int M, int K, float eps, float fmin,
                                float fmax, cudaStream_t st);
 
+cudaError_t quant_rows_int8_sum(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s,
+                                void* row_sum, int M, int K, cudaStream_t st);
+
+// quant_fused.cu
+struct FusedQuantArgs {
+  const void* x;      // [M, K] (NONE / RMSNORM) or [M, 2K] (SILU_MUL: gate | up)
+  int64_t ldx;
+  void* residual;     // RMSNORM: optional in/out residual rows
+  int64_t ldr;
+  const void* weight; // RMSNORM: [K], dtype of x
+  float eps;          // RMSNORM epsilon
+  void* y;            // optional: the produced row in x's dtype (what the unfused op would have stored)
+  int64_t ldy;
+  uint8_t* q;
+  int64_t ldq;
+  float* s;
+  int64_t s_row_stride, s_grp_stride, s_exp_stride;
+  const int32_t* masked_m;  // optional [E]: valid tokens per expert of an [E, T, ...] layout
+  int64_t tokens_per_expert;
+  int64_t M;          // rows (E * T for the masked layout)
+  int K;
+  float q_eps, fmin, fmax;  // group modes
+};
+// prod: 0 none, 1 silu_and_mul, 2 rmsnorm;  mode: 0 int8 rows, 1 fp8 rows, 2 fp8 1x128 (v1), 3 fp8 1x128 (v2)
+cudaError_t fused_quant_launch(int prod, int mode, int x_dtype, const FusedQuantArgs& a, cudaStream_t st);
+cudaError_t quant_fp8_tensor(const void* x, int x_dtype, uint8_t* q, float* s, float* s_repeat, int64_t n,
+                             int64_t rows, int is_static, cudaStream_t st);
+cudaError_t broadcast_scales(const float* a_scale, const float* b_scale, float* as, float* bs, int m, int n,
+                             cudaStream_t st);
+
 // gemm_sm100.cu
 struct GemmArgs {
   const void* A;   // [M,K] 8-bit, K contiguous

@@ -188,6 +188,107 @@ int b2_quant_fp8_group128(const void* x, int x_dtype, int64_t ldx, uint8_t* q, i
   return B2_OK;
 }
 
+int b2_quant_int8_rows_sum(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s, void* row_sum,
+                           int M, int K, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (int r = check_act_dtype(x_dtype, "per_token_quant_int8: input")) return r;
+  if (M < 0 || K <= 0 || !x || !q || !s || !row_sum || ldx < K || ldq < K)
+    return fail(B2_ERR_ARG, "per_token_quant_int8(cal_sum): bad arguments (M=%d K=%d)", M, K);
+  if (K % 8 != 0 || ldx % 8 != 0 || ldq % 8 != 0 || !aligned16(x) || (reinterpret_cast<uintptr_t>(q) & 7u))
+    return fail(B2_ERR_ARG, "per_token_quant_int8(cal_sum): K, ldx and ldq must be multiples of 8 and rows 16-byte aligned");
+  if (M == 0) return B2_OK;
+  if (int r = check_cuda(quant_rows_int8_sum(x, x_dtype, ldx, q, ldq, s, row_sum, M, K, static_cast<cudaStream_t>(stream)),
+                         "per_token_quant_int8(cal_sum) launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
+int b2_quant_fp8_tensor(const void* x, int x_dtype, uint8_t* q, float* s, float* s_repeat, int64_t numel, int64_t rows,
+                        int is_static, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (int r = check_act_dtype(x_dtype, "sgl_per_tensor_quant_fp8: input")) return r;
+  if (numel < 0 || rows < 0 || !x || !q || !s) return fail(B2_ERR_ARG, "sgl_per_tensor_quant_fp8: bad arguments");
+  if (!aligned16(x) || !aligned16(q)) return fail(B2_ERR_ARG, "sgl_per_tensor_quant_fp8: input and output must be 16-byte aligned");
+  if (numel == 0) return B2_OK;
+  if (int r = check_cuda(quant_fp8_tensor(x, x_dtype, q, s, s_repeat, numel, s_repeat ? rows : 0, is_static,
+                                          static_cast<cudaStream_t>(stream)),
+                         "sgl_per_tensor_quant_fp8 launch"))
+    return r;
+  count_launch();  // the absmax pass of the dynamic form counted itself
+  return B2_OK;
+}
+
+static int check_fused_common(const char* op, const void* x, int x_dtype, int64_t ldx, int64_t row_elems, const void* q,
+                              int64_t ldq, const void* s, int qmode, int64_t M, int K) {
+  if (int r = check_arch()) return r;
+  if (x_dtype != B2_DTYPE_BF16 && x_dtype != B2_DTYPE_F16) return fail(B2_ERR_ARG, "%s: input must be bfloat16 or float16", op);
+  if (M < 0 || K <= 0 || !x || !q || !s) return fail(B2_ERR_ARG, "%s: bad arguments", op);
+  if (K % 8 != 0 || K > 32768) return fail(B2_ERR_ARG, "%s: K=%d must be a multiple of 8 and <= 32768", op, K);
+  if ((qmode == B2_QMODE_FP8_GROUP128 || qmode == B2_QMODE_FP8_GROUP128_V2) && K % 128 != 0)
+    return fail(B2_ERR_ARG, "%s: K=%d must be a multiple of group_size 128", op, K);
+  if (ldx < row_elems || ldx % 8 != 0 || ldq < K || ldq % 8 != 0 || !aligned16(x) || (reinterpret_cast<uintptr_t>(q) & 7u))
+    return fail(B2_ERR_ARG, "%s: input rows must be 16-byte aligned, output rows 8-byte aligned", op);
+  return B2_OK;
+}
+
+int b2_silu_mul_quant(const void* x, int x_dtype, int64_t ldx, int qmode, uint8_t* q, int64_t ldq, float* s,
+                      int64_t s_row_stride, int64_t s_grp_stride, int64_t s_exp_stride, void* y, int64_t ldy,
+                      const int32_t* masked_m, int64_t tokens_per_expert, int64_t M, int K, b2_stream_t stream) {
+  const char* op = "silu_and_mul + quant";
+  if (int r = check_fused_common(op, x, x_dtype, ldx, 2ll * K, q, ldq, s, qmode, M, K)) return r;
+  if (qmode != B2_QMODE_INT8_ROWS && qmode != B2_QMODE_FP8_ROWS && qmode != B2_QMODE_FP8_GROUP128_V2)
+    return fail(B2_ERR_ARG, "%s: qmode must be INT8_ROWS, FP8_ROWS or FP8_GROUP128_V2", op);
+  if (masked_m && tokens_per_expert <= 0) return fail(B2_ERR_ARG, "%s: masked layout needs tokens_per_expert > 0", op);
+  if (y && (ldy < K || ldy % 8 != 0 || !aligned16(y))) return fail(B2_ERR_ARG, "%s: y rows must be 16-byte aligned", op);
+  if (M == 0) return B2_OK;
+  FusedQuantArgs a{};
+  a.x = x; a.ldx = ldx; a.y = y; a.ldy = ldy; a.q = q; a.ldq = ldq; a.s = s;
+  a.s_row_stride = s_row_stride; a.s_grp_stride = s_grp_stride; a.s_exp_stride = masked_m ? s_exp_stride : 0;
+  a.masked_m = masked_m; a.tokens_per_expert = masked_m ? tokens_per_expert : 1; a.M = M; a.K = K;
+  a.q_eps = 1e-10f; a.fmin = -448.f; a.fmax = 448.f;
+  if (int r = check_cuda(fused_quant_launch(1, qmode, x_dtype, a, static_cast<cudaStream_t>(stream)), "silu_and_mul + quant launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
+int b2_rmsnorm_quant(const void* x, int x_dtype, int64_t ldx, void* residual, int64_t ldr, const void* weight,
+                     float eps, int qmode, uint8_t* q, int64_t ldq, float* s, int64_t s_row_stride,
+                     int64_t s_grp_stride, void* y_out, int64_t ldy, int64_t M, int K, b2_stream_t stream) {
+  const char* op = "rmsnorm + quant";
+  if (int r = check_fused_common(op, x, x_dtype, ldx, K, q, ldq, s, qmode, M, K)) return r;
+  if (qmode != B2_QMODE_INT8_ROWS && qmode != B2_QMODE_FP8_ROWS && qmode != B2_QMODE_FP8_GROUP128)
+    return fail(B2_ERR_ARG, "%s: qmode must be INT8_ROWS, FP8_ROWS or FP8_GROUP128", op);
+  if (!weight || !aligned16(weight)) return fail(B2_ERR_ARG, "%s: weight must be a 16-byte aligned [K] vector", op);
+  if (residual && (ldr < K || ldr % 8 != 0 || !aligned16(residual))) return fail(B2_ERR_ARG, "%s: residual rows must be 16-byte aligned", op);
+  if (y_out && (ldy < K || ldy % 8 != 0 || !aligned16(y_out))) return fail(B2_ERR_ARG, "%s: y rows must be 16-byte aligned", op);
+  if (M == 0) return B2_OK;
+  FusedQuantArgs a{};
+  a.x = x; a.ldx = ldx; a.residual = residual; a.ldr = ldr; a.weight = weight; a.eps = eps; a.y = y_out; a.ldy = ldy;
+  a.q = q; a.ldq = ldq; a.s = s; a.s_row_stride = s_row_stride; a.s_grp_stride = s_grp_stride; a.s_exp_stride = 0;
+  a.masked_m = nullptr; a.tokens_per_expert = 1; a.M = M; a.K = K; a.q_eps = 1e-10f; a.fmin = -448.f; a.fmax = 448.f;
+  if (int r = check_cuda(fused_quant_launch(2, qmode, x_dtype, a, static_cast<cudaStream_t>(stream)), "rmsnorm + quant launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
+int b2_quant_fp8_group128_v2(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s,
+                             int64_t s_row_stride, int64_t s_grp_stride, int64_t M, int K, b2_stream_t stream) {
+  const char* op = "sgl_per_token_group_quant_8bit_v2";
+  if (int r = check_fused_common(op, x, x_dtype, ldx, K, q, ldq, s, B2_QMODE_FP8_GROUP128_V2, M, K)) return r;
+  if (M == 0) return B2_OK;
+  FusedQuantArgs a{};
+  a.x = x; a.ldx = ldx; a.q = q; a.ldq = ldq; a.s = s; a.s_row_stride = s_row_stride; a.s_grp_stride = s_grp_stride;
+  a.tokens_per_expert = 1; a.M = M; a.K = K; a.q_eps = 1e-10f; a.fmin = -448.f; a.fmax = 448.f;
+  if (int r = check_cuda(fused_quant_launch(0, B2_QMODE_FP8_GROUP128_V2, x_dtype, a, static_cast<cudaStream_t>(stream)),
+                         "sgl_per_token_group_quant_8bit_v2 launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
 int b2_gemm_s8(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
                const void* bias, int bias_dtype, void* D, int64_t ldd, int out_dtype, int M, int N, int K,
                b2_stream_t stream) {
@@ -259,6 +360,36 @@ int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64
   int r = gemm_launch(GEMM_E4M3_BLOCK128, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err,
                       sizeof(err));
   if (r) return fail(r, "fp8_blockwise_scaled_mm: %s", err);
+  return B2_OK;
+}
+
+size_t b2_bmm_e4m3_workspace(int M, int N) {
+  return (static_cast<size_t>(M > 0 ? M : 0) + static_cast<size_t>(N > 0 ? N : 0)) * sizeof(float) + 512;
+}
+
+int b2_bmm_e4m3(const uint8_t* A, int64_t lda, int64_t a_batch_stride, const uint8_t* W, int64_t ldw,
+                int64_t w_batch_stride, const float* a_scale, const float* b_scale, void* D, int64_t ldd,
+                int64_t d_batch_stride, int out_dtype, int batch, int M, int N, int K, void* workspace,
+                size_t workspace_bytes, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (batch < 0 || !a_scale || !b_scale) return fail(B2_ERR_ARG, "bmm_fp8: bad arguments");
+  if (batch == 0 || M == 0) return B2_OK;
+  if (!workspace || workspace_bytes < b2_bmm_e4m3_workspace(M, N) || !aligned16(workspace))
+    return fail(B2_ERR_ARG, "bmm_fp8: workspace too small or misaligned (need %zu bytes)", b2_bmm_e4m3_workspace(M, N));
+  if (a_batch_stride % 16 != 0 || w_batch_stride % 16 != 0 || (d_batch_stride * 2) % 16 != 0)
+    return fail(B2_ERR_ARG, "bmm_fp8: batch strides must keep every matrix 16-byte aligned");
+  float* as = static_cast<float*>(workspace);
+  float* bs = as + ((M + 63) & ~63);
+  if (int r = check_cuda(broadcast_scales(a_scale, b_scale, as, bs, M, N, static_cast<cudaStream_t>(stream)),
+                         "bmm_fp8 scale broadcast launch"))
+    return r;
+  count_launch();
+  const int ob = out_dtype == B2_DTYPE_F32 ? 4 : 2;
+  for (int b = 0; b < batch; ++b) {
+    if (int r = b2_gemm_e4m3(A + b * a_batch_stride, lda, W + b * w_batch_stride, ldw, as, bs, nullptr, B2_DTYPE_BF16,
+                             static_cast<uint8_t*>(D) + b * d_batch_stride * ob, ldd, out_dtype, M, N, K, stream))
+      return r;
+  }
   return B2_OK;
 }
 

@@ -21,96 +21,31 @@
 #include <cuda_fp8.h>
 
 #include <cstdlib>
+#include <type_traits>
 
 #include "b200_w8a8_internal.h"
 #include "ptx.cuh"
+#include "quant_common.cuh"
 
 namespace b2 {
-
-enum class QMode { INT8, FP8 };
-
-template <typename T>
-B2_DEVICE float to_f32(T v);
-template <>
-B2_DEVICE float to_f32<__nv_bfloat16>(__nv_bfloat16 v) {
-  return __bfloat162float(v);
-}
-template <>
-B2_DEVICE float to_f32<__half>(__half v) {
-  return __half2float(v);
-}
-
-template <int BYTES>
-struct VecT;
-template <>
-struct VecT<16> {
-  using type = uint4;
-};
-template <>
-struct VecT<8> {
-  using type = uint2;
-};
-template <>
-struct VecT<4> {
-  using type = uint32_t;
-};
-template <>
-struct VecT<2> {
-  using type = uint16_t;
-};
-template <>
-struct VecT<1> {
-  using type = uint8_t;
-};
-
-// streaming load: read-only path, do not keep the line in L1
-template <typename V>
-B2_DEVICE V ld_stream(const V* p) {
-  return __ldg(p);
-}
-template <>
-B2_DEVICE uint4 ld_stream<uint4>(const uint4* p) {
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
-  return r;
-}
-
-B2_DEVICE uint8_t f32_to_e4m3_sat(float v) {
-  return static_cast<uint8_t>(__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E4M3));
-}
-
-// pack two floats -> two e4m3 codes (low = a)
-B2_DEVICE uint16_t f32x2_to_e4m3x2(float a, float b) {
-  uint16_t r;
-  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %2, %1;" : "=h"(r) : "f"(a), "f"(b));
-  return r;
-}
-
-template <QMode MODE>
-B2_DEVICE uint8_t quant_one(float x, float inv) {
-  if constexpr (MODE == QMode::INT8) {
-    return static_cast<uint8_t>(static_cast<int8_t>(__float2int_rn(__fmul_rn(x, inv))));
-  } else {
-    float v = __fmul_rn(x, inv);
-    v = fmaxf(fminf(v, 448.f), -448.f);
-    return f32_to_e4m3_sat(v);
-  }
-}
 
 // One row is processed by TPR threads; a CTA of BLOCK threads owns BLOCK/TPR rows.
 // Each thread caches up to NCACHE vectors of VEC elements; a row longer than
 // TPR*VEC*NCACHE re-reads the overflow from L2 in the second pass.
-template <typename T, QMode MODE, int VEC, int TPR, int BLOCK, int NCACHE>
+// SUM: also emit the fp32 sum of the (unquantized) row, stored in T -- per_token_quant_int8(cal_sum=True) of
+// python/sglang/srt/layers/quantization/int8_kernel.py:46-56 (QoQ); the sum is free once the row is in registers.
+template <typename T, QMode MODE, int VEC, int TPR, int BLOCK, int NCACHE, bool SUM = false>
 __global__ void __launch_bounds__(BLOCK) quant_rows_kernel(const T* __restrict__ x, int64_t ldx,
                                                            uint8_t* __restrict__ q, int64_t ldq,
-                                                           float* __restrict__ s, int M, int K) {
+                                                           float* __restrict__ s, int M, int K,
+                                                           T* __restrict__ row_sum) {
   using V = typename VecT<VEC * sizeof(T)>::type;
   using QV = typename VecT<VEC>::type;
   constexpr int ROWS = BLOCK / TPR;
   constexpr int WARPS_PER_ROW = (TPR + 31) / 32;
   __shared__ float s_red[ROWS][WARPS_PER_ROW > 1 ? WARPS_PER_ROW : 1];
+  __shared__ float s_sum[SUM ? ROWS : 1][WARPS_PER_ROW > 1 ? WARPS_PER_ROW : 1];
+  float rsum = 0.f;
 
   // Release programmatically-launched dependents at once (a no-op for ordinary successors): the decode GEMM that
   // follows starts fetching its weights while these rows are quantized, and waits for this grid's completion
@@ -141,24 +76,41 @@ __global__ void __launch_bounds__(BLOCK) quant_rows_kernel(const T* __restrict__
       if (v < nvec) {
         const T* e = reinterpret_cast<const T*>(&cache[i]);
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) amax = fmaxf(amax, fabsf(to_f32(e[j])));
+        for (int j = 0; j < VEC; ++j) {
+          amax = fmaxf(amax, fabsf(to_f32(e[j])));
+          if constexpr (SUM) rsum += to_f32(e[j]);
+        }
       }
     }
     for (int v = t + NCACHE * TPR; v < nvec; v += TPR) {
       V tmp = ld_stream(xr + v);
       const T* e = reinterpret_cast<const T*>(&tmp);
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) amax = fmaxf(amax, fabsf(to_f32(e[j])));
+      for (int j = 0; j < VEC; ++j) {
+        amax = fmaxf(amax, fabsf(to_f32(e[j])));
+        if constexpr (SUM) rsum += to_f32(e[j]);
+      }
     }
   }
   // reduce over the TPR threads of the row
   constexpr int SHFL_W = TPR < 32 ? TPR : 32;
 #pragma unroll
-  for (int o = SHFL_W / 2; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  for (int o = SHFL_W / 2; o > 0; o >>= 1) {
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if constexpr (SUM) rsum += __shfl_xor_sync(0xffffffffu, rsum, o);
+  }
   if constexpr (WARPS_PER_ROW > 1) {
     const int w = t / 32;
-    if ((t & 31) == 0) s_red[r_in_cta][w] = amax;
+    if ((t & 31) == 0) {
+      s_red[r_in_cta][w] = amax;
+      if constexpr (SUM) s_sum[r_in_cta][w] = rsum;
+    }
     __syncthreads();
+    if constexpr (SUM) {
+      rsum = 0.f;
+#pragma unroll
+      for (int i = 0; i < WARPS_PER_ROW; ++i) rsum += s_sum[r_in_cta][i];
+    }
     float m = s_red[r_in_cta][0];
 #pragma unroll
     for (int i = 1; i < WARPS_PER_ROW; ++i) m = fmaxf(m, s_red[r_in_cta][i]);
@@ -175,7 +127,13 @@ __global__ void __launch_bounds__(BLOCK) quant_rows_kernel(const T* __restrict__
     scale = __fdiv_rn(amax, 448.f);
     inv = (scale == 0.f) ? 0.f : __frcp_rn(scale);
   }
-  if (t == 0) s[row] = scale;
+  if (t == 0) {
+    s[row] = scale;
+    if constexpr (SUM) {
+      if constexpr (std::is_same<T, __nv_bfloat16>::value) row_sum[row] = __float2bfloat16_rn(rsum);
+      else row_sum[row] = __float2half_rn(rsum);
+    }
+  }
 
   QV* qr = reinterpret_cast<QV*>(q + static_cast<int64_t>(row) * ldq);
 #pragma unroll
@@ -237,7 +195,7 @@ static cudaError_t launch_rows(const void* x, int64_t ldx, uint8_t* q, int64_t l
   }();
   cfg.numAttrs = (chain_quantizer && weight_prefetch_enabled() && M <= 128) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, quant_rows_kernel<T, MODE, VEC, TPR, BLOCK, NCACHE>, static_cast<const T*>(x), ldx,
-                            q, ldq, s, M, K);
+                            q, ldq, s, M, K, static_cast<T*>(nullptr));
 }
 
 template <typename T, QMode MODE, int VEC>
@@ -281,6 +239,31 @@ cudaError_t quant_rows_int8(const void* x, int x_dtype, int64_t ldx, int8_t* q, 
   return dispatch_vec<__half, QMode::INT8>(x, ldx, qq, ldq, s, M, K, st);
 }
 
+// per_token_quant_int8(cal_sum=True): same quantizer, plus the row sums in x's dtype.  K % 8 == 0 and 16-byte aligned rows.
+template <typename T>
+static cudaError_t launch_rows_sum(const void* x, int64_t ldx, uint8_t* q, int64_t ldq, float* s, void* row_sum, int M,
+                                   int K, cudaStream_t st) {
+  const int nvec = K / 8;
+  auto go = [&](auto tpr_c) {
+    constexpr int TPR = decltype(tpr_c)::value;
+    constexpr int BLOCK = TPR > 256 ? TPR : 256;
+    constexpr int ROWS = BLOCK / TPR;
+    quant_rows_kernel<T, QMode::INT8, 8, TPR, BLOCK, 8, true><<<(M + ROWS - 1) / ROWS, BLOCK, 0, st>>>(
+        static_cast<const T*>(x), ldx, q, ldq, s, M, K, static_cast<T*>(row_sum));
+    return cudaGetLastError();
+  };
+  if (nvec <= 32 * 8) return go(std::integral_constant<int, 32>{});
+  if (nvec <= 128 * 8) return go(std::integral_constant<int, 128>{});
+  return go(std::integral_constant<int, 1024>{});
+}
+
+cudaError_t quant_rows_int8_sum(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s,
+                                void* row_sum, int M, int K, cudaStream_t st) {
+  uint8_t* qq = reinterpret_cast<uint8_t*>(q);
+  if (x_dtype == B2_DTYPE_BF16) return launch_rows_sum<__nv_bfloat16>(x, ldx, qq, ldq, s, row_sum, M, K, st);
+  return launch_rows_sum<__half>(x, ldx, qq, ldq, s, row_sum, M, K, st);
+}
+
 cudaError_t quant_rows_fp8(const void* x, int x_dtype, int64_t ldx, uint8_t* q, int64_t ldq, float* s, int M,
                            int K, cudaStream_t st) {
   if (x_dtype == B2_DTYPE_BF16) return dispatch_vec<__nv_bfloat16, QMode::FP8>(x, ldx, q, ldq, s, M, K, st);
@@ -310,32 +293,7 @@ B2_DEVICE float group128_quantize(const uint4& v, float eps, float fmin, float f
   }
 #pragma unroll
   for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-  const float ys = __fdiv_rn(amax, fmax);
-  const float r = __frcp_rn(ys);
-  float qv[8];
-  // ONE group-uniform branch (not one per element): the all-ones significand is the only case the reciprocal
-  // sequence does not cover
-  if ((__float_as_uint(ys) & 0x7fffffu) != 0x7fffffu) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float q0 = __fmul_rn(f[j], r);
-      qv[j] = __fmaf_rn(__fmaf_rn(-q0, ys, f[j]), r, q0);
-    }
-  } else {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) qv[j] = __fdiv_rn(f[j], ys);
-  }
-  // reference: fmaxf(fmin, fminf(q, fmax)) then a saturating cast.  The upper fminf also maps NaN to fmax as the
-  // reference does; the lower bound is what cvt.satfinite does by itself when fmin is the format's own minimum.
-  const bool lower = fmin > -448.f;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    qv[j] = fminf(qv[j], fmax);
-    if (lower) qv[j] = fmaxf(qv[j], fmin);
-  }
-  out.x = static_cast<uint32_t>(f32x2_to_e4m3x2(qv[0], qv[1])) | (static_cast<uint32_t>(f32x2_to_e4m3x2(qv[2], qv[3])) << 16);
-  out.y = static_cast<uint32_t>(f32x2_to_e4m3x2(qv[4], qv[5])) | (static_cast<uint32_t>(f32x2_to_e4m3x2(qv[6], qv[7])) << 16);
-  return ys;
+  return group128_quantize_v1(f, amax, fmin, fmax, out);
 }
 
 // GQ_GROUPS adjacent groups per CTA tile = independent 16-byte loads in flight per thread

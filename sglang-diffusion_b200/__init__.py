@@ -48,6 +48,12 @@ from .ops import (  # noqa: E402,F401
     sgl_per_token_quant_fp8,
     sglang_per_token_group_quant_fp8,
     sglang_per_token_quant_fp8,
+    bmm_fp8,
+    rmsnorm_quant,
+    scaled_fp8_quant,
+    sgl_per_tensor_quant_fp8,
+    silu_and_mul_quant,
+    static_quant_fp8,
 )
 from .linear import (  # noqa: E402,F401
     W8A8Fp8LinearMethod,
@@ -67,6 +73,7 @@ __all__ = [
     "capi", "ops", "int8_scaled_mm", "fp8_scaled_mm", "fp8_blockwise_scaled_mm", "sgl_per_token_quant_fp8",
     "sgl_per_token_group_quant_8bit", "per_token_quant_int8", "per_token_quant_int8_cpu",
     "int8_scaled_mm_with_quant", "sglang_per_token_quant_fp8", "sglang_per_token_group_quant_fp8",
-    "per_token_group_quant_fp8", "W8A8Int8LinearMethod", "W8A8Fp8LinearMethod", "W8A8BlockFp8LinearMethod",
+    "per_token_group_quant_fp8", "bmm_fp8", "rmsnorm_quant", "scaled_fp8_quant", "sgl_per_tensor_quant_fp8",
+    "silu_and_mul_quant", "static_quant_fp8", "W8A8Int8LinearMethod", "W8A8Fp8LinearMethod", "W8A8BlockFp8LinearMethod",
     "QuantLinear", "apply_fp8_linear", "cutlass_w8a8_block_fp8_linear_with_fallback", "install_into_sglang", "shard_rows",
 ]

@@ -26,6 +26,8 @@ SYMBOLS = [
     "b2_launch_count", "b2_launch_count_reset", "b2_set_gemm_config", "b2_last_gemm_config",
     "b2_set_profile_buffer", "b2_set_weight_prefetch", "b2_get_weight_prefetch",
     "b2_allreduce_symm",
+    "b2_quant_int8_rows_sum", "b2_quant_fp8_tensor", "b2_silu_mul_quant", "b2_rmsnorm_quant",
+    "b2_quant_fp8_group128_v2", "b2_bmm_e4m3_workspace", "b2_bmm_e4m3",
 ]
 
 if not os.path.isfile(LIB_PATH):
@@ -72,6 +74,18 @@ lib.b2_set_weight_prefetch.restype = None
 lib.b2_get_weight_prefetch.restype = _i
 lib.b2_allreduce_symm.argtypes = [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp]
 lib.b2_allreduce_symm.restype = _i
+lib.b2_quant_int8_rows_sum.argtypes = [_vp, _i, _i64, _vp, _i64, _vp, _vp, _i, _i, _vp]
+lib.b2_quant_fp8_tensor.argtypes = [_vp, _i, _vp, _vp, _vp, _i64, _i64, _i, _vp]
+lib.b2_silu_mul_quant.argtypes = [_vp, _i, _i64, _i, _vp, _i64, _vp, _i64, _i64, _i64, _vp, _i64, _vp, _i64, _i64, _i, _vp]
+lib.b2_rmsnorm_quant.argtypes = [_vp, _i, _i64, _vp, _i64, _vp, _f, _i, _vp, _i64, _vp, _i64, _i64, _vp, _i64, _i64, _i, _vp]
+lib.b2_quant_fp8_group128_v2.argtypes = [_vp, _i, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _i, _vp]
+lib.b2_bmm_e4m3_workspace.argtypes = [_i, _i]
+lib.b2_bmm_e4m3_workspace.restype = _sz
+lib.b2_bmm_e4m3.argtypes = [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _i, _i, _vp, _sz, _vp]
+for _n in ("b2_quant_int8_rows_sum", "b2_quant_fp8_tensor", "b2_silu_mul_quant", "b2_rmsnorm_quant",
+           "b2_quant_fp8_group128_v2", "b2_bmm_e4m3"):
+    getattr(lib, _n).restype = _i
+QMODE_INT8_ROWS, QMODE_FP8_ROWS, QMODE_FP8_GROUP128, QMODE_FP8_GROUP128_V2 = 0, 1, 2, 3
 
 
 class B2Error(RuntimeError):

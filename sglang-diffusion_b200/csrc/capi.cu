@@ -348,6 +348,7 @@ int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64
   const int ob = 2;
   if (int r = check_gemm_common(A, lda, W, ldw, D, ldd, ob, M, N, K)) return r;
   if (K % 128 != 0) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: K=%d must be a multiple of 128", K);
+  if (N % 128 != 0) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: N=%d must be a multiple of 128", N);
   if (!sfa || !sfb) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: scales must not be null");
   if (bias && !aligned16(bias)) return fail(B2_ERR_ARG, "fp8_blockwise_scaled_mm: bias must be 16-byte aligned");
   if (M == 0) return B2_OK;

@@ -14,6 +14,7 @@
 #include <c10/cuda/CUDAStream.h>
 #include <torch/library.h>
 
+#include <cmath>
 #include <optional>
 #include <tuple>
 
@@ -130,6 +131,10 @@ at::Tensor fp8_blockwise_scaled_mm(const at::Tensor& mat_a, const at::Tensor& ma
   TORCH_CHECK(out_dtype == at::kHalf || out_dtype == at::kBFloat16, "out_dtype must be Half or BFloat16");
   TORCH_CHECK(scales_a.dim() == 2 && scales_b.dim() == 2, "scales must be 2D tensors");
   TORCH_CHECK(mat_a.size(0) == scales_a.size(0), "size of scales_a is not matched");
+  // the reference's floor-division checks let N = 192 through and then read one scale out of bounds; the kernel
+  // walks ceil(N/128) blocks, so both extents must sit on the 128 grid
+  TORCH_CHECK(mat_a.size(1) % 128 == 0, "mat_a.size(1) must be a multiple of 128 for 128x128 block scales");
+  TORCH_CHECK(mat_b.size(1) % 128 == 0, "mat_b.size(1) must be a multiple of 128 for 128x128 block scales");
   TORCH_CHECK(mat_a.size(1) / 128 == scales_a.size(1), "size of scales_a is not matched");
   TORCH_CHECK(mat_b.size(0) / 128 == scales_b.size(0), "size of scales_b is not matched");
   TORCH_CHECK(mat_b.size(1) / 128 == scales_b.size(1), "size of scales_b is not matched");
@@ -188,6 +193,95 @@ void sgl_per_token_group_quant_8bit(at::Tensor input, at::Tensor output_q, at::T
                                        output_s.stride(0), output_s.stride(1), (int)M, (int)K, (float)eps,
                                        (float)min_8bit, (float)max_8bit, cur_stream(input));
   check_status(st, "sgl_per_token_group_quant_8bit");
+}
+
+// sgl_per_token_group_quant_8bit_v2 (common_extension.cc:149-152; per_token_group_quant_8bit_v2.cu:396-447):
+// input [M, K] -- or [M, 2K] with fuse_silu_and_mul, or [E, T, 2K] + masked_m[E] -- into e4m3 [.., K] and fp32 scales
+// (any strides: row-major, column-major, TMA-aligned column-major).
+void sgl_per_token_group_quant_8bit_v2(at::Tensor input, at::Tensor output_q, at::Tensor output_s, int64_t group_size,
+                                       double eps, double min_8bit, double max_8bit, bool scale_ue8m0,
+                                       bool fuse_silu_and_mul, const std::optional<at::Tensor>& masked_m) {
+  TORCH_CHECK(input.is_cuda() && output_q.is_cuda() && output_s.is_cuda(), "tensors must be CUDA tensors");
+  TORCH_CHECK(input.is_contiguous() && output_q.is_contiguous(), "input and output_q must be contiguous");
+  TORCH_CHECK(input.numel() > 0, "input must not be empty");
+  TORCH_CHECK(std::abs(1e-10 - eps) < 1e-13, "eps must be 1e-10");
+  TORCH_CHECK(input.numel() % group_size == 0, "input.numel() must be divisible by group_size");
+  TORCH_CHECK_NOT_IMPLEMENTED(group_size == 128, "sgl_per_token_group_quant_8bit_v2: only group_size 128 is built");
+  TORCH_CHECK_NOT_IMPLEMENTED(!scale_ue8m0, "sgl_per_token_group_quant_8bit_v2: UE8M0 scales are not built");
+  TORCH_CHECK_NOT_IMPLEMENTED(output_q.scalar_type() == at::kFloat8_e4m3fn,
+                              "sgl_per_token_group_quant_8bit_v2: only e4m3 output is built");
+  TORCH_CHECK(min_8bit == -448.0 && max_8bit == 448.0, "fp8_min / fp8_max must be -448 / 448");
+  TORCH_CHECK(output_s.scalar_type() == at::kFloat, "output_s must be Float32");
+  const bool masked = masked_m.has_value();
+  TORCH_CHECK(!masked || fuse_silu_and_mul, "masked_m needs fuse_silu_and_mul");
+  TORCH_CHECK(output_s.dim() == (masked ? 3 : 2), "output_s has the wrong rank");
+  const int64_t K = output_q.size(-1);
+  TORCH_CHECK(input.size(-1) == (fuse_silu_and_mul ? 2 * K : K), "input / output_q hidden sizes do not match");
+  const int64_t T = output_q.size(-2);
+  const int64_t M = output_q.numel() / K;
+  TORCH_CHECK(output_s.size(-2) == T && output_s.size(-1) == K / group_size, "output_s shape mismatch");
+  if (masked) {
+    TORCH_CHECK(masked_m->is_cuda() && masked_m->scalar_type() == at::kInt && masked_m->is_contiguous() &&
+                    masked_m->numel() == input.size(0), "masked_m must be an int32 CUDA tensor [num_experts]");
+  }
+  c10::cuda::CUDAGuard guard(input.device());
+  int st;
+  if (fuse_silu_and_mul) {
+    st = b2_silu_mul_quant(input.data_ptr(), act_dtype(input.scalar_type(), "input"), 2 * K, B2_QMODE_FP8_GROUP128_V2,
+                           static_cast<uint8_t*>(output_q.data_ptr()), K, output_s.data_ptr<float>(), output_s.stride(-2),
+                           output_s.stride(-1), masked ? output_s.stride(0) : 0, nullptr, 0,
+                           masked ? masked_m->data_ptr<int32_t>() : nullptr, T, M, (int)K, cur_stream(input));
+  } else {
+    st = b2_quant_fp8_group128_v2(input.data_ptr(), act_dtype(input.scalar_type(), "input"), K,
+                                  static_cast<uint8_t*>(output_q.data_ptr()), K, output_s.data_ptr<float>(),
+                                  output_s.stride(-2), output_s.stride(-1), M, (int)K, cur_stream(input));
+  }
+  check_status(st, "sgl_per_token_group_quant_8bit_v2");
+}
+
+// sgl_per_tensor_quant_fp8 (common_extension.cc:154-155; per_tensor_quant_fp8.cu:98-123)
+void sgl_per_tensor_quant_fp8(at::Tensor input, at::Tensor output_q, at::Tensor output_s, bool is_static) {
+  TORCH_CHECK(input.is_cuda() && output_q.is_cuda() && output_s.is_cuda(), "tensors must be CUDA tensors");
+  TORCH_CHECK(input.is_contiguous() && output_q.is_contiguous() && output_s.is_contiguous(),
+              "tensors must be contiguous");
+  TORCH_CHECK(output_q.scalar_type() == at::kFloat8_e4m3fn, "output_q must be Float8_e4m3fn");
+  TORCH_CHECK(output_s.scalar_type() == at::kFloat && output_s.numel() == 1, "output_s must be one Float32");
+  TORCH_CHECK(output_q.numel() >= input.numel(), "output_q is smaller than input");
+  c10::cuda::CUDAGuard guard(input.device());
+  const int st = b2_quant_fp8_tensor(input.data_ptr(), act_dtype(input.scalar_type(), "input"),
+                                     static_cast<uint8_t*>(output_q.data_ptr()), output_s.data_ptr<float>(), nullptr,
+                                     input.numel(), 0, is_static ? 1 : 0, cur_stream(input));
+  check_status(st, "sgl_per_tensor_quant_fp8");
+}
+
+// bmm_fp8 (common_extension.cc:397-401; bmm_fp8.cu): A [b,m,k] e4m3 row-major, B [b,k,n] e4m3 "column major"
+// (stride(-2) == 1, i.e. the memory of [b,n,k]), D [b,m,n] bf16 / f16, per-tensor scales.  The cuBLASLt handle of the
+// reference signature is not used (no cuBLAS on this path); the workspace holds the broadcast scale vectors.
+void bmm_fp8(at::Tensor A, at::Tensor B, at::Tensor D, at::Tensor A_scale, at::Tensor B_scale,
+             at::Tensor workspace_buffer, int64_t /*cublas_handle*/) {
+  TORCH_CHECK(A.is_cuda(), "A must be a CUDA tensor");
+  TORCH_CHECK(B.is_cuda(), "B must be a CUDA tensor");
+  TORCH_CHECK(D.is_cuda(), "D must be a CUDA tensor");
+  TORCH_CHECK(A.dim() == 3, "Expected 3D tensor for A");
+  TORCH_CHECK(B.dim() == 3, "Expected 3D tensor for B");
+  TORCH_CHECK(D.dim() == 3, "Expected 3D tensor for D");
+  TORCH_CHECK(A.size(0) == B.size(0) && A.size(0) == D.size(0), "Batch sizes must match");
+  TORCH_CHECK(A.size(2) == B.size(1), "Incompatible matrix sizes");
+  TORCH_CHECK(A.size(1) == D.size(1) && B.size(2) == D.size(2), "Result tensor has incorrect shape");
+  TORCH_CHECK(A.scalar_type() == at::kFloat8_e4m3fn && B.scalar_type() == at::kFloat8_e4m3fn,
+              "bmm_fp8: only e4m3 x e4m3 is built");
+  TORCH_CHECK(A.stride(2) == 1 && D.stride(2) == 1, "A and D must be row major");
+  TORCH_CHECK(B.stride(1) == 1, "B must be column major");
+  TORCH_CHECK(A_scale.scalar_type() == at::kFloat && B_scale.scalar_type() == at::kFloat && A_scale.numel() == 1 &&
+                  B_scale.numel() == 1, "A_scale / B_scale must be single Float32 values");
+  c10::cuda::CUDAGuard guard(A.device());
+  const int64_t b = A.size(0), m = A.size(1), k = A.size(2), n = B.size(2);
+  const int st = b2_bmm_e4m3(static_cast<const uint8_t*>(A.data_ptr()), A.stride(1), A.stride(0),
+                             static_cast<const uint8_t*>(B.data_ptr()), n > 1 ? B.stride(2) : k, B.stride(0),
+                             A_scale.data_ptr<float>(), B_scale.data_ptr<float>(), D.data_ptr(), D.stride(1), D.stride(0),
+                             act_dtype(D.scalar_type(), "D"), (int)b, (int)m, (int)n, (int)k, workspace_buffer.data_ptr(),
+                             (size_t)workspace_buffer.numel() * workspace_buffer.element_size(), cur_stream(A));
+  check_status(st, "bmm_fp8");
 }
 
 // ---- CPU-path op names with CUDA kernels (torch_extension_cpu.cpp:419-447) ------------------
@@ -290,6 +384,17 @@ TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
     m.def(
         "sgl_per_token_group_quant_8bit(Tensor input, Tensor! output_q, Tensor! output_s, int group_size,"
         " float eps, float fp8_min, float fp8_max, bool scale_ue8m0) -> ()");
+  if (!has_schema("sgl_kernel::sgl_per_token_group_quant_8bit_v2"))
+    m.def(
+        "sgl_per_token_group_quant_8bit_v2(Tensor input, Tensor! output_q, Tensor! output_s, int group_size,"
+        " float eps, float fp8_min, float fp8_max, bool scale_ue8m0, bool fuse_silu_and_mul, Tensor? masked_m) -> ()");
+  if (!has_schema("sgl_kernel::sgl_per_tensor_quant_fp8"))
+    m.def("sgl_per_tensor_quant_fp8(Tensor input, Tensor! output_q, Tensor! output_s, bool is_static) -> ()");
+  if (!has_schema("sgl_kernel::bmm_fp8"))
+    m.def(
+        "bmm_fp8(Tensor A, Tensor B, Tensor! D, Tensor A_scale, Tensor B_scale, Tensor workspace_buffer, "
+        "int cublas_handle) -> ()",
+        {at::Tag::needs_fixed_stride_order});
   if (!has_schema("sgl_kernel::per_token_quant_int8_cpu"))
     m.def("per_token_quant_int8_cpu(Tensor A) -> (Tensor, Tensor)");
   if (!has_schema("sgl_kernel::int8_scaled_mm_cpu"))
@@ -308,6 +413,9 @@ TORCH_LIBRARY_IMPL(sgl_kernel, CUDA, m) {
   m.impl("fp8_blockwise_scaled_mm", &fp8_blockwise_scaled_mm);
   m.impl("sgl_per_token_quant_fp8", &sgl_per_token_quant_fp8);
   m.impl("sgl_per_token_group_quant_8bit", &sgl_per_token_group_quant_8bit);
+  m.impl("sgl_per_token_group_quant_8bit_v2", &sgl_per_token_group_quant_8bit_v2);
+  m.impl("sgl_per_tensor_quant_fp8", &sgl_per_tensor_quant_fp8);
+  m.impl("bmm_fp8", &bmm_fp8);
   m.impl("per_token_quant_int8_cpu", &per_token_quant_int8_cuda);
   m.impl("int8_scaled_mm_cpu", &int8_scaled_mm_cpuname_cuda);
   m.impl("int8_scaled_mm_with_quant", &int8_scaled_mm_with_quant_cuda);

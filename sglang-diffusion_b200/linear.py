@@ -71,13 +71,17 @@ class W8A8Int8LinearMethod:
 def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor,
                      input_scale: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
                      **_ignored) -> torch.Tensor:
-    """Dynamic per-token branch of fp8_utils.py:1194-1276 (weight is [K,N] with stride(0)==1)."""
-    if input_scale is not None:
-        raise NotImplementedError("static per-tensor fp8 activation scales are a 'next' row (SURVEY 8f rank 4)")
+    """fp8_utils.py:1194-1276 (weight is [K,N] with stride(0)==1): dynamic per-token activation scales, or -- with
+    `input_scale` -- the static per-tensor branch (:1232-1239), whose scale is broadcast to one value per token so
+    that the same per-token x per-channel GEMM epilogue serves both."""
     input_2d = input.view(-1, input.shape[-1])
     output_shape = [*input.shape[:-1], weight.shape[1]]
     assert weight_scale.numel() == weight.shape[1], "per-channel weight scales expected"
-    qinput, x_scale = ops.sglang_per_token_quant_fp8(input_2d)
+    if input_scale is not None:
+        assert input_scale.numel() == 1
+        qinput, x_scale = ops.static_quant_fp8(input_2d.contiguous(), input_scale, repeat_scale=True)
+    else:
+        qinput, x_scale = ops.sglang_per_token_quant_fp8(input_2d)
     output = ops.fp8_scaled_mm(qinput, weight, x_scale, weight_scale, out_dtype=input.dtype, bias=bias)
     return output.view(*output_shape)
 
@@ -100,7 +104,8 @@ class W8A8Fp8LinearMethod:
 
     def apply(self, layer, x: torch.Tensor, bias: Optional[torch.Tensor] = None):
         with capi.static_weights():  # see W8A8Int8LinearMethod.apply
-            return apply_fp8_linear(x, layer.weight, layer.weight_scale, bias=bias)
+            return apply_fp8_linear(x, layer.weight, layer.weight_scale,
+                                    input_scale=getattr(layer, "input_scale", None), bias=bias)
 
 
 def cutlass_w8a8_block_fp8_linear_with_fallback(input: torch.Tensor, weight: torch.Tensor, block_size: List[int],
@@ -115,10 +120,9 @@ def cutlass_w8a8_block_fp8_linear_with_fallback(input: torch.Tensor, weight: tor
     input_2d = input.view(-1, input.shape[-1])
     output_shape = [*input.shape[:-1], weight.shape[0]]
     q_input, x_scale = ops.per_token_group_quant_fp8(input_2d, block_size[1], column_major_scales=True)
-    output = ops.fp8_blockwise_scaled_mm(q_input, weight.T, x_scale, weight_scale.T, out_dtype=input_2d.dtype)
-    if bias is not None:
-        output += bias
-    return output.to(dtype=input_2d.dtype).view(*output_shape)
+    # the reference adds the bias with a second kernel (fp8_utils.py:546-547); here it rides in the GEMM epilogue
+    output = ops.fp8_blockwise_scaled_mm_bias(q_input, weight.T, x_scale, weight_scale.T, input_2d.dtype, bias)
+    return output.view(*output_shape)
 
 
 class W8A8BlockFp8LinearMethod:

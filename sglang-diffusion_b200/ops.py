@@ -51,12 +51,57 @@ def scaled_mm_out(mat_a, mat_b, scales_a, scales_b, out, bias=None):
     assert scales_a.numel() == M and scales_b.numel() == N and scales_a.is_contiguous() and scales_b.is_contiguous()
     dt = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16, torch.float32: capi.DTYPE_F32}
     fn = capi.lib.b2_gemm_s8 if mat_a.dtype == torch.int8 else capi.lib.b2_gemm_e4m3
-    stream = torch.cuda.current_stream(mat_a.device).cuda_stream
-    capi.check(fn(mat_a.data_ptr(), mat_a.stride(0), mat_b.data_ptr(), mat_b.stride(1), scales_a.data_ptr(),
-                  scales_b.data_ptr(), None if bias is None else bias.data_ptr(),
-                  dt[bias.dtype] if bias is not None else capi.DTYPE_F32, out.data_ptr(), out.stride(0),
-                  dt[out.dtype], M, N, K, stream))
+    with torch.cuda.device(mat_a.device):  # the library plans for and launches on the CURRENT device
+        stream = torch.cuda.current_stream(mat_a.device).cuda_stream
+        capi.check(fn(mat_a.data_ptr(), mat_a.stride(0), mat_b.data_ptr(), mat_b.stride(1), scales_a.data_ptr(),
+                      scales_b.data_ptr(), None if bias is None else bias.data_ptr(),
+                      dt[bias.dtype] if bias is not None else capi.DTYPE_F32, out.data_ptr(), out.stride(0),
+                      dt[out.dtype], M, N, K, stream))
     return out
+
+
+def fp8_blockwise_scaled_mm_bias(mat_a, mat_b, scales_a, scales_b, out_dtype, bias=None):
+    """fp8_blockwise_scaled_mm with the bias add fused into the GEMM epilogue.  The reference op has no bias
+    parameter (its caller adds it with a second kernel, fp8_utils.py:546-547); the C ABI has one, so the linear
+    method calls b2_gemm_e4m3_block128 directly when a bias is present.  Same argument checks as the torch op."""
+    from . import capi
+
+    if bias is None:
+        return fp8_blockwise_scaled_mm(mat_a, mat_b, scales_a, scales_b, out_dtype)
+    M, K = mat_a.shape
+    N = mat_b.shape[1]
+    assert mat_b.shape[0] == K and mat_b.stride(0) == 1 and mat_a.stride(1) == 1
+    assert scales_a.shape == (M, K // 128) and scales_b.shape == (K // 128, N // 128)
+    assert bias.numel() == N and bias.is_contiguous()
+    dt = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16, torch.float32: capi.DTYPE_F32}
+    out = torch.empty(M, N, dtype=out_dtype, device=mat_a.device)
+    with torch.cuda.device(mat_a.device):
+        stream = torch.cuda.current_stream(mat_a.device).cuda_stream
+        capi.check(capi.lib.b2_gemm_e4m3_block128(
+            mat_a.data_ptr(), mat_a.stride(0) if M > 1 else K, mat_b.data_ptr(), mat_b.stride(1) if N > 1 else K,
+            scales_a.data_ptr(), scales_a.stride(0), scales_a.stride(1), scales_b.data_ptr(), scales_b.stride(1),
+            scales_b.stride(0), bias.data_ptr(), dt[bias.dtype], out.data_ptr(), N, dt[out_dtype], M, N, K, stream))
+    return out
+
+
+def bmm_fp8(A, B, A_scale, B_scale, dtype, out=None):
+    """sgl-kernel/python/sgl_kernel/gemm.py:65-81: A [b,m,k] e4m3, B [b,k,n] e4m3 column-major, per-tensor scales."""
+    if out is None:
+        out = torch.empty((A.shape[0], A.shape[1], B.shape[2]), device=A.device, dtype=dtype)
+    ws = _cache_buf("bmm_fp8_workspace", 1 << 20, A.device)
+    _ops.bmm_fp8.default(A, B, out, A_scale, B_scale, ws, 0)
+    return out
+
+
+_BUFS = {}
+
+
+def _cache_buf(name, nbytes, device):
+    key = (name, torch.device(device))
+    buf = _BUFS.get(key)
+    if buf is None:
+        buf = _BUFS[key] = torch.empty(nbytes, dtype=torch.uint8, device=device)
+    return buf
 
 
 def int8_scaled_mm_with_quant(mat1, mat2, scales2, bias, out_dtype, is_vnni=False):
@@ -77,10 +122,22 @@ def per_token_quant_int8(x: torch.Tensor, scale_dtype=torch.float32, cal_sum: bo
     """Signature of int8_kernel.py:59-89 (the Triton quantizer the CUDA linear method calls):
     returns (x_q int8 like x, scales [..., 1]).  Arithmetic is the CPU path's (eps 1e-7,
     round-half-even), which BASELINE.json makes the bit-exact target."""
-    if cal_sum:
-        raise NotImplementedError("per_token_quant_int8(cal_sum=True) (QoQ row sums) is out of scope")
     assert x.is_contiguous()
     K = x.shape[-1]
+    if cal_sum:  # int8_kernel.py:46-56 (QoQ): also the row sums of x, in x's dtype
+        from . import capi
+
+        x2 = x.view(-1, K)
+        M = x2.shape[0]
+        q = torch.empty_like(x, dtype=torch.int8)
+        s = torch.empty(x.shape[:-1] + (1,), dtype=torch.float32, device=x.device)
+        x_sum = torch.empty(x.shape[:-1], dtype=x.dtype, device=x.device)
+        dt = capi.DTYPE_BF16 if x.dtype == torch.bfloat16 else capi.DTYPE_F16
+        with torch.cuda.device(x.device):
+            capi.check(capi.lib.b2_quant_int8_rows_sum(x2.data_ptr(), dt, K, q.data_ptr(), K, s.data_ptr(),
+                                                       x_sum.data_ptr(), M, K,
+                                                       torch.cuda.current_stream(x.device).cuda_stream))
+        return q, (s if scale_dtype == torch.float32 else s.to(scale_dtype)), x_sum
     q, s = _ops.per_token_quant_int8_cpu.default(x.view(-1, K))
     s = s.view(x.shape[:-1] + (1,))
     if scale_dtype != torch.float32:
@@ -102,9 +159,129 @@ def sglang_per_token_quant_fp8(x: torch.Tensor, dtype: torch.dtype = fp8_dtype):
 
 
 def sgl_per_token_group_quant_8bit(input, output_q, output_s, group_size, eps, fp8_min, fp8_max,
-                                   scale_ue8m0=False) -> None:
+                                   scale_ue8m0=False, fuse_silu_and_mul=False, masked_m=None,
+                                   enable_v2: Optional[bool] = None) -> None:
+    """sgl-kernel/python/sgl_kernel/gemm.py:99-135."""
+    if enable_v2 is None:
+        enable_v2 = fuse_silu_and_mul or masked_m is not None
+    if enable_v2:
+        return _ops.sgl_per_token_group_quant_8bit_v2.default(input, output_q, output_s, group_size, eps, fp8_min,
+                                                              fp8_max, scale_ue8m0, fuse_silu_and_mul, masked_m)
+    assert not fuse_silu_and_mul, "only v2 support fuse_silu_and_mul"
+    assert masked_m is None, "only v2 support masked_m"
     _ops.sgl_per_token_group_quant_8bit.default(input, output_q, output_s, group_size, eps, fp8_min, fp8_max,
                                                 scale_ue8m0)
+
+
+def sgl_per_tensor_quant_fp8(input, output_q, output_s, is_static: bool) -> None:
+    """sgl-kernel/python/sgl_kernel/gemm.py:143-151."""
+    _ops.sgl_per_tensor_quant_fp8.default(input, output_q, output_s, is_static)
+
+
+def scaled_fp8_quant(input: torch.Tensor, scale: Optional[torch.Tensor] = None,
+                     num_token_padding: Optional[int] = None, use_per_token_if_dynamic: bool = False):
+    """fp8_kernel.py:1650-1684 (the sgl_kernel branch)."""
+    assert input.ndim == 2, f"Expected 2D input tensor, got {input.ndim}D"
+    shape = input.shape
+    if num_token_padding:
+        shape = (max(num_token_padding, input.shape[0]), shape[1])
+    output = torch.empty(shape, device=input.device, dtype=fp8_dtype)
+    if scale is None:
+        if use_per_token_if_dynamic:
+            scale = torch.empty((shape[0], 1), device=input.device, dtype=torch.float32)
+            sgl_per_token_quant_fp8(input, output[: input.shape[0]], scale[: input.shape[0]])
+        else:
+            scale = torch.zeros(1, device=input.device, dtype=torch.float32)
+            sgl_per_tensor_quant_fp8(input, output, scale, is_static=False)
+    else:
+        assert scale.numel() == 1, f"Expected scalar scale, got numel={scale.numel()}"
+        sgl_per_tensor_quant_fp8(input, output, scale, is_static=True)
+    return output, scale
+
+
+def static_quant_fp8(x: torch.Tensor, x_s: torch.Tensor, repeat_scale: bool = False):
+    """fp8_kernel.py:649-700: quantize with the given per-tensor scale; repeat_scale also returns the scale once
+    per token row ([M,1]) for the per-token GEMM epilogue.  One launch of b2_quant_fp8_tensor."""
+    from . import capi
+
+    assert x.is_contiguous(), "`x` is not contiguous"
+    assert x_s.numel() == 1, "only supports per-tensor scale"
+    assert x_s.dtype == torch.float32 and x_s.device == x.device
+    x_q = torch.empty_like(x, dtype=fp8_dtype)
+    M = x.numel() // x.shape[-1]
+    x_s_repeat = torch.empty((M, 1), device=x.device, dtype=torch.float32) if repeat_scale else None
+    if x.numel() > 0:
+        dt = capi.DTYPE_BF16 if x.dtype == torch.bfloat16 else capi.DTYPE_F16
+        with torch.cuda.device(x.device):
+            capi.check(capi.lib.b2_quant_fp8_tensor(x.data_ptr(), dt, x_q.data_ptr(), x_s.data_ptr(),
+                                                    x_s_repeat.data_ptr() if repeat_scale else None, x.numel(), M, 1,
+                                                    torch.cuda.current_stream(x.device).cuda_stream))
+    return x_q, (x_s_repeat if repeat_scale else x_s)
+
+
+_QMODES = {"int8": 0, "fp8": 1, "fp8_group128": 2, "fp8_group128_v2": 3}
+
+
+def silu_and_mul_quant(x: torch.Tensor, mode: str = "int8", return_act: bool = False):
+    """silu_and_mul (sgl-kernel/csrc/elementwise/activation.cu) fused into the activation quantizer of the following
+    down_proj: x [..., 2K] (gate | up) -> (q [..., K], scales) with mode "int8" | "fp8" (per-token, scales [..., 1]) or
+    "fp8_group128_v2" (1x128, M-major scales as the block-wise GEMM wants).  One kernel, one read of x."""
+    from . import capi
+
+    assert x.is_contiguous() and x.shape[-1] % 2 == 0
+    K = x.shape[-1] // 2
+    x2 = x.view(-1, 2 * K)
+    M = x2.shape[0]
+    qm = _QMODES[mode]
+    assert qm in (0, 1, 3)
+    q = torch.empty(x.shape[:-1] + (K,), dtype=torch.int8 if qm == 0 else fp8_dtype, device=x.device)
+    if qm == 3:
+        s = create_per_token_group_quant_fp8_output_scale((M, K), x.device, 128, True)
+        srow, sgrp = s.stride(0), s.stride(1)
+    else:
+        s = torch.empty(x.shape[:-1] + (1,), dtype=torch.float32, device=x.device)
+        srow, sgrp = 1, 0
+    y = torch.empty(x.shape[:-1] + (K,), dtype=x.dtype, device=x.device) if return_act else None
+    if M > 0:
+        dt = capi.DTYPE_BF16 if x.dtype == torch.bfloat16 else capi.DTYPE_F16
+        with torch.cuda.device(x.device):
+            capi.check(capi.lib.b2_silu_mul_quant(x2.data_ptr(), dt, 2 * K, qm, q.data_ptr(), K, s.data_ptr(), srow, sgrp,
+                                                  0, y.data_ptr() if return_act else None, K, None, 0, M, K,
+                                                  torch.cuda.current_stream(x.device).cuda_stream))
+    return (q, s, y) if return_act else (q, s)
+
+
+def rmsnorm_quant(x: torch.Tensor, weight: torch.Tensor, eps: float = 1e-6, residual: Optional[torch.Tensor] = None,
+                  mode: str = "int8", return_normed: bool = False):
+    """rmsnorm / fused_add_rmsnorm (sgl-kernel/python/sgl_kernel/elementwise.py) fused into the activation quantizer
+    of the following qkv_proj / gate_up_proj.  With `residual` the sum x + residual is written back to it in place
+    (the reference op's contract).  mode "int8" | "fp8" | "fp8_group128".  Returns (q, scales[, normed])."""
+    from . import capi
+
+    assert x.is_contiguous() and weight.is_contiguous() and weight.dtype == x.dtype and weight.numel() == x.shape[-1]
+    K = x.shape[-1]
+    x2 = x.view(-1, K)
+    M = x2.shape[0]
+    qm = _QMODES[mode]
+    assert qm in (0, 1, 2)
+    if residual is not None:
+        assert residual.is_contiguous() and residual.shape == x.shape and residual.dtype == x.dtype
+    q = torch.empty_like(x, dtype=torch.int8 if qm == 0 else fp8_dtype)
+    if qm == 2:
+        s = create_per_token_group_quant_fp8_output_scale((M, K), x.device, 128, True)
+        srow, sgrp = s.stride(0), s.stride(1)
+    else:
+        s = torch.empty(x.shape[:-1] + (1,), dtype=torch.float32, device=x.device)
+        srow, sgrp = 1, 0
+    y = torch.empty_like(x) if return_normed else None
+    if M > 0:
+        dt = capi.DTYPE_BF16 if x.dtype == torch.bfloat16 else capi.DTYPE_F16
+        with torch.cuda.device(x.device):
+            capi.check(capi.lib.b2_rmsnorm_quant(x2.data_ptr(), dt, K, residual.data_ptr() if residual is not None else None,
+                                                 K, weight.data_ptr(), float(eps), qm, q.data_ptr(), K, s.data_ptr(), srow,
+                                                 sgrp, y.data_ptr() if return_normed else None, K, M, K,
+                                                 torch.cuda.current_stream(x.device).cuda_stream))
+    return (q, s, y) if return_normed else (q, s)
 
 
 def create_per_token_group_quant_fp8_output_scale(x_shape, device, group_size, column_major_scales: bool,
@@ -129,13 +306,13 @@ def sglang_per_token_group_quant_fp8(x: torch.Tensor, group_size: int, eps: floa
     """fp8_kernel.py:479-541."""
     assert x.shape[-1] % group_size == 0, "the last dimension of `x` cannot be divisible by `group_size`"
     assert x.is_contiguous(), "`x` is not contiguous"
-    if fuse_silu_and_mul or masked_m is not None:
-        raise NotImplementedError("fused silu_and_mul / masked_m group quant is a 'next' row (SURVEY 8f rank 1)")
-    x_q = torch.empty(x.shape, device=x.device, dtype=fp8_dtype)
-    x_s = create_per_token_group_quant_fp8_output_scale(x.shape, x.device, group_size, column_major_scales,
+    out_shape = (*x.shape[:-1], x.shape[-1] // (2 if fuse_silu_and_mul else 1))
+    x_q = torch.empty(out_shape, device=x.device, dtype=fp8_dtype)
+    x_s = create_per_token_group_quant_fp8_output_scale(out_shape, x.device, group_size, column_major_scales,
                                                         scale_tma_aligned, scale_ue8m0)
     if x.shape[0] > 0:
-        sgl_per_token_group_quant_8bit(x, x_q, x_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0)
+        sgl_per_token_group_quant_8bit(x, x_q, x_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0,
+                                       fuse_silu_and_mul, masked_m, enable_v2=enable_v2)
     return x_q, x_s
 
 
@@ -168,7 +345,18 @@ def _register_fakes() -> None:
     def _void8(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0):
         return None
 
+    def _void10(input, output_q, output_s, group_size, eps, fp8_min, fp8_max, scale_ue8m0, fuse_silu_and_mul, masked_m):
+        return None
+
+    def _void4(input, output_q, output_s, is_static):
+        return None
+
+    def _void7(A, B, D, A_scale, B_scale, workspace_buffer, cublas_handle):
+        return None
+
     for name, fn in (
+        ("sgl_kernel::sgl_per_token_group_quant_8bit_v2", _void10), ("sgl_kernel::sgl_per_tensor_quant_fp8", _void4),
+        ("sgl_kernel::bmm_fp8", _void7),
         ("sgl_kernel::int8_scaled_mm", _mm_fake), ("sgl_kernel::fp8_scaled_mm", _mm_fake),
         ("sgl_kernel::fp8_blockwise_scaled_mm", _bw_fake), ("sgl_kernel::per_token_quant_int8_cpu", _quant_fake),
         ("sgl_kernel::int8_scaled_mm_cpu", _mm_cpu_fake), ("sgl_kernel::int8_scaled_mm_with_quant", _wq_fake),

@@ -186,5 +186,58 @@ def fp8_blockwise_scaled_mm(Aq_u8, W_u8, sfa, sfb) -> torch.Tensor:
     return out
 
 
+# ------------------------------------------- producer fusion / per-tensor (8f) ----
+# Restated in torch fp32 on CPU (every step an IEEE fp32 operation, same order as the CUDA sources named).
+
+def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
+    """y = T(silu(f32(gate))) * up in T -- per_token_group_quant_8bit_v2.cu:330-341.  The sm_100 source computes silu
+    as 0.5x(1 + tanh.approx(0.5x)) (:32-40), a hardware approximation this exact-tanh restatement can only bound:
+    tolerance-pinned (<= 1 ulp of T on the activation, see tests)."""
+    _chk_cpu(x)
+    K = x.shape[-1] // 2
+    g, u = x[..., :K].float(), x[..., K:]
+    half = g * 0.5
+    act = (half * (1.0 + torch.tanh(half))).to(x.dtype)
+    return (act.float() * u.float()).to(x.dtype)
+
+
+def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: torch.Tensor | None = None):
+    """flashinfer norm.cuh FusedAddRMSNormKernel / RMSNormKernel as called by
+    sgl-kernel/csrc/elementwise/fused_add_rms_norm_kernel.cu: s = f32(x) + f32(res); res <- T(s);
+    y = T((s * rsqrt(mean(s^2) + eps)) * w).  Returns (y, new_residual or None).  The sum of squares is reduced in a
+    different order on the GPU and rsqrt is 2-ulp there: tolerance-pinned."""
+    _chk_cpu(x, weight, residual)
+    s = x.float() if residual is None else x.float() + residual.float()
+    new_res = None if residual is None else s.to(x.dtype)
+    rcp = torch.rsqrt((s.double() * s.double()).sum(-1, keepdim=True).float() / x.shape[-1] + eps)
+    y = ((s * rcp) * weight.float()).to(x.dtype)
+    return y, new_res
+
+
+def per_token_group_quant_fp8_v2(y: torch.Tensor, group_size=128):
+    """(codes uint8 [M,K], scales f32 [M,K/G]) -- per_token_group_quant_8bit_v2.cu:69-81,343-372, fp32 scales:
+    amax = max(1e-10, max|y|); s = amax * f32(1/448); q = e4m3_rn(clamp(y * (448/amax), +-448))."""
+    _chk_cpu(y)
+    M, K = y.shape
+    g = y.float().view(M, K // group_size, group_size)
+    amax = g.abs().amax(-1, keepdim=True).clamp_min(1e-10)
+    s = amax * torch.tensor(1.0 / 448.0, dtype=torch.float32)
+    ys = torch.tensor(448.0, dtype=torch.float32) / amax
+    q = (g * ys).clamp(-448.0, 448.0).to(torch.float8_e4m3fn).view(torch.uint8).view(M, K)
+    return q, s.squeeze(-1)
+
+
+def per_tensor_quant_fp8(x: torch.Tensor, scale: torch.Tensor | None = None):
+    """(codes uint8 like x, scale f32 [1]) -- per_tensor_quant_fp8.cu:11-96: dynamic s = max|x|/448;
+    q = e4m3_rn(clamp(x * (1/s), +-448)).  (The reference build's --use_fast_math turns 1/s into rcp.approx; the IEEE
+    quotient is the documented arithmetic and what the library computes.)"""
+    _chk_cpu(x, scale)
+    if scale is None:
+        scale = (x.float().abs().max() / 448.0).reshape(1)
+    inv = torch.tensor(1.0, dtype=torch.float32) / scale.float().reshape(1)
+    q = (x.float() * inv).clamp(-448.0, 448.0).to(torch.float8_e4m3fn).view(torch.uint8)
+    return q, scale.float().reshape(1)
+
+
 if __name__ == "__main__":
     print(build(force=True))

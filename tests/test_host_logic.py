@@ -54,13 +54,38 @@ def test_group_scale_allocation_layouts():
 
 
 def test_out_of_scope_modes_raise():
-    x = torch.zeros(2, 256, dtype=torch.bfloat16)
+    """What is still not built says so: UE8M0 group scales.  (cal_sum, fused silu_and_mul and the
+    static input_scale branch are built in round 2 -- tests/test_gpu_fused.py.)"""
     with pytest.raises(NotImplementedError):
-        b2.per_token_quant_int8(x, cal_sum=True)
-    with pytest.raises(NotImplementedError):
-        b2.per_token_group_quant_fp8(x, 128, fuse_silu_and_mul=True)
-    with pytest.raises(NotImplementedError):
-        b2.apply_fp8_linear(x, x, x, input_scale=torch.ones(1))
+        b2.ops.create_per_token_group_quant_fp8_output_scale((4, 256), "cpu", 128, True, True, scale_ue8m0=True)
+
+
+def test_triton_quantizer_formula_delta_is_ties_and_zero_rows_only():
+    """ADVICE: ops.per_token_quant_int8 carries the Triton quantizer's name (int8_kernel.py:28-89) but computes the
+    CPU path's arithmetic (eps 1e-7, round-half-even; BASELINE makes that the bit-exact target).  Bound the delta
+    against the Triton formula (eps 1e-10, round-half-away): codes differ only on exact .5 ties, by one LSB; scales
+    differ only on rows whose absmax is below 1e-7."""
+    from oracle import restate
+
+    g = torch.Generator().manual_seed(0)
+    x = (torch.randn(64, 512, generator=g) / 10).bfloat16()
+    x[3] = 0  # all-zero row
+    x[5, :8] = torch.tensor([0.5, 1.5, 2.5, -0.5, -1.5, 127.0, -127.0, 63.5]).bfloat16()  # ties once amax = 127
+    x[5, 8:] = 0
+    q_u8, s = restate.per_token_quant_int8_cpu(x)
+    ours = q_u8.to(torch.int16) - 128
+    xf = x.float()
+    absmax = xf.abs().amax(-1, keepdim=True).clamp_min(1e-10)
+    t = xf * (torch.tensor(127.0) / absmax)
+    triton_q = torch.where(t >= 0, torch.floor(t + 0.5), torch.ceil(t - 0.5)).to(torch.int16)
+    diff = (ours - triton_q).abs()
+    assert int(diff.max()) <= 1
+    ties = (t - torch.trunc(t)).abs() == 0.5
+    assert bool((diff[~ties] == 0).all())
+    assert int(diff[5].sum()) >= 1  # the tie row really exercises the difference
+    triton_s = (absmax / 127).view(-1)
+    differ = s != triton_s
+    assert bool((differ == (xf.abs().amax(-1) < 1e-7)).all())
 
 
 # -------------------------------------------------------------- linear methods ----

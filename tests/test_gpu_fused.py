@@ -38,11 +38,15 @@ def test_silu_and_mul_quant_equals_unfused(mode, M, K, dtype):
     g = torch.Generator(device=DEV).manual_seed(M + K)
     x = (torch.randn(M, 2 * K, generator=g, device=DEV) * 1.5).to(dtype)
     q, s, y = ops.silu_and_mul_quant(x, mode, return_act=True)
-    # producer: <= 1 ulp of `dtype` on the activation (tanh.approx vs exact), then the exact T*T product
+    # producer: tanh.approx.f32 has a maximum relative error of 2^-11 (PTX ISA), i.e. <= 2^-11 absolute on tanh, so
+    # the activation 0.5x(1 + tanh(0.5x)) is within |0.5x| 2^-11 + 1 ulp(T) of the exact-tanh restatement (the
+    # reference's sm_100 kernel has the same error: it IS this formula); then the exact T*T product, one more rounding
     ref = restate.silu_and_mul(x.cpu())
-    act_ref = (x[:, :K].float() * 0.5 * (1 + torch.tanh(x[:, :K].float() * 0.5))).cpu()
+    half = (x[:, :K].float() * 0.5).cpu()
+    act_ref = half * (1 + torch.tanh(half))
     err = (y.float().cpu() - ref.float()).abs()
-    bound = (_ulp(act_ref, dtype) * x[:, K:].float().abs().cpu() * 1.01 + _ulp(ref.float(), dtype))
+    bound = ((half.abs() * 2.0 ** -10.5 + _ulp(act_ref, dtype)) * x[:, K:].float().abs().cpu() * 1.01
+             + _ulp(ref.float(), dtype))
     assert torch.all(err <= bound)
     # quantizer stage: bit-exact against the pinned separate quantizers on the SAME activation rows
     if mode == "int8":

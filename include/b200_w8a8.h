@@ -202,7 +202,9 @@ const char* b2_last_gemm_config(void);
  *   signal_pads_dev  device array of `world` pointers to u32 signal pads of >= 8 KiB each, zeroed once at allocation
  *                    and mapped like the buffers.  Words [0, world * max_blocks) hold the barrier numbers the peers
  *                    post, words [1024, 1024 + max_blocks) this rank's per-CTA barrier counters (device-resident so
- *                    that CUDA-graph replays advance them); nothing is reset between calls.
+ *                    that CUDA-graph replays advance them), word 1536 the time-out record; nothing is reset between
+ *                    calls, so the pads are OWNED by this library: do not use the same symmetric-memory handle for
+ *                    barrier() / put_signal() / wait_signal() of another library.
  *   multicast_ptr    NVSwitch multicast mapping of the buffer, or NULL (then only the one-shot path is available)
  *   out              private [numel] output of this rank (16-byte aligned), dtype bf16 / f16 like the buffers; NULL =
  *                    in place: the sums stay in the symmetric buffer only (two-shot path; saves the copy for
@@ -213,6 +215,14 @@ const char* b2_last_gemm_config(void);
  * sglang_diffusion_b200/comm.py); every rank must make the same call.  No NCCL on this path. */
 int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* signal_pads_dev, void* multicast_ptr, void* out,
                       int64_t numel, int dtype, int rank, int world, int algo, int max_blocks, b2_stream_t stream);
+
+/* Waits of b2_allreduce_symm on a peer.  0 (default): wait for ever -- a late peer (first-iteration skew, weight load,
+ * debugger) is not an error, hangs are the host watchdog's business, as with the reference's custom all-reduce.
+ * ms > 0: a wait gives up after that long (%globaltimer), stores the barrier number in word 1536 of this rank's
+ * signal pad (0 = never timed out) and lets the kernel finish; the result of that call is undefined and the host is
+ * expected to read the word and tear the group down.  Never traps: the CUDA context stays usable.  Process-wide. */
+void b2_set_allreduce_timeout_ms(long long ms);
+long long b2_get_allreduce_timeout_ms(void);
 
 /* Static-weight declaration (calling thread; default 0).  When non-zero the caller promises that the W operand of
  * the following GEMM calls is NOT written by the kernel that precedes the GEMM in its stream (inference weights:

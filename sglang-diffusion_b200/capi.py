@@ -28,6 +28,7 @@ SYMBOLS = [
     "b2_allreduce_symm",
     "b2_quant_int8_rows_sum", "b2_quant_fp8_tensor", "b2_silu_mul_quant", "b2_rmsnorm_quant",
     "b2_quant_fp8_group128_v2", "b2_bmm_e4m3_workspace", "b2_bmm_e4m3",
+    "b2_set_allreduce_timeout_ms", "b2_get_allreduce_timeout_ms",
 ]
 
 if not os.path.isfile(LIB_PATH):
@@ -85,6 +86,9 @@ lib.b2_bmm_e4m3.argtypes = [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _vp, _i6
 for _n in ("b2_quant_int8_rows_sum", "b2_quant_fp8_tensor", "b2_silu_mul_quant", "b2_rmsnorm_quant",
            "b2_quant_fp8_group128_v2", "b2_bmm_e4m3"):
     getattr(lib, _n).restype = _i
+lib.b2_set_allreduce_timeout_ms.argtypes = [ctypes.c_longlong]
+lib.b2_set_allreduce_timeout_ms.restype = None
+lib.b2_get_allreduce_timeout_ms.restype = ctypes.c_longlong
 QMODE_INT8_ROWS, QMODE_FP8_ROWS, QMODE_FP8_GROUP128, QMODE_FP8_GROUP128_V2 = 0, 1, 2, 3
 
 

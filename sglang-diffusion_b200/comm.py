@@ -40,10 +40,23 @@ class SymmAllReduce:
         self.multicast_ptr = int(getattr(self.handle, "multicast_ptr", 0) or 0)
         self.bufs_dev = int(self.handle.buffer_ptrs_dev)
         self.pads_dev = int(self.handle.signal_pad_ptrs_dev)
-        # signal pad layout of csrc/allreduce_symm.cu: words [0, world * blocks) flags, [1024, 1024 + blocks) counters
-        if int(self.handle.signal_pad_size) < 8192:
-            raise ValueError("signal pad smaller than the 8 KiB b2_allreduce_symm needs")
+        # signal pad layout of csrc/allreduce_symm.cu: words [0, world * blocks) flags, [1024, 1024 + blocks) counters,
+        # word 1536 the time-out record.  The pad of this handle is owned by b2_allreduce_symm (barrier numbers only
+        # grow and are never reset): do not call handle.barrier() / put_signal() / wait_signal() on it.
         self.max_blocks = min(128, 1024 // self.world)
+        need = 4 * (1536 + 1)
+        if int(self.handle.signal_pad_size) < need:
+            raise ValueError(f"signal pad of {self.handle.signal_pad_size} bytes is smaller than the {need} b2_allreduce_symm needs")
+
+    @staticmethod
+    def set_timeout_ms(ms: int) -> None:
+        """Bound every wait on a peer (b2_set_allreduce_timeout_ms; 0 = wait for ever, the default)."""
+        capi.lib.b2_set_allreduce_timeout_ms(int(ms))
+
+    def timed_out(self) -> int:
+        """Barrier number at which a wait of this rank gave up (0 = never).  Synchronises the device."""
+        pad = self.handle.get_signal_pad(self.rank, (1537,), torch.uint32)
+        return int(pad[1536].item())
 
     def partial(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
         """[M,N] view of the local symmetric buffer: the GEMM's output operand."""
@@ -60,8 +73,10 @@ class SymmAllReduce:
         stream) over the ranks; returns a fresh private tensor, or -- inplace=True, multicast only -- `partial`
         itself holding the sums (valid until the next call that uses this buffer).  Collective: every rank calls it."""
         out = None if inplace else torch.empty(partial.shape, dtype=partial.dtype, device=partial.device)
-        stream = torch.cuda.current_stream(partial.device).cuda_stream
-        capi.check(capi.lib.b2_allreduce_symm(self.bufs_dev, self.pads_dev, self.multicast_ptr or None,
-                                              None if inplace else out.data_ptr(), partial.numel(),
-                                              _DT[partial.dtype], self.rank, self.world, algo, self.max_blocks, stream))
+        with torch.cuda.device(partial.device):  # the library launches on the current device
+            stream = torch.cuda.current_stream(partial.device).cuda_stream
+            capi.check(capi.lib.b2_allreduce_symm(self.bufs_dev, self.pads_dev, self.multicast_ptr or None,
+                                                  None if inplace else out.data_ptr(), partial.numel(),
+                                                  _DT[partial.dtype], self.rank, self.world, algo, self.max_blocks,
+                                                  stream))
         return partial if inplace else out

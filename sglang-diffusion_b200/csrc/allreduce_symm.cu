@@ -47,6 +47,8 @@ AR_DEVICE uint32_t ld_acquire_sys(const uint32_t* addr) {
 // this rank for CTA b;  [kEpochWord + b] = barrier number CTA b of THIS rank has completed (kept on the device so
 // that a CUDA-graph replay, whose kernel arguments are frozen, still advances).
 constexpr int kEpochWord = 1024;
+// [kTimeoutWord] = barrier number at which a wait of THIS rank gave up (0 = never); see b2_set_allreduce_timeout_ms
+constexpr int kTimeoutWord = 1024 + 512;
 
 // Barrier number `seq` between CTA `blockIdx.x` of all ranks.  A posted release-store to every peer (no NVLink round
 // trip), then an acquire-poll of the local pad.  Barrier numbers only grow and a peer can be at most one barrier
@@ -55,8 +57,13 @@ constexpr int kEpochWord = 1024;
 // RELEASE = false when this CTA has written nothing a peer will read since the last barrier (the partials of the
 // preceding GEMM kernel are already visible at its completion; "I have finished READING" needs no release either:
 // the loads have returned before the dependent stores that precede the bar.sync were issued).
+// A peer that is only late (first-iteration skew, a weight load or a compile on one rank, a debugger) must not poison
+// this rank's CUDA context, so the wait never traps.  timeout_ns == 0 (default) waits for ever, like the reference's
+// custom all-reduce (custom_all_reduce.cuh:204-260) and leaves hangs to the host watchdog; otherwise the wait gives up
+// after timeout_ns of %globaltimer, records the barrier number in word kTimeoutWord of the local pad for the host to
+// read (the result of that call is then undefined) and lets the kernel finish.
 template <bool RELEASE>
-AR_DEVICE void xgpu_barrier(uint32_t* const* pads, int rank, int world, uint32_t seq) {
+AR_DEVICE void xgpu_barrier(uint32_t* const* pads, int rank, int world, uint32_t seq, unsigned long long timeout_ns) {
   __syncthreads();
   if (static_cast<int>(threadIdx.x) < world) {
     const int peer = static_cast<int>(threadIdx.x);
@@ -64,9 +71,18 @@ AR_DEVICE void xgpu_barrier(uint32_t* const* pads, int rank, int world, uint32_t
     if constexpr (RELEASE) st_release_sys(send, seq);
     else st_relaxed_sys(send, seq);
     const uint32_t* recv = pads[rank] + static_cast<size_t>(blockIdx.x) * world + peer;
-    unsigned long long spins = 0;
+    unsigned int spins = 0;
+    unsigned long long t0 = 0;
     while (static_cast<int32_t>(ld_acquire_sys(recv) - seq) < 0) {
-      if (++spins > (1ull << 28)) __trap();  // a peer that never arrives must not hang the box
+      if (timeout_ns != 0 && (++spins & 1023u) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > timeout_ns) {
+          pads[rank][kTimeoutWord] = seq;
+          break;
+        }
+      }
     }
   }
   __syncthreads();
@@ -133,11 +149,11 @@ AR_DEVICE uint4 pack8(const float (&f)[8]) {
 template <bool BF16>
 __global__ void __launch_bounds__(512) allreduce_two_shot_kernel(uint4* const* bufs, uint32_t* const* pads,
                                                                   uint4* mc, uint4* out, long long nvec, int rank,
-                                                                  int world) {
+                                                                  int world, unsigned long long timeout_ns) {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // the next quantizer may come up; it waits for us
   asm volatile("griddepcontrol.wait;" ::: "memory");               // this rank's GEMM (and everything before it) is done
   const uint32_t epoch = pads[rank][kEpochWord + blockIdx.x];
-  xgpu_barrier<false>(pads, rank, world, epoch + 1);  // every rank's GEMM has written its partials (stream order)
+  xgpu_barrier<false>(pads, rank, world, epoch + 1, timeout_ns);  // every rank's GEMM has written its partials (stream order)
   const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
   const long long lane0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   // four independent switch reductions in flight per thread: large (prefill) messages are NVLink-latency x
@@ -152,7 +168,7 @@ __global__ void __launch_bounds__(512) allreduce_two_shot_kernel(uint4* const* b
     for (int u = 0; u < 4; ++u)
       if (v + u * step < nvec) multimem_st(mc + v + u * step, sum[u]);
   }
-  xgpu_barrier<true>(pads, rank, world, epoch + 2);  // the sums of every slice have landed in this rank's buffer
+  xgpu_barrier<true>(pads, rank, world, epoch + 2, timeout_ns);  // the sums of every slice have landed in this rank's buffer
   if (threadIdx.x == 0) pads[rank][kEpochWord + blockIdx.x] = epoch + 2;
   if (out == nullptr) return;  // in place: the caller consumes the sums from its symmetric buffer
   const uint4* mine = bufs[rank];
@@ -171,11 +187,12 @@ __global__ void __launch_bounds__(512) allreduce_two_shot_kernel(uint4* const* b
 
 template <bool BF16>
 __global__ void __launch_bounds__(512) allreduce_one_shot_kernel(uint4* const* bufs, uint32_t* const* pads, uint4* out,
-                                                                  long long nvec, int rank, int world) {
+                                                                  long long nvec, int rank, int world,
+                                                                  unsigned long long timeout_ns) {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");
   const uint32_t epoch = pads[rank][kEpochWord + blockIdx.x];
-  xgpu_barrier<false>(pads, rank, world, epoch + 1);
+  xgpu_barrier<false>(pads, rank, world, epoch + 1, timeout_ns);
   const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
   for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += stride) {
     float acc[8];
@@ -188,13 +205,19 @@ __global__ void __launch_bounds__(512) allreduce_one_shot_kernel(uint4* const* b
     }
     out[v] = pack8<BF16>(acc);
   }
-  xgpu_barrier<false>(pads, rank, world, epoch + 2);  // every peer has read this rank's partials: the buffer may be reused
+  xgpu_barrier<false>(pads, rank, world, epoch + 2, timeout_ns);  // every peer has read this rank's partials: the buffer may be reused
   if (threadIdx.x == 0) pads[rank][kEpochWord + blockIdx.x] = epoch + 2;
 }
 
 }  // namespace b2
 
 using namespace b2;
+
+#include <atomic>
+static std::atomic<long long> g_ar_timeout_ms{0};
+
+extern "C" void b2_set_allreduce_timeout_ms(long long ms) { g_ar_timeout_ms.store(ms < 0 ? 0 : ms); }
+extern "C" long long b2_get_allreduce_timeout_ms(void) { return g_ar_timeout_ms.load(); }
 
 extern "C" int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* signal_pads_dev, void* multicast_ptr,
                                  void* out, int64_t numel, int dtype, int rank, int world, int algo,
@@ -237,15 +260,16 @@ extern "C" int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* si
   cfg.numAttrs = 1;
   uint4* mc = static_cast<uint4*>(multicast_ptr);
   uint4* o = static_cast<uint4*>(out);
+  const unsigned long long tmo = static_cast<unsigned long long>(g_ar_timeout_ms.load()) * 1000000ull;
   cudaError_t le;
   if (two_shot) {
     le = dtype == B2_DTYPE_BF16
-             ? cudaLaunchKernelEx(&cfg, allreduce_two_shot_kernel<true>, bufs, signal_pads_dev, mc, o, nvec, rank, world)
-             : cudaLaunchKernelEx(&cfg, allreduce_two_shot_kernel<false>, bufs, signal_pads_dev, mc, o, nvec, rank, world);
+             ? cudaLaunchKernelEx(&cfg, allreduce_two_shot_kernel<true>, bufs, signal_pads_dev, mc, o, nvec, rank, world, tmo)
+             : cudaLaunchKernelEx(&cfg, allreduce_two_shot_kernel<false>, bufs, signal_pads_dev, mc, o, nvec, rank, world, tmo);
   } else {
     le = dtype == B2_DTYPE_BF16
-             ? cudaLaunchKernelEx(&cfg, allreduce_one_shot_kernel<true>, bufs, signal_pads_dev, o, nvec, rank, world)
-             : cudaLaunchKernelEx(&cfg, allreduce_one_shot_kernel<false>, bufs, signal_pads_dev, o, nvec, rank, world);
+             ? cudaLaunchKernelEx(&cfg, allreduce_one_shot_kernel<true>, bufs, signal_pads_dev, o, nvec, rank, world, tmo)
+             : cudaLaunchKernelEx(&cfg, allreduce_one_shot_kernel<false>, bufs, signal_pads_dev, o, nvec, rank, world, tmo);
   }
   if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm launch: %s", cudaGetErrorString(le));
   cudaError_t e = cudaGetLastError();

@@ -164,6 +164,43 @@ def linear_int8(M, N, K):
     line("int8 linear (q+mm)", M, N, K, t, 2.0 * M * N * K, 2 * M * K + N * K + 2 * M * N + 4 * N)
 
 
+def fused(kind, mode, M, K):
+    """Producer-fused quantizers against the unfused pair (torch eager producer + separate quantizer).  Bytes =
+    algorithmic bytes of the FUSED op: silu 2*2K in + K (+scales) out per row; rmsnorm with residual 2K + 2K in,
+    2K (residual) + K out."""
+    if kind == "silu":
+        nset = copies_for(5 * M * K)
+        xs = [torch.randn(M, 2 * K, device=dev).bfloat16() for _ in range(nset)]
+        fns = [(lambda x=x: b2.silu_and_mul_quant(x, mode)) for x in xs]
+        byts = 4 * M * K + M * K + (4 * M if "group" not in mode else 4 * M * K // 128)
+    else:
+        nset = copies_for(7 * M * K)
+        xs = [(torch.randn(M, K, device=dev).bfloat16(), torch.randn(M, K, device=dev).bfloat16()) for _ in range(nset)]
+        w = torch.ones(K, device=dev).bfloat16()
+        fns = [(lambda x=x, r=r: b2.rmsnorm_quant(x, w, 1e-6, residual=r, mode=mode)) for x, r in xs]
+        byts = 6 * M * K + M * K + (4 * M if "group" not in mode else 4 * M * K // 128)
+    t = timed(fns)
+    line(f"{kind}->{mode}", M, 0, K, t, 0.0, byts)
+
+
+if "fused" in want:
+    print("# producer-fused quantizers (bytes = algorithmic bytes of the fused op)")
+    for M, K in ((8192, 14336), (8192, 4096), (32768, 5120), (4096, 2048), (16, 14336)):
+        for mode in ("int8", "fp8", "fp8_group128_v2"):
+            fused("silu", mode, M, K)
+        for mode in ("int8", "fp8", "fp8_group128"):
+            fused("rms", mode, M, K)
+    for M, K in ((8192, 4096), (8192, 14336)):
+        x = (torch.randn(M, K, device=dev) / 10).bfloat16()
+        nset = copies_for(3 * M * K)
+        xs = [(torch.randn(M, K, device=dev) / 10).bfloat16() for _ in range(nset)]
+        st = torch.tensor([0.01], device=dev)
+        t = timed([(lambda x=x: b2.scaled_fp8_quant(x, st)) for x in xs])
+        line("per_tensor static", M, 0, K, t, 0.0, 3 * M * K)
+        t = timed([(lambda x=x: b2.scaled_fp8_quant(x)) for x in xs])
+        line("per_tensor dynamic", M, 0, K, t, 0.0, 5 * M * K)
+        t = timed([(lambda x=x: b2.sglang_per_token_group_quant_fp8(x, 128, column_major_scales=True, enable_v2=True)) for x in xs])
+        line("group128 v2", M, 0, K, t, 0.0, 3 * M * K + 4 * M * K // 128)
 if "splitk" in want:
     # decode kernel (gemm_splitk_sm100.cu): the planner's pick, then every forced (BN, S), per C2 decode shape
     for K, N in ((4096, 6144), (4096, 28672), (14336, 4096), (8192, 1280), (1024, 8192)):

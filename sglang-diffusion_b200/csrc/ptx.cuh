@@ -103,6 +103,20 @@ B2_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 
+// Non-blocking probe of the phase: returns at once (mbarrier.try_wait suspends the warp for a hardware time slice
+// of ~150-250 clocks even when the phase has already completed).
+B2_DEVICE bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
 B2_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
 #if B2_WAIT_WATCHDOG
   // Reading %globaltimer costs several hundred cycles (measured: it put a ~580-cycle floor under

@@ -142,7 +142,8 @@ __global__ void __launch_bounds__(128, 1) mma_ring(const uint8_t* __restrict__ s
     for (int g = 0; g < groups; ++g) {
       long long c0 = clock64();
       if (g >= S && !(variant & 2)) {
-        mbar_wait(&bars[slot], phase ^ 1);  // the commit of the previous trip round this ring slot
+        if (variant & 16) { while (!mbar_test_wait(&bars[slot], phase ^ 1)) {} }
+        else mbar_wait(&bars[slot], phase ^ 1);  // the commit of the previous trip round this ring slot
         if (hop) { const long long t0 = clock64(); while (clock64() - t0 < hop) {} }
       }
       long long c1 = clock64();
@@ -151,8 +152,10 @@ __global__ void __launch_bounds__(128, 1) mma_ring(const uint8_t* __restrict__ s
       const int buf = g & (NBUF - 1);
       const uint64_t da = make_smem_desc_sw128(smem_u32(sa + buf * A_BYTES));
       const uint64_t db = make_smem_desc_sw128(smem_u32(sb + buf * B_BYTES));
-      const uint32_t d = tmem_base + ((same_acc || !((g >> 5) & 1)) ? 0 : BN);  // switch accumulator every 32 groups
-      for (int k = 0; k < G; ++k) umma<KIND, CG>(d, da + 2 * (k & 3), db + 2 * (k & 3), idesc, (g | k) != 0);
+      uint32_t d = tmem_base + ((same_acc || !((g >> 5) & 1)) ? 0 : BN);  // switch accumulator every 32 groups
+      if (variant & 8) d = tmem_base + (g & (512 / BN - 1)) * BN;  // block-wise pattern: a fresh slot per group
+      for (int k = 0; k < G; ++k)
+        umma<KIND, CG>(d, da + 2 * (k & 3), db + 2 * (k & 3), idesc, (variant & 8) ? k != 0 : (g | k) != 0);
       long long c3 = clock64();
       if (CG == 1) umma_commit(&bars[slot]); else umma_commit_cg2(&bars[slot], 0x1);
       long long c4 = clock64();
@@ -227,6 +230,18 @@ int main(int argc, char** argv) {
   uint8_t* d;
   cudaMalloc(&d, h.size());
   cudaMemcpy(d, h.data(), h.size(), cudaMemcpyHostToDevice);
+  if (argc > 1 && !strcmp(argv[1], "ring128")) {
+    // the block-wise fp8 GEMM's issue pattern: groups of 4 MMAs (one 128-deep K block), a commit per group
+    for (int variant : {8, 8 | 16, 8 | 2})
+      for (int G : {4})
+        for (int S : {4, 8}) {
+          run_ring<MmaKind::F8, 1, 128>("f8 1cta128x128", d, sms, G, S, 0, 1, variant);
+          run_ring<MmaKind::F8, 2, 128>("f8 2cta256x128", d, sms, G, S, 0, 1, variant);
+          run_ring<MmaKind::F8, 1, 256>("f8 1cta128x256", d, sms, G, S, 0, 1, variant);
+          run_ring<MmaKind::F8, 2, 256>("f8 2cta256x256", d, sms, G, S, 0, 1, variant);
+        }
+    return 0;
+  }
   if (argc > 1 && !strcmp(argv[1], "ring")) {
     const bool zero = argc > 2 && !strcmp(argv[2], "zeros");
     if (zero) cudaMemset(d, 0, h.size());

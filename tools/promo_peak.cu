@@ -62,28 +62,44 @@ __global__ void __launch_bounds__(64 + 32 * PW, 1)
   long long t0 = clock64();
   if (warp == 0) {
     if (do_mma && lane == 0) {
-      constexpr uint32_t idesc = make_idesc<MmaKind::F8>(128, 128);
+      constexpr uint32_t idesc128 = make_idesc<MmaKind::F8>(128, 128);
+      constexpr uint32_t idesc256 = make_idesc<MmaKind::F8>(128, 256);
+      const uint32_t idesc = do_mma == 3 ? idesc256 : idesc128;
       uint32_t phase[4] = {0, 0, 0, 0};
+      if (do_mma == 3) iters /= 2;  // N = 256: each K block carries twice the flops
       for (int kb = 0; kb < iters; ++kb) {
-        const int slot = kb & 3;
-        if (kb >= 4) {  // at most 4 K blocks (16 MMAs) in flight
+        const int slot = do_mma == 2 ? 0 : (do_mma == 3 ? (kb & 1) * 2 : (kb & 3));
+        const int nk = do_mma == 5 ? 8 : 4;  // 5: chains of 8 MMAs (a 256-deep K block)
+        if (do_mma == 5 && kb >= iters / 2) break;
+        if ((do_mma == 1 || do_mma >= 4) ? kb >= 4 : (do_mma == 3 ? kb >= 2 : kb >= 1)) {  // at most 4 K blocks (16 MMAs) in flight
           mbar_wait(&bars[slot], phase[slot]);
           phase[slot] ^= 1;
         }
         const uint64_t da = make_smem_desc_sw128(smem_u32(smem + slot * 32768));
         const uint64_t db = make_smem_desc_sw128(smem_u32(smem + slot * 32768 + 16384));
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma<MmaKind::F8, 1>(tmem_base + slot * 128, da + 2 * k, db + 2 * k, idesc, k != 0);
+        for (int k = 0; k < 8; ++k)
+          if (k < nk)
+            umma<MmaKind::F8, 1>(tmem_base + slot * 128, da + 2 * (k & 3), db + 2 * (k & 3), idesc,
+                                 do_mma == 4 ? (kb | k) != 0 : k != 0);
         umma_commit(&bars[slot]);
       }
-      for (int s = 0; s < 4 && s < iters; ++s) {
-        const int slot = (iters - 1 - s) & 3;
-        mbar_wait(&bars[slot], phase[slot]);
-        phase[slot] ^= 1;
+      if (do_mma == 1 || do_mma >= 4) {
+        if (do_mma == 5) iters /= 2;
+        for (int s = 0; s < 4 && s < iters; ++s) {
+          const int slot = (iters - 1 - s) & 3;
+          mbar_wait(&bars[slot], phase[slot]);
+          phase[slot] ^= 1;
+        }
+      } else if (do_mma == 2) {
+        mbar_wait(&bars[0], phase[0]);
+      } else {
+        mbar_wait(&bars[0], phase[0]);
+        mbar_wait(&bars[2], phase[2]);
       }
       out[blockIdx.x * 2 + 0] = clock64() - t0;
     }
-  } else if (warp >= 2) {
+  } else if (warp >= 2 && do_fma != 2) {
     const int ew = warp - 2;
     const uint32_t t = tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) + (ew >> 2) * CW;
     float acc[CW];
@@ -167,6 +183,12 @@ int main() {
     cudaMemcpy(seed, h, 1 << 20, cudaMemcpyHostToDevice);
     free(h);
   }
+  // MMA alone in the promotion pattern (no TMEM reader): 4 rotating 128-col slots / one slot / two 256-col slots
+  run<8, 32>(seed, 1, 2);
+  run<8, 32>(seed, 2, 2);
+  run<8, 32>(seed, 3, 2);
+  run<8, 32>(seed, 4, 2);  // always accumulate
+  run<8, 32>(seed, 5, 2);  // chains of 8
   for (int mma = 0; mma < 2; ++mma)
     for (int fma = 0; fma < 2; ++fma) {
       run<4, 32>(seed, mma, fma);

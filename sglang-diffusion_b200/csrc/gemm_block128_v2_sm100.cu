@@ -1,0 +1,515 @@
+// Block-wise (1x128 / 128x128 scales) e4m3 GEMM, second generation: parity-split promotion.
+//
+// Same arithmetic contract as gemm_block128_sm100.cu (fp8_blockwise_scaled_mm,
+// sgl-kernel/csrc/gemm/fp8_blockwise_gemm_kernel.cu:368-465): every 128-deep K block is multiplied into its own TMEM
+// slot with a non-accumulating MMA chain and folded into fp32 register accumulators with ONE fma per element,
+// acc += (SFA[m,kb] * SFB[nb,kb]) * partial.
+//
+// What changed, and why (profiles/r02f_block128_handshake.md): the first kernel ran at ~500 clocks per K block against
+// a 256-clock MMA, and did so even with the MMAs or the FMAs compiled out -- it is bound by the slot hand-shake.  Its
+// roles step two K blocks at a time (an mbarrier wait costs ~100 clocks even when the phase is complete, a remote
+// arrive ~215), which leaves only TWO steps in flight on the four-slot ring.  Here
+//   * the MMA warp walks the ring one K block at a time (four hand-shakes in flight), and
+//   * the eight promotion warps are split by K-block PARITY: the even group (4 warps, one per TMEM lane quarter) drains
+//     slots 0/2, the odd group slots 1/3, each warp folding all 128 columns of its 32 rows.  A warp therefore visits
+//     the ring every OTHER K block and moves twice the data per visit, so its fixed costs (wait, TMEM-load latency,
+//     arrive) are paid half as often, and the two groups overlap each other on the same scheduler.
+//   * at the end of a tile the two partial sums of a row are added through shared memory (fixed order even + odd),
+//     each warp of a pair finishing and storing 64 of the 128 columns.
+#include <cstdlib>
+
+#include "gemm_common.cuh"
+
+namespace b2 {
+
+constexpr int V2_BN = 128;
+constexpr int V2_SLOTS = 4;
+constexpr int V2_PROMO_WARPS = 8;
+constexpr int V2_PROMO_WARP0 = 2;                               // warps 0 (TMA), 1 (MMA), 2..9 promotion
+constexpr int V2_THREADS = 32 * (V2_PROMO_WARP0 + V2_PROMO_WARPS);  // 320
+constexpr int V2_SC = 16;                                       // K blocks per shared-memory scale chunk
+constexpr int V2_XBUF_BYTES = 64 * 32 * 4;                      // one warp's exchange buffer: 64 columns x 32 rows fp32
+
+struct BlockwiseV2Params {
+  const float* sfa;
+  const float* sfb;
+  int64_t sfa_m_stride, sfa_k_stride, sfb_n_stride, sfb_k_stride;
+  const void* bias;
+  int bias_dtype;
+  int M, N, K;
+  int num_m_blocks, num_n_blocks, num_kb;
+  int stages;
+  int group_m;
+  int band_n;
+  uint64_t policy_a, policy_b;
+  int a_box_rows;
+  unsigned long long* prof;  // [0] MMA waits [2] producer waits [3] promotion waits for a partial [5] scales+barrier
+                             // [6] merge + store [4] CTA life
+  int debug_flags;
+};
+
+template <int N>
+B2_DEVICE void v2_promote(float* acc, const uint32_t (&x)[N], float scale) {
+  uint64_t s2;
+  asm("mov.b64 %0, {%1, %1};" : "=l"(s2) : "f"(scale));
+#pragma unroll
+  for (int j = 0; j < N; j += 2) {
+    asm("{\n\t.reg .b64 xx, cc;\n\t"
+        "mov.b64 xx, {%2, %3};\n\t"
+        "mov.b64 cc, {%0, %1};\n\t"
+        "fma.rn.f32x2 cc, xx, %4, cc;\n\t"
+        "mov.b64 {%0, %1}, cc;\n\t}"
+        : "+f"(acc[j]), "+f"(acc[j + 1])
+        : "r"(x[j]), "r"(x[j + 1]), "l"(s2));
+  }
+}
+
+B2_DEVICE void v2_tile_coords(int tile, const BlockwiseV2Params& p, int& m_blk, int& n_blk) {
+  const int fast_blocks = p.band_n ? p.num_n_blocks : p.num_m_blocks;
+  const int slow_blocks = p.band_n ? p.num_m_blocks : p.num_n_blocks;
+  const int band_tiles = p.group_m * slow_blocks;
+  const int band = tile / band_tiles;
+  const int in_band = tile - band * band_tiles;
+  const int first = band * p.group_m;
+  const int width = min(p.group_m, fast_blocks - first);
+  const int f = first + in_band % width;
+  const int s = in_band / width;
+  m_blk = p.band_n ? s : f;
+  n_blk = p.band_n ? f : s;
+}
+
+B2_DEVICE void pair_bar_sync(int quarter) {  // the even and the odd promotion warp of one lane quarter
+  asm volatile("bar.sync %0, 64;" ::"r"(2 + quarter) : "memory");
+}
+
+template <int OUT_KIND, int CG>
+__global__ void __launch_bounds__(V2_THREADS, 1)
+    gemm_block128_v2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                            const __grid_constant__ CUtensorMap tmap_d, const BlockwiseV2Params p) {
+  constexpr int BN = V2_BN;
+  constexpr int B_ROWS = BN / CG;
+  constexpr uint32_t A_STAGE_BYTES = BM * BK;
+  constexpr uint32_t B_STAGE_BYTES = B_ROWS * BK;
+  constexpr uint32_t TMEM_COLS = V2_SLOTS * BN;  // 512
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  const int stages = p.stages;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + static_cast<size_t>(stages) * A_STAGE_BYTES;
+  uint8_t* smem_x = smem_b + static_cast<size_t>(stages) * B_STAGE_BYTES;            // 8 warps x 8 KB exchange
+  float* smem_sfa = reinterpret_cast<float*>(smem_x + V2_PROMO_WARPS * V2_XBUF_BYTES);  // [2][V2_SC][128]
+  float* smem_sfb = smem_sfa + 2 * V2_SC * BM;                                          // [2][V2_SC]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_sfb + 2 * V2_SC);
+  uint64_t* empty_bar = full_bar + stages;
+  uint64_t* part_full = empty_bar + stages;
+  uint64_t* part_empty = part_full + V2_SLOTS;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(part_empty + V2_SLOTS);
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const long long t_start = p.prof ? clock64() : 0;
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;  // tiles of (BM*CG) x BN
+  const int cta_rank = CG == 1 ? 0 : static_cast<int>(cluster_ctarank());
+  const int unit = CG == 1 ? static_cast<int>(blockIdx.x) : static_cast<int>(blockIdx.x >> 1);
+  const int num_units = CG == 1 ? static_cast<int>(gridDim.x) : static_cast<int>(gridDim.x >> 1);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    tma_prefetch_desc(&tmap_d);
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < V2_SLOTS; ++i) {
+      mbar_init(&part_full[i], 1);
+      mbar_init(&part_empty[i], (V2_PROMO_WARPS / 2) * CG);  // the four warps of ONE parity group, in every CTA
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<CG>(tmem_ptr, TMEM_COLS);
+  tc_fence_before_sync();
+  if constexpr (CG == 1) {
+    __syncthreads();
+  } else {
+    __syncwarp();
+    cluster_sync_all();
+  }
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer ====
+    int stage = 0;
+    uint32_t phase = 0;
+    const uint32_t tx_bytes = (static_cast<uint32_t>(p.a_box_rows) * BK + B_STAGE_BYTES) * CG;
+    long long prof_wait = 0;
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
+      int m_blk, n_blk;
+      v2_tile_coords(tile, p, m_blk, n_blk);
+      const int m_row = (m_blk * CG + cta_rank) * BM;
+      const int n_row = n_blk * BN + cta_rank * B_ROWS;
+      for (int kb = 0; kb < p.num_kb; kb += 2) {
+        const int n2 = kb + 1 < p.num_kb ? 2 : 1;
+        const int stage1 = stage + 1 == stages ? 0 : stage + 1;
+        const uint32_t phase1 = stage + 1 == stages ? phase ^ 1 : phase;
+        const long long w0 = p.prof ? clock64() : 0;
+        mbar_wait_lanes(&empty_bar[lane == 1 ? stage1 : stage], (lane == 1 ? phase1 : phase) ^ 1, lane < n2);
+        if (p.prof) prof_wait += clock64() - w0;
+        if (elect_one()) {
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            if (j < n2) {
+              const int st_j = j ? stage1 : stage;
+              uint8_t* a_dst = smem_a + static_cast<size_t>(st_j) * A_STAGE_BYTES;
+              uint8_t* b_dst = smem_b + static_cast<size_t>(st_j) * B_STAGE_BYTES;
+              if constexpr (CG == 1) {
+                mbar_arrive_expect_tx(&full_bar[st_j], tx_bytes);
+                tma_load_2d(a_dst, &tmap_a, &full_bar[st_j], (kb + j) * BK, m_row, p.policy_a);
+                tma_load_2d(b_dst, &tmap_b, &full_bar[st_j], (kb + j) * BK, n_row, p.policy_b);
+              } else {
+                if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[st_j], tx_bytes);
+                const uint32_t bar0 = smem_u32(&full_bar[st_j]) & kPeerBitMask;
+                tma_load_2d_cg2(smem_u32(a_dst), &tmap_a, bar0, (kb + j) * BK, m_row, p.policy_a);
+                tma_load_2d_cg2(smem_u32(b_dst), &tmap_b, bar0, (kb + j) * BK, n_row, p.policy_b);
+              }
+            }
+          }
+        }
+        __syncwarp();
+        for (int j = 0; j < n2; ++j) {
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    if (p.prof && lane == 0) p.prof[blockIdx.x * 8 + 2] = static_cast<unsigned long long>(prof_wait);
+  } else if (warp == 1) {
+    // ======================================================= MMA issuer ====
+    // ONE K block per step: lane 0 waits for the operand stage, lane 1 for the TMEM slot, in one try_wait round.
+    if (cta_rank == 0) {
+      constexpr uint32_t idesc = make_idesc<MmaKind::F8>(BM * CG, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t it = 0;  // running K-block counter: slot = it & 3, slot phase = (it >> 2) & 1
+      long long prof_full = 0;
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          {
+            uint64_t* bar = lane == 0 ? &full_bar[stage] : &part_empty[it & (V2_SLOTS - 1)];
+            const uint32_t par = lane == 0 ? phase : (((it >> 2) & 1) ^ 1);
+            const long long w0 = p.prof ? clock64() : 0;
+            mbar_wait_lanes(bar, par, lane < 2);
+            if (p.prof) prof_full += clock64() - w0;
+          }
+          tc_fence_after_sync();
+          if (elect_one()) {
+            const int slot = static_cast<int>(it & (V2_SLOTS - 1));
+            const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(slot * BN);
+            const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES));
+            const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
+            if (!(p.debug_flags & 1)) {
+#pragma unroll
+              for (int k = 0; k < BK / UMMA_K; ++k) {
+                umma<MmaKind::F8, CG>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
+                                      db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, k != 0 ? 1u : 0u);
+              }
+            }
+            if constexpr (CG == 1) {
+              umma_commit(&empty_bar[stage]);
+              umma_commit(&part_full[slot]);
+            } else {
+              umma_commit_cg2(&empty_bar[stage], 0x3);
+              umma_commit_cg2(&part_full[slot], 0x3);
+            }
+          }
+          __syncwarp();
+          ++it;
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+      if (p.prof && lane == 0) p.prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(prof_full);
+    }
+  } else {
+    // ============================================== promotion + epilogue ====
+    const int ew = warp - V2_PROMO_WARP0;  // 0..7
+    const int quarter = warp & 3;          // TMEM lane quarter this warp may read
+    const int g = ew >> 2;                 // parity group: K blocks with (running index & 1) == g
+    const int ptid = ew * 32 + lane;       // 0..255
+    float* xbuf_mine = reinterpret_cast<float*>(smem_x + static_cast<size_t>(ew) * V2_XBUF_BYTES);
+    float* xbuf_peer = reinterpret_cast<float*>(smem_x + static_cast<size_t>(ew ^ 4) * V2_XBUF_BYTES);
+    const bool has_bias = p.bias != nullptr;
+    uint32_t it0 = 0;  // running K-block index of the first K block of the current tile
+    long long prof_part = 0, prof_sc = 0, prof_st = 0;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+
+    auto issue_scales = [&](int m_blk_, int n_blk_, int chunk, int b) {
+      const int m_base = (m_blk_ * CG + cta_rank) * BM;
+      float* dst_a = smem_sfa + b * (V2_SC * BM);
+      float* dst_b = smem_sfb + b * V2_SC;
+      const int r = ptid & (BM - 1);
+      const bool r_ok = m_base + r < p.M;
+      const float* src_row = p.sfa + static_cast<int64_t>(r_ok ? m_base + r : 0) * p.sfa_m_stride;
+#pragma unroll
+      for (int i = 0; i < V2_SC / 2; ++i) {
+        const int kl = (ptid >> 7) + 2 * i;
+        const int kb = chunk * V2_SC + kl;
+        if (r_ok && kb < p.num_kb) cp_async_4(dst_a + kl * BM + r, src_row + static_cast<int64_t>(kb) * p.sfa_k_stride);
+      }
+      if (ptid < V2_SC) {
+        const int kb = chunk * V2_SC + ptid;
+        if (kb < p.num_kb)
+          cp_async_4(dst_b + ptid, p.sfb + static_cast<int64_t>(n_blk_) * p.sfb_n_stride +
+                                       static_cast<int64_t>(kb) * p.sfb_k_stride);
+      }
+      cp_async_commit();
+    };
+    const int nchunks = (p.num_kb + V2_SC - 1) / V2_SC;
+    int sbuf = 0;
+    if (unit < num_tiles) {
+      int m0, n0;
+      v2_tile_coords(unit, p, m0, n0);
+      issue_scales(m0, n0, 0, 0);
+    }
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
+      int m_blk, n_blk;
+      v2_tile_coords(tile, p, m_blk, n_blk);
+      const int row0 = (m_blk * CG + cta_rank) * BM + quarter * 32;
+      const int col0 = n_blk * BN + g * 64;
+
+      float acc[128];
+#pragma unroll
+      for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+      uint32_t r0[16], r1[16];
+
+      // the previous tile's TMA store has read its staging box (which lives in the partner's exchange buffer)
+      tma_store_wait_read<0>();
+      for (int chunk = 0; chunk < nchunks; ++chunk) {
+        {
+          const long long w0 = p.prof ? clock64() : 0;
+          cp_async_wait<0>();  // my copies of this chunk have landed ...
+          promo_bar_sync();    // ... so have everybody's, and everybody is done with the other buffer
+          if (p.prof) prof_sc += clock64() - w0;
+        }
+        if (chunk + 1 < nchunks) {
+          issue_scales(m_blk, n_blk, chunk + 1, sbuf ^ 1);
+        } else if (tile + num_units < num_tiles) {
+          int m1, n1;
+          v2_tile_coords(tile + num_units, p, m1, n1);
+          issue_scales(m1, n1, 0, sbuf ^ 1);
+        }
+        const float* sa_s = smem_sfa + sbuf * (V2_SC * BM) + quarter * 32 + lane;
+        const float* sb_s = smem_sfb + sbuf * V2_SC;
+        const int kb_begin = chunk * V2_SC;
+        const int kb_end = min(p.num_kb, kb_begin + V2_SC);
+        // first K block of this chunk that belongs to my parity group
+        for (int kb = kb_begin + ((static_cast<int>(it0) + kb_begin + g) & 1); kb < kb_end; kb += 2) {
+          const uint32_t itk = it0 + static_cast<uint32_t>(kb);
+          const int slot = static_cast<int>(itk & (V2_SLOTS - 1));
+          const uint32_t col = static_cast<uint32_t>(slot * BN);
+          const float scale = __fmul_rn(sa_s[(kb - kb_begin) * BM], sb_s[kb - kb_begin]);
+          {
+            const long long w0 = p.prof ? clock64() : 0;
+            mbar_wait_lanes(&part_full[slot], (itk >> 2) & 1, lane == 0);
+            if (p.prof) prof_part += clock64() - w0;
+          }
+          tc_fence_after_sync();
+          // eight 16-column chunks, the load of chunk c+1 in flight under the FMAs of chunk c (two 16-register
+          // buffers: 128 accumulators + 2 x 32 would spill at the 168 registers a 320-thread CTA gets)
+          tmem_ld_32x32b_x16(t_lane + col, r0);
+#pragma unroll
+          for (int c = 0; c < 7; ++c) {
+            tmem_ld_wait();
+            if (c & 1) {
+              tmem_ld_32x32b_x16(t_lane + col + (c + 1) * 16, r0);
+              if (!(p.debug_flags & 2)) v2_promote<16>(acc + c * 16, r1, scale);
+            } else {
+              tmem_ld_32x32b_x16(t_lane + col + (c + 1) * 16, r1);
+              if (!(p.debug_flags & 2)) v2_promote<16>(acc + c * 16, r0, scale);
+            }
+          }
+          tmem_ld_wait();
+          // the whole slot is in registers: hand it back
+          tc_fence_before_sync();
+          __syncwarp();
+          if (lane == 0) {
+            if constexpr (CG == 1) mbar_arrive(&part_empty[slot]);
+            else mbar_arrive_cluster(&part_empty[slot], 0);
+          }
+          if (!(p.debug_flags & 2)) v2_promote<16>(acc + 112, r1, scale);
+        }
+        sbuf ^= 1;
+      }
+      it0 += static_cast<uint32_t>(p.num_kb);
+
+      // ---- merge the two parity sums of my rows, then bias, cast, stage and TMA-store my 64 columns ----
+      const long long ws0 = p.prof ? clock64() : 0;
+      if (g == 0) {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) xbuf_mine[j * 32 + lane] = acc[64 + j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) xbuf_mine[j * 32 + lane] = acc[j];
+      }
+      pair_bar_sync(quarter);
+      float v[64];
+      if (g == 0) {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) v[j] = __fadd_rn(acc[j], xbuf_peer[j * 32 + lane]);  // even + odd
+      } else {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) v[j] = __fadd_rn(xbuf_peer[j * 32 + lane], acc[64 + j]);
+      }
+      __syncwarp();  // every lane has read the partner's buffer: its first 4 KB become my staging box
+      uint8_t* stage_buf = reinterpret_cast<uint8_t*>(xbuf_peer);
+#pragma unroll
+      for (int c8 = 0; c8 < 8; ++c8) {
+        const int colg = col0 + c8 * 8;
+        float o8[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o8[j] = v[c8 * 8 + j];
+        if (has_bias && colg < p.N) {
+          float bi[8];
+          load_bias8(p.bias, p.bias_dtype, colg, bi);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o8[j] = __fadd_rn(o8[j], bi[j]);
+        }
+        uint4 o;
+        o.x = pack16<OUT_KIND>(o8[0], o8[1]);
+        o.y = pack16<OUT_KIND>(o8[2], o8[3]);
+        o.z = pack16<OUT_KIND>(o8[4], o8[5]);
+        o.w = pack16<OUT_KIND>(o8[6], o8[7]);
+        const int chunk16 = c8 ^ (lane & 7);
+        *reinterpret_cast<uint4*>(stage_buf + lane * 128 + chunk16 * 16) = o;
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (row0 < p.M && col0 < p.N && elect_one()) {
+        tma_store_2d(&tmap_d, stage_buf, col0, row0);
+        tma_store_commit();
+      }
+      if (p.prof) prof_st += clock64() - ws0;
+    }
+    tma_store_wait_all<0>();
+    if (p.prof && warp == V2_PROMO_WARP0 && lane == 0) {
+      p.prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(prof_part);
+      p.prof[blockIdx.x * 8 + 5] = static_cast<unsigned long long>(prof_sc);
+      p.prof[blockIdx.x * 8 + 6] = static_cast<unsigned long long>(prof_st);
+    }
+  }
+  if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);
+
+  tc_fence_before_sync();
+  if constexpr (CG == 1) {
+    __syncthreads();
+  } else {
+    __syncwarp();
+    cluster_sync_all();
+  }
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc<CG>(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------ host ----
+
+static int v2_fixed_smem() { return V2_PROMO_WARPS * V2_XBUF_BYTES + 2 * V2_SC * BM * 4 + 2 * V2_SC * 4 + 256; }
+
+template <int OUT_KIND, int CG>
+static int launch_v2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const BlockwiseV2Params& p,
+                     int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
+  auto kern = gemm_block128_v2_kernel<OUT_KIND, CG>;
+  static thread_local int attr_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr_dev != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+    if (e != cudaSuccess) {
+      snprintf(err, err_len, "cudaFuncSetAttribute(max dynamic smem): %s", cudaGetErrorString(e));
+      return B2_ERR_CUDA;
+    }
+    attr_dev = dev;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(V2_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = CG;
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p);
+  if (e != cudaSuccess) {
+    snprintf(err, err_len, "block-wise gemm (v2) kernel launch: %s", cudaGetErrorString(e));
+    return B2_ERR_CUDA;
+  }
+  count_launch();
+  return B2_OK;
+}
+
+// cg: 1 = 1-CTA 128x128 tiles, 2 = 2-CTA 256x128 tiles
+int gemm_launch_blockwise_v2(const GemmArgs& a, int cg, int debug_flags, const char** used_config, cudaStream_t st,
+                             char* err, size_t err_len) {
+  const int sms = device_sm_count();
+  if (used_config) *used_config = cg == 2 ? "2cta_256x128_block128_v2" : "1cta_128x128_block128_v2";
+  const int b_rows = V2_BN / cg;
+
+  BlockwiseV2Params p;
+  p.sfa = a.As;
+  p.sfb = a.Bs;
+  p.sfa_m_stride = a.sfa_m_stride;
+  p.sfa_k_stride = a.sfa_k_stride;
+  p.sfb_n_stride = a.sfb_n_stride;
+  p.sfb_k_stride = a.sfb_k_stride;
+  p.bias = a.bias;
+  p.bias_dtype = a.bias_dtype;
+  p.M = a.M;
+  p.N = a.N;
+  p.K = a.K;
+  p.num_m_blocks = (a.M + BM * cg - 1) / (BM * cg);
+  p.num_n_blocks = (a.N + V2_BN - 1) / V2_BN;
+  p.num_kb = (a.K + BK - 1) / BK;
+  int stages = (SMEM_LIMIT - v2_fixed_smem()) / (BM * BK + b_rows * BK);
+  if (stages > 10) stages = 10;
+  p.stages = stages;
+  choose_raster(a.M, a.N, a.K, BM * cg, V2_BN, p.num_m_blocks, p.num_n_blocks, &p.group_m, &p.band_n, &p.policy_a,
+                &p.policy_b);
+  p.a_box_rows = (a.M >= BM || cg == 2) ? BM : ((a.M + 7) / 8) * 8;
+  p.prof = static_cast<unsigned long long*>(profile_buffer());
+  p.debug_flags = debug_flags;
+
+  const CUtensorMapDataType d_dt =
+      a.out_dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  CUtensorMap ta, tb, td;
+  if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, p.a_box_rows, BK) ||
+      !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, b_rows, BK) ||
+      !make_tmap_2d(&td, d_dt, 2, a.D, a.M, a.N, a.ldd * 2, 32, 64)) {
+    snprintf(err, err_len, "cuTensorMapEncodeTiled failed (block-wise v2 M=%d N=%d K=%d)", a.M, a.N, a.K);
+    return B2_ERR_CUDA;
+  }
+  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  const int units = sms / cg;
+  const int grid = (tiles < units ? tiles : units) * cg;
+  const size_t smem = static_cast<size_t>(stages) * (BM * BK + b_rows * BK) + v2_fixed_smem();
+  const bool f16 = a.out_dtype == B2_DTYPE_F16;
+  if (cg == 2) {
+    if (f16) return launch_v2<1, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
+    return launch_v2<0, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
+  }
+  if (f16) return launch_v2<1, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+  return launch_v2<0, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+}
+
+}  // namespace b2

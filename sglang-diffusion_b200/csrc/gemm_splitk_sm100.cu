@@ -77,17 +77,6 @@ B2_DEVICE uint32_t part_offset(int row, int chunk, uint32_t pitch_bytes) {
   return static_cast<uint32_t>(row) * pitch_bytes + static_cast<uint32_t>((chunk ^ (row & 7)) << 4);
 }
 
-// 32 lanes x 16 consecutive 32-bit columns -> 16 registers per thread
-B2_DEVICE void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr)
-      : "memory");
-}
-
 template <MmaKind KIND>
 __global__ void __launch_bounds__(NUM_THREADS)
     gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,

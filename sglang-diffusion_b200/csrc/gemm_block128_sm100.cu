@@ -196,10 +196,11 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;  // running K-block counter: slot = it & 3, slot phase = (it >> 2) & 1
-      long long prof_full = 0;
+      long long prof_full = 0, prof_issue = 0;
+      const int mma_step = (p.debug_flags & 4) ? 1 : 2;  // experiment: one K block per MMA hand-shake
       for (int tile = unit; tile < num_tiles; tile += num_units) {
-        for (int kb = 0; kb < p.num_kb; kb += 2) {
-          const int n2 = kb + 1 < p.num_kb ? 2 : 1;
+        for (int kb = 0; kb < p.num_kb; kb += mma_step) {
+          const int n2 = (mma_step == 2 && kb + 1 < p.num_kb) ? 2 : 1;
           const int stage1 = stage + 1 == stages ? 0 : stage + 1;
           const uint32_t phase1 = stage + 1 == stages ? phase ^ 1 : phase;
           {
@@ -212,6 +213,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
             if (p.prof) prof_full += clock64() - w0;
           }
           tc_fence_after_sync();
+          const long long wi0 = p.prof ? clock64() : 0;
           if (elect_one()) {
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
@@ -239,6 +241,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
             }
           }
           __syncwarp();
+          if (p.prof) prof_issue += clock64() - wi0;
           it += n2;
           for (int j = 0; j < n2; ++j) {
             if (++stage == stages) {
@@ -250,7 +253,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
       }
       if (p.prof && lane == 0) {
         p.prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(prof_full);
-        p.prof[blockIdx.x * 8 + 1] = 0;
+        p.prof[blockIdx.x * 8 + 1] = static_cast<unsigned long long>(prof_issue);
       }
     }
   } else {
@@ -262,7 +265,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
     uint8_t* stage_buf = smem_epi + static_cast<size_t>(ew) * EPI_BUF_BYTES;
     const bool has_bias = p.bias != nullptr;
     uint32_t it = 0;
-    long long prof_part = 0, prof_sc = 0;
+    long long prof_part = 0, prof_sc = 0, prof_ld = 0, prof_body = 0;
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(half * 64);
 
     // Scales travel through shared memory in chunks of BW_SC K blocks (SFA: 128 rows x BW_SC, SFB: BW_SC),
@@ -340,9 +343,11 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
             if (p.prof) prof_part += clock64() - w0;
           }
           tc_fence_after_sync();
+          const long long wb0 = p.prof ? clock64() : 0;
           tmem_ld_32x32b_x32(t_lane + col_a, r0);
           tmem_ld_32x32b_x32(t_lane + col_a + 32, r1);
           tmem_ld_wait();
+          if (p.prof) prof_ld += clock64() - wb0;
           // slot a is in registers: hand it back
           tc_fence_before_sync();
           __syncwarp();
@@ -372,6 +377,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
             }
           }
           it += two ? 2 : 1;
+          if (p.prof) prof_body += clock64() - wb0;
         }
         sbuf ^= 1;
       }
@@ -410,6 +416,8 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
     if (p.prof && warp == EPI_WARP0 && lane == 0) {
       p.prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(prof_part);
       p.prof[blockIdx.x * 8 + 5] = static_cast<unsigned long long>(prof_sc);
+      p.prof[blockIdx.x * 8 + 6] = static_cast<unsigned long long>(prof_ld);
+      p.prof[blockIdx.x * 8 + 7] = static_cast<unsigned long long>(prof_body);
     }
   }
   if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);

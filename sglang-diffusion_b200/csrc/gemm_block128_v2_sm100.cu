@@ -1,21 +1,17 @@
-// Block-wise (1x128 / 128x128 scales) e4m3 GEMM, second generation: parity-split promotion.
+// Block-wise (1x128 / 128x128 scales) e4m3 GEMM, second generation: sixteen promotion warps.
 //
 // Same arithmetic contract as gemm_block128_sm100.cu (fp8_blockwise_scaled_mm,
 // sgl-kernel/csrc/gemm/fp8_blockwise_gemm_kernel.cu:368-465): every 128-deep K block is multiplied into its own TMEM
 // slot with a non-accumulating MMA chain and folded into fp32 register accumulators with ONE fma per element,
-// acc += (SFA[m,kb] * SFB[nb,kb]) * partial.
+// acc += (SFA[m,kb] * SFB[nb,kb]) * partial, K blocks in order.
 //
-// What changed, and why (profiles/r02f_block128_handshake.md): the first kernel ran at ~500 clocks per K block against
-// a 256-clock MMA, and did so even with the MMAs or the FMAs compiled out -- it is bound by the slot hand-shake.  Its
-// roles step two K blocks at a time (an mbarrier wait costs ~100 clocks even when the phase is complete, a remote
-// arrive ~215), which leaves only TWO steps in flight on the four-slot ring.  Here
-//   * the MMA warp walks the ring one K block at a time (four hand-shakes in flight), and
-//   * the eight promotion warps are split by K-block PARITY: the even group (4 warps, one per TMEM lane quarter) drains
-//     slots 0/2, the odd group slots 1/3, each warp folding all 128 columns of its 32 rows.  A warp therefore visits
-//     the ring every OTHER K block and moves twice the data per visit, so its fixed costs (wait, TMEM-load latency,
-//     arrive) are paid half as often, and the two groups overlap each other on the same scheduler.
-//   * at the end of a tile the two partial sums of a row are added through shared memory (fixed order even + odd),
-//     each warp of a pair finishing and storing 64 of the 128 columns.
+// What changed, and why (profiles/r02f_block128_handshake.md): in the first kernel the eight promotion warps are the
+// critical path -- ~370 busy clocks per K block against a 256-clock MMA -- and most of that is latency, not issue:
+// two tcgen05.wait::ld round trips per step per warp with only two warps per scheduler to cover them (the wait cannot
+// name a load, so loads cannot be software-pipelined past it).  Here SIXTEEN warps drain the slots, four per TMEM lane
+// quarter, each folding 32 rows x 32 columns: per two-K-block step a warp issues its two TMEM loads back to back,
+// waits ONCE, hands both slots back and runs 32 packed FMAs; four warps per scheduler overlap each other's waits.
+// Outputs go straight from registers to global memory (each thread owns 64 contiguous bytes of one row).
 #include <cstdlib>
 
 #include "gemm_common.cuh"
@@ -24,11 +20,10 @@ namespace b2 {
 
 constexpr int V2_BN = 128;
 constexpr int V2_SLOTS = 4;
-constexpr int V2_PROMO_WARPS = 8;
-constexpr int V2_PROMO_WARP0 = 2;                               // warps 0 (TMA), 1 (MMA), 2..9 promotion
-constexpr int V2_THREADS = 32 * (V2_PROMO_WARP0 + V2_PROMO_WARPS);  // 320
+constexpr int V2_PROMO_WARPS = 16;
+constexpr int V2_PROMO_WARP0 = 4;                               // warps 0 (TMA), 1 (MMA), 2-3 idle, 4..19 promotion
+constexpr int V2_THREADS = 32 * (V2_PROMO_WARP0 + V2_PROMO_WARPS);  // 640
 constexpr int V2_SC = 16;                                       // K blocks per shared-memory scale chunk
-constexpr int V2_XBUF_BYTES = 64 * 32 * 4;                      // one warp's exchange buffer: 64 columns x 32 rows fp32
 
 struct BlockwiseV2Params {
   const float* sfa;
@@ -43,8 +38,10 @@ struct BlockwiseV2Params {
   int band_n;
   uint64_t policy_a, policy_b;
   int a_box_rows;
-  unsigned long long* prof;  // [0] MMA waits [2] producer waits [3] promotion waits for a partial [5] scales+barrier
-                             // [6] merge + store [4] CTA life
+  void* D;
+  int64_t ldd;
+  unsigned long long* prof;  // [0] MMA waits [1] MMA issue [2] producer waits [3] promotion waits for a partial
+                             // [5] scales+barrier [7] promotion body [4] CTA life
   int debug_flags;
 };
 
@@ -78,9 +75,7 @@ B2_DEVICE void v2_tile_coords(int tile, const BlockwiseV2Params& p, int& m_blk, 
   n_blk = p.band_n ? f : s;
 }
 
-B2_DEVICE void pair_bar_sync(int quarter) {  // the even and the odd promotion warp of one lane quarter
-  asm volatile("bar.sync %0, 64;" ::"r"(2 + quarter) : "memory");
-}
+B2_DEVICE void v2_promo_bar_sync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 
 template <int OUT_KIND, int CG>
 __global__ void __launch_bounds__(V2_THREADS, 1)
@@ -98,8 +93,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
   const int stages = p.stages;
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + static_cast<size_t>(stages) * A_STAGE_BYTES;
-  uint8_t* smem_x = smem_b + static_cast<size_t>(stages) * B_STAGE_BYTES;            // 8 warps x 8 KB exchange
-  float* smem_sfa = reinterpret_cast<float*>(smem_x + V2_PROMO_WARPS * V2_XBUF_BYTES);  // [2][V2_SC][128]
+  float* smem_sfa = reinterpret_cast<float*>(smem_b + static_cast<size_t>(stages) * B_STAGE_BYTES);  // [2][V2_SC][128]
   float* smem_sfb = smem_sfa + 2 * V2_SC * BM;                                          // [2][V2_SC]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_sfb + 2 * V2_SC);
   uint64_t* empty_bar = full_bar + stages;
@@ -118,14 +112,13 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
-    tma_prefetch_desc(&tmap_d);
     for (int i = 0; i < stages; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
     for (int i = 0; i < V2_SLOTS; ++i) {
       mbar_init(&part_full[i], 1);
-      mbar_init(&part_empty[i], (V2_PROMO_WARPS / 2) * CG);  // the four warps of ONE parity group, in every CTA
+      mbar_init(&part_empty[i], V2_PROMO_WARPS * CG);  // one arrival per promotion warp of every CTA of the cluster
     }
     fence_mbar_init();
   }
@@ -190,65 +183,84 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     if (p.prof && lane == 0) p.prof[blockIdx.x * 8 + 2] = static_cast<unsigned long long>(prof_wait);
   } else if (warp == 1) {
     // ======================================================= MMA issuer ====
-    // ONE K block per step: lane 0 waits for the operand stage, lane 1 for the TMEM slot, in one try_wait round.
+    // two K blocks per step: lanes 0-1 wait for the two operand stages, lanes 2-3 for the two TMEM slots, in
+    // ONE try_wait round (measured: 1966 vs 1812 TOPS against one block per step on 4096 x 36864 x 7168)
     if (cta_rank == 0) {
       constexpr uint32_t idesc = make_idesc<MmaKind::F8>(BM * CG, BN);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;  // running K-block counter: slot = it & 3, slot phase = (it >> 2) & 1
-      long long prof_full = 0;
+      long long prof_full = 0, prof_issue = 0;
+      constexpr int mma_step = 2;
       for (int tile = unit; tile < num_tiles; tile += num_units) {
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        for (int kb = 0; kb < p.num_kb; kb += mma_step) {
+          const int n2 = (mma_step == 2 && kb + 1 < p.num_kb) ? 2 : 1;
+          const int stage1 = stage + 1 == stages ? 0 : stage + 1;
+          const uint32_t phase1 = stage + 1 == stages ? phase ^ 1 : phase;
           {
-            uint64_t* bar = lane == 0 ? &full_bar[stage] : &part_empty[it & (V2_SLOTS - 1)];
-            const uint32_t par = lane == 0 ? phase : (((it >> 2) & 1) ^ 1);
+            const int j = lane & 1;
+            const uint32_t itj = it + j;
+            uint64_t* bar = lane < 2 ? &full_bar[j ? stage1 : stage] : &part_empty[itj & (V2_SLOTS - 1)];
+            const uint32_t par = lane < 2 ? (j ? phase1 : phase) : (((itj >> 2) & 1) ^ 1);
             const long long w0 = p.prof ? clock64() : 0;
-            mbar_wait_lanes(bar, par, lane < 2);
+            mbar_wait_lanes(bar, par, lane < 4 && j < n2);
             if (p.prof) prof_full += clock64() - w0;
           }
           tc_fence_after_sync();
+          const long long wi0 = p.prof ? clock64() : 0;
           if (elect_one()) {
-            const int slot = static_cast<int>(it & (V2_SLOTS - 1));
-            const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(slot * BN);
-            const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * A_STAGE_BYTES));
-            const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
-            if (!(p.debug_flags & 1)) {
 #pragma unroll
-              for (int k = 0; k < BK / UMMA_K; ++k) {
-                umma<MmaKind::F8, CG>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
-                                      db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, k != 0 ? 1u : 0u);
+            for (int j = 0; j < 2; ++j) {
+              if (j < n2) {
+                const int st_j = j ? stage1 : stage;
+                const int slot = static_cast<int>((it + j) & (V2_SLOTS - 1));
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(slot * BN);
+                const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(st_j) * A_STAGE_BYTES));
+                const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(st_j) * B_STAGE_BYTES));
+                if (!(p.debug_flags & 1)) {
+#pragma unroll
+                  for (int k = 0; k < BK / UMMA_K; ++k) {
+                    umma<MmaKind::F8, CG>(d_tmem, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
+                                          db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, k != 0 ? 1u : 0u);
+                  }
+                }
+                if constexpr (CG == 1) {
+                  umma_commit(&empty_bar[st_j]);
+                  umma_commit(&part_full[slot]);
+                } else {
+                  umma_commit_cg2(&empty_bar[st_j], 0x3);
+                  umma_commit_cg2(&part_full[slot], 0x3);
+                }
               }
-            }
-            if constexpr (CG == 1) {
-              umma_commit(&empty_bar[stage]);
-              umma_commit(&part_full[slot]);
-            } else {
-              umma_commit_cg2(&empty_bar[stage], 0x3);
-              umma_commit_cg2(&part_full[slot], 0x3);
             }
           }
           __syncwarp();
-          ++it;
-          if (++stage == stages) {
-            stage = 0;
-            phase ^= 1;
+          if (p.prof) prof_issue += clock64() - wi0;
+          it += n2;
+          for (int j = 0; j < n2; ++j) {
+            if (++stage == stages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
         }
       }
-      if (p.prof && lane == 0) p.prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(prof_full);
+      if (p.prof && lane == 0) {
+        p.prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(prof_full);
+        p.prof[blockIdx.x * 8 + 1] = static_cast<unsigned long long>(prof_issue);
+      }
     }
   } else {
     // ============================================== promotion + epilogue ====
-    const int ew = warp - V2_PROMO_WARP0;  // 0..7
+    if (warp >= V2_PROMO_WARP0) {
+    const int ew = warp - V2_PROMO_WARP0;  // 0..15
     const int quarter = warp & 3;          // TMEM lane quarter this warp may read
-    const int g = ew >> 2;                 // parity group: K blocks with (running index & 1) == g
-    const int ptid = ew * 32 + lane;       // 0..255
-    float* xbuf_mine = reinterpret_cast<float*>(smem_x + static_cast<size_t>(ew) * V2_XBUF_BYTES);
-    float* xbuf_peer = reinterpret_cast<float*>(smem_x + static_cast<size_t>(ew ^ 4) * V2_XBUF_BYTES);
+    const int cq = ew >> 2;                // which 32 of the slot's 128 columns
+    const int ptid = ew * 32 + lane;       // 0..511
     const bool has_bias = p.bias != nullptr;
-    uint32_t it0 = 0;  // running K-block index of the first K block of the current tile
-    long long prof_part = 0, prof_sc = 0, prof_st = 0;
-    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    uint32_t it = 0;
+    long long prof_part = 0, prof_sc = 0, prof_body = 0;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(cq * 32);
 
     auto issue_scales = [&](int m_blk_, int n_blk_, int chunk, int b) {
       const int m_base = (m_blk_ * CG + cta_rank) * BM;
@@ -258,8 +270,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
       const bool r_ok = m_base + r < p.M;
       const float* src_row = p.sfa + static_cast<int64_t>(r_ok ? m_base + r : 0) * p.sfa_m_stride;
 #pragma unroll
-      for (int i = 0; i < V2_SC / 2; ++i) {
-        const int kl = (ptid >> 7) + 2 * i;
+      for (int i = 0; i < V2_SC / 4; ++i) {
+        const int kl = (ptid >> 7) + 4 * i;
         const int kb = chunk * V2_SC + kl;
         if (r_ok && kb < p.num_kb) cp_async_4(dst_a + kl * BM + r, src_row + static_cast<int64_t>(kb) * p.sfa_k_stride);
       }
@@ -281,21 +293,19 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     for (int tile = unit; tile < num_tiles; tile += num_units) {
       int m_blk, n_blk;
       v2_tile_coords(tile, p, m_blk, n_blk);
-      const int row0 = (m_blk * CG + cta_rank) * BM + quarter * 32;
-      const int col0 = n_blk * BN + g * 64;
+      const int row = (m_blk * CG + cta_rank) * BM + quarter * 32 + lane;
+      const int col0 = n_blk * BN + cq * 32;
 
-      float acc[128];
+      float acc[32];
 #pragma unroll
-      for (int i = 0; i < 128; ++i) acc[i] = 0.f;
-      uint32_t r0[16], r1[16];
+      for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+      uint32_t r0[32], r1[16];
 
-      // the previous tile's TMA store has read its staging box (which lives in the partner's exchange buffer)
-      tma_store_wait_read<0>();
       for (int chunk = 0; chunk < nchunks; ++chunk) {
         {
           const long long w0 = p.prof ? clock64() : 0;
-          cp_async_wait<0>();  // my copies of this chunk have landed ...
-          promo_bar_sync();    // ... so have everybody's, and everybody is done with the other buffer
+          cp_async_wait<0>();   // my copies of this chunk have landed ...
+          v2_promo_bar_sync();  // ... so have everybody's, and everybody is done with the other buffer
           if (p.prof) prof_sc += clock64() - w0;
         }
         if (chunk + 1 < nchunks) {
@@ -309,99 +319,80 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
         const float* sb_s = smem_sfb + sbuf * V2_SC;
         const int kb_begin = chunk * V2_SC;
         const int kb_end = min(p.num_kb, kb_begin + V2_SC);
-        // first K block of this chunk that belongs to my parity group
-        for (int kb = kb_begin + ((static_cast<int>(it0) + kb_begin + g) & 1); kb < kb_end; kb += 2) {
-          const uint32_t itk = it0 + static_cast<uint32_t>(kb);
-          const int slot = static_cast<int>(itk & (V2_SLOTS - 1));
-          const uint32_t col = static_cast<uint32_t>(slot * BN);
-          const float scale = __fmul_rn(sa_s[(kb - kb_begin) * BM], sb_s[kb - kb_begin]);
+        for (int kb = kb_begin; kb < kb_end; kb += 2) {
+          const bool two = kb + 1 < kb_end;
+          const uint32_t ita = it, itb = it + 1;
+          const uint32_t col_a = static_cast<uint32_t>((ita & (V2_SLOTS - 1)) * BN);
+          const uint32_t col_b = static_cast<uint32_t>((itb & (V2_SLOTS - 1)) * BN);
+          const float scale_a = __fmul_rn(sa_s[(kb - kb_begin) * BM], sb_s[kb - kb_begin]);
+          const float scale_b = two ? __fmul_rn(sa_s[(kb + 1 - kb_begin) * BM], sb_s[kb + 1 - kb_begin]) : 0.f;
           {
+            const uint32_t itj = lane == 1 ? itb : ita;
             const long long w0 = p.prof ? clock64() : 0;
-            mbar_wait_lanes(&part_full[slot], (itk >> 2) & 1, lane == 0);
+            mbar_wait_lanes(&part_full[itj & (V2_SLOTS - 1)], (itj >> 2) & 1, lane == 0 || (lane == 1 && two));
             if (p.prof) prof_part += clock64() - w0;
           }
+          const long long wb0 = p.prof ? clock64() : 0;
           tc_fence_after_sync();
-          // eight 16-column chunks, the load of chunk c+1 in flight under the FMAs of chunk c (two 16-register
-          // buffers: 128 accumulators + 2 x 32 would spill at the 168 registers a 320-thread CTA gets)
-          tmem_ld_32x32b_x16(t_lane + col, r0);
-#pragma unroll
-          for (int c = 0; c < 7; ++c) {
-            tmem_ld_wait();
-            if (c & 1) {
-              tmem_ld_32x32b_x16(t_lane + col + (c + 1) * 16, r0);
-              if (!(p.debug_flags & 2)) v2_promote<16>(acc + c * 16, r1, scale);
-            } else {
-              tmem_ld_32x32b_x16(t_lane + col + (c + 1) * 16, r1);
-              if (!(p.debug_flags & 2)) v2_promote<16>(acc + c * 16, r0, scale);
-            }
-          }
+          // 96 registers per thread (640-thread CTA): 32 accumulators + a 32- and a 16-register load buffer.  Block a
+          // and the low half of block b are loaded together (one wait); the high half of b flies under the FMAs.
+          tmem_ld_32x32b_x32(t_lane + col_a, r0);
+          if (two) tmem_ld_32x32b_x16(t_lane + col_b, r1);
           tmem_ld_wait();
-          // the whole slot is in registers: hand it back
           tc_fence_before_sync();
           __syncwarp();
           if (lane == 0) {
-            if constexpr (CG == 1) mbar_arrive(&part_empty[slot]);
-            else mbar_arrive_cluster(&part_empty[slot], 0);
+            if constexpr (CG == 1) mbar_arrive(&part_empty[ita & (V2_SLOTS - 1)]);
+            else mbar_arrive_cluster(&part_empty[ita & (V2_SLOTS - 1)], 0);
           }
-          if (!(p.debug_flags & 2)) v2_promote<16>(acc + 112, r1, scale);
+          if (!(p.debug_flags & 2)) v2_promote<32>(acc, r0, scale_a);  // K blocks in order: kb, then kb + 1
+          if (two) {
+            uint32_t(&r0lo)[16] = *reinterpret_cast<uint32_t(*)[16]>(&r0[0]);
+            tmem_ld_32x32b_x16(t_lane + col_b + 16, r0lo);
+            if (!(p.debug_flags & 2)) v2_promote<16>(acc, r1, scale_b);
+            tmem_ld_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) {
+              if constexpr (CG == 1) mbar_arrive(&part_empty[itb & (V2_SLOTS - 1)]);
+              else mbar_arrive_cluster(&part_empty[itb & (V2_SLOTS - 1)], 0);
+            }
+            if (!(p.debug_flags & 2)) v2_promote<16>(acc + 16, r0lo, scale_b);
+          }
+          it += two ? 2 : 1;
+          if (p.prof) prof_body += clock64() - wb0;
         }
         sbuf ^= 1;
       }
-      it0 += static_cast<uint32_t>(p.num_kb);
 
-      // ---- merge the two parity sums of my rows, then bias, cast, stage and TMA-store my 64 columns ----
-      const long long ws0 = p.prof ? clock64() : 0;
-      if (g == 0) {
+      // ---- bias, cast, store: each thread owns 32 consecutive columns (64 bytes) of one row ----
+      if (row < p.M && col0 < p.N) {
+        uint8_t* drow = static_cast<uint8_t*>(p.D) + (static_cast<int64_t>(row) * p.ldd + col0) * 2;
 #pragma unroll
-        for (int j = 0; j < 64; ++j) xbuf_mine[j * 32 + lane] = acc[64 + j];
-      } else {
+        for (int c8 = 0; c8 < 4; ++c8) {
+          float o8[8];
 #pragma unroll
-        for (int j = 0; j < 64; ++j) xbuf_mine[j * 32 + lane] = acc[j];
-      }
-      pair_bar_sync(quarter);
-      float v[64];
-      if (g == 0) {
+          for (int j = 0; j < 8; ++j) o8[j] = acc[c8 * 8 + j];
+          if (has_bias) {
+            float bi[8];
+            load_bias8(p.bias, p.bias_dtype, col0 + c8 * 8, bi);
 #pragma unroll
-        for (int j = 0; j < 64; ++j) v[j] = __fadd_rn(acc[j], xbuf_peer[j * 32 + lane]);  // even + odd
-      } else {
-#pragma unroll
-        for (int j = 0; j < 64; ++j) v[j] = __fadd_rn(xbuf_peer[j * 32 + lane], acc[64 + j]);
-      }
-      __syncwarp();  // every lane has read the partner's buffer: its first 4 KB become my staging box
-      uint8_t* stage_buf = reinterpret_cast<uint8_t*>(xbuf_peer);
-#pragma unroll
-      for (int c8 = 0; c8 < 8; ++c8) {
-        const int colg = col0 + c8 * 8;
-        float o8[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o8[j] = v[c8 * 8 + j];
-        if (has_bias && colg < p.N) {
-          float bi[8];
-          load_bias8(p.bias, p.bias_dtype, colg, bi);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) o8[j] = __fadd_rn(o8[j], bi[j]);
+            for (int j = 0; j < 8; ++j) o8[j] = __fadd_rn(o8[j], bi[j]);
+          }
+          uint4 o;
+          o.x = pack16<OUT_KIND>(o8[0], o8[1]);
+          o.y = pack16<OUT_KIND>(o8[2], o8[3]);
+          o.z = pack16<OUT_KIND>(o8[4], o8[5]);
+          o.w = pack16<OUT_KIND>(o8[6], o8[7]);
+          *reinterpret_cast<uint4*>(drow + c8 * 16) = o;
         }
-        uint4 o;
-        o.x = pack16<OUT_KIND>(o8[0], o8[1]);
-        o.y = pack16<OUT_KIND>(o8[2], o8[3]);
-        o.z = pack16<OUT_KIND>(o8[4], o8[5]);
-        o.w = pack16<OUT_KIND>(o8[6], o8[7]);
-        const int chunk16 = c8 ^ (lane & 7);
-        *reinterpret_cast<uint4*>(stage_buf + lane * 128 + chunk16 * 16) = o;
       }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (row0 < p.M && col0 < p.N && elect_one()) {
-        tma_store_2d(&tmap_d, stage_buf, col0, row0);
-        tma_store_commit();
-      }
-      if (p.prof) prof_st += clock64() - ws0;
     }
-    tma_store_wait_all<0>();
     if (p.prof && warp == V2_PROMO_WARP0 && lane == 0) {
       p.prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(prof_part);
       p.prof[blockIdx.x * 8 + 5] = static_cast<unsigned long long>(prof_sc);
-      p.prof[blockIdx.x * 8 + 6] = static_cast<unsigned long long>(prof_st);
+      p.prof[blockIdx.x * 8 + 7] = static_cast<unsigned long long>(prof_body);
+    }
     }
   }
   if (p.prof && threadIdx.x == 0) p.prof[blockIdx.x * 8 + 4] = static_cast<unsigned long long>(clock64() - t_start);
@@ -421,7 +412,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
 
 // ------------------------------------------------------------------ host ----
 
-static int v2_fixed_smem() { return V2_PROMO_WARPS * V2_XBUF_BYTES + 2 * V2_SC * BM * 4 + 2 * V2_SC * 4 + 256; }
+static int v2_fixed_smem() { return 2 * V2_SC * BM * 4 + 2 * V2_SC * 4 + 256; }
 
 template <int OUT_KIND, int CG>
 static int launch_v2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const BlockwiseV2Params& p,
@@ -489,6 +480,8 @@ int gemm_launch_blockwise_v2(const GemmArgs& a, int cg, int debug_flags, const c
   p.a_box_rows = (a.M >= BM || cg == 2) ? BM : ((a.M + 7) / 8) * 8;
   p.prof = static_cast<unsigned long long*>(profile_buffer());
   p.debug_flags = debug_flags;
+  p.D = a.D;
+  p.ldd = a.ldd;
 
   const CUtensorMapDataType d_dt =
       a.out_dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;

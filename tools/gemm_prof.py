@@ -65,5 +65,6 @@ for cfg in cfgs:
         kbs = tiles_total / 148 * nkb  # K blocks per CTA
         print(f"   block-wise, clk per K block: loop {life.mean()/kbs:.0f} | promotion warp waits: partial {p[:,3].mean()/kbs:.0f} "
               f"scales+barrier {p[:,5].mean()/kbs:.0f} | MMA warp waits (stage + slot) {lead[:,0].mean()/kbs:.0f} | "
-              f"producer waits {p[:,2].mean()/kbs:.0f}", flush=True)
+              f"producer waits {p[:,2].mean()/kbs:.0f} | MMA issue block {lead[:,1].mean()/kbs:.0f} | promotion: first 2 LDTM+wait "
+              f"{p[:,6].mean()/kbs:.0f} body after wait {p[:,7].mean()/kbs:.0f}", flush=True)
 b2.capi.set_gemm_config(0)

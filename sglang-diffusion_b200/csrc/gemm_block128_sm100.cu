@@ -475,11 +475,7 @@ static int launch_bw(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
   return B2_OK;
 }
 
-int gemm_launch_blockwise_v2(const GemmArgs& a, int cg, int debug_flags, const char** used_config, cudaStream_t st,
-                             char* err, size_t err_len);
-
-// forced_config (low byte): 0 = automatic, 1 = 1-CTA 128x128 tiles, 2 = 2-CTA 256x128 tiles (first-generation
-// kernel, two K blocks per hand-shake), 3 / 4 = 1-CTA / 2-CTA parity-split kernel (gemm_block128_v2_sm100.cu)
+// forced_config (low byte): 0 = automatic, 1 = 1-CTA 128x128 tiles, 2 = 2-CTA 256x128 tiles
 int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** used_config, cudaStream_t st,
                           char* err, size_t err_len) {
   const int forced_debug = forced_config >> 8;
@@ -492,13 +488,6 @@ int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** use
     const char* e = getenv("B2_GEMM_DEBUG");
     return e ? atoi(e) : 0;
   }();
-  static const int v2_env = [] {  // developer A/B switch: B2_BLOCK_V2=0 keeps the first-generation kernel
-    const char* e = getenv("B2_BLOCK_V2");
-    return e ? atoi(e) : 1;
-  }();
-  if (forced_config == 3 || forced_config == 4 || (forced_config == 0 && v2_env))
-    return gemm_launch_blockwise_v2(a, forced_config == 3 ? 1 : (forced_config == 4 ? 2 : cg), dbg_env | forced_debug,
-                                    used_config, st, err, err_len);
   if (used_config) *used_config = cg == 2 ? "2cta_256x128_block128" : "1cta_128x128_block128";
   const int b_rows = BW_BN / cg;
 
@@ -524,11 +513,7 @@ int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** use
                 &p.policy_b);
   p.a_box_rows = (a.M >= BM || cg == 2) ? BM : ((a.M + 7) / 8) * 8;
   p.prof = static_cast<unsigned long long*>(profile_buffer());
-  static const int dbg = [] {
-    const char* e = getenv("B2_GEMM_DEBUG");
-    return e ? atoi(e) : 0;
-  }();
-  p.debug_flags = dbg | forced_debug;
+  p.debug_flags = dbg_env | forced_debug;
 
   const CUtensorMapDataType d_dt =
       a.out_dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;

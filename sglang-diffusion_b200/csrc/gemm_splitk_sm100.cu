@@ -369,8 +369,12 @@ static SplitPlan plan_splitk(int N, int K, int a_rows) {
   int bn = a_rows <= 32 ? 128 : 64;
   if (N < bn) bn = (N + 15) / 16 * 16;
   const int tiles = (N + bn - 1) / bn;
+  // grid target: ~0.85 x #SMs CTAs for the narrow activation boxes; 1.5 x #SMs once the box is 64+ rows (two
+  // resident CTAs per SM then cover each other's 8-16 KB activation loads and the DSMEM reduction tail --
+  // profiles/r02g_splitk_plans_{int8,fp8}.log: C1 M=128 4096x4096 10.1 -> 9.2 us, M=64 8192x3584 11.6 -> 10.6 us)
+  const int target = a_rows > 32 ? (sms * 3) / 2 : (sms * 85) / 100;
   int s = 1;
-  while (s < 8 && tiles * s < (sms * 85) / 100 && num_kb / (2 * s) >= 4) s *= 2;
+  while (s < 8 && tiles * s < target && num_kb / (2 * s) >= 4) s *= 2;
   const int kb_per = (num_kb + s - 1) / s;
   const long ctas = static_cast<long>(tiles) * s;
   const int need_occ = static_cast<int>((ctas + sms - 1) / sms);

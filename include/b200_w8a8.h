@@ -164,6 +164,40 @@ int b2_bmm_e4m3(const uint8_t* A, int64_t lda, int64_t a_batch_stride, const uin
                 int64_t d_batch_stride, int out_dtype, int batch, int M, int N, int K, void* workspace,
                 size_t workspace_bytes, b2_stream_t stream);
 
+/* ---- W8A8-int8 mixture of experts --------------------------- */
+
+/* moe_align_block_size with 128-row blocks (sgl-kernel/csrc/moe/moe_align_kernel.cu; CPU twin
+ * sgl-kernel/csrc/cpu/moe.cpp moe_align_block_size): groups the n = tokens * topk routed rows by expert, every
+ * expert's run padded to a multiple of 128 rows so that one UMMA tile never mixes experts.
+ *   sorted_ids[max_padded]       flat index token*topk + k of every row, padding rows hold n
+ *   tile_expert[max_padded/128]  expert of every 128-row block, -1 for blocks past num_post_pad
+ *   inv_pos[n]                   row of flat index i (-1 for an expert id outside [0, E))
+ *   num_post_pad[1]              rows in use
+ * max_padded must be a multiple of 128 and >= b2_moe_max_padded(n, E).  E <= 4096. */
+int64_t b2_moe_max_padded(int64_t n, int num_experts);
+int b2_moe_align_block128(const int32_t* topk_ids, int n, int num_experts, int32_t* sorted_ids, int32_t* tile_expert,
+                          int32_t* inv_pos, int32_t* num_post_pad, int64_t max_padded, b2_stream_t stream);
+
+/* Stage 0 / 2 of fused_experts_int8_kernel_impl (moe_int8.cpp:620-626): per-token int8 quantization (arithmetic of
+ * b2_quant_int8_rows) of row row_map[r] / row_div of x into row r of q, for r < P; ids >= row_limit are padding
+ * rows and become all-zero codes.  K % 8 == 0, K <= 32768. */
+int b2_quant_int8_rows_gather(const void* x, int x_dtype, int64_t ldx, const int32_t* row_map, int row_div,
+                              int row_limit, int8_t* q, int64_t ldq, float* s, int64_t P, int K, b2_stream_t stream);
+
+/* Grouped int8 GEMM over expert-sorted rows (stage 1 / 2 of moe_int8.cpp, the tinygemm / brgemm blocks of
+ * :640-760): for every 128-row block b with e = tile_expert[b] >= 0,
+ *     D[rows of b, :] = out_t( (f32(acc) * As[row]) * Bs[e*N + n] ),  acc = A[rows] . W[e*N + n, :]^T  (exact int32)
+ * W is the stacked expert weight [num_experts * N, K] (the checkpoint layout [E, N, K]), Bs [num_experts * N].
+ * The arithmetic of one row is that of b2_gemm_s8 with the expert's weight: bit-identical to the dense op. */
+int b2_gemm_s8_grouped(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
+                       const int32_t* tile_expert, int num_experts, void* D, int64_t ldd, int out_dtype, int64_t P,
+                       int N, int K, b2_stream_t stream);
+
+/* Stage 3: out[t, :] = out_t( sum_k topk_weights[t,k] * f32(y[inv_pos[t*topk + k], :]) ), k ascending, fp32
+ * accumulation (moe_int8.cpp:830-846).  H % 8 == 0. */
+int b2_moe_combine(const void* y, int64_t ldy, const int32_t* inv_pos, const float* topk_weights, void* out,
+                   int64_t ldo, int tokens, int topk, int H, int dtype, b2_stream_t stream);
+
 /* ---- fused linear ----------------------------------------------------------- */
 
 /* int8_scaled_mm_with_quant (sgl-kernel/csrc/cpu/gemm_int8.cpp:481-547):

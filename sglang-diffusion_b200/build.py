@@ -25,7 +25,7 @@ CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
 NVCC = os.path.join(CUDA_HOME, "bin", "nvcc")
 GXX = "/usr/bin/g++"
 
-CU_SOURCES = ["capi.cu", "quant.cu", "quant_fused.cu", "gemm_sm100.cu", "gemm_splitk_sm100.cu", "gemm_block128_sm100.cu", "allreduce_symm.cu"]
+CU_SOURCES = ["capi.cu", "quant.cu", "quant_fused.cu", "moe.cu", "gemm_sm100.cu", "gemm_splitk_sm100.cu", "gemm_block128_sm100.cu", "allreduce_symm.cu"]
 CU_HEADERS = ["ptx.cuh", "quant_common.cuh", "gemm_common.cuh", "b200_w8a8_internal.h"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",

@@ -38,6 +38,9 @@ struct FusedQuantArgs {
   int64_t M;          // rows (E * T for the masked layout)
   int K;
   float q_eps, fmin, fmax;  // group modes
+  const int32_t* row_map;   // optional gather: output row r quantizes input row row_map[r] / row_div
+  int row_div;
+  int row_limit;            // ids >= row_limit are padding rows (all-zero codes)
 };
 // prod: 0 none, 1 silu_and_mul, 2 rmsnorm;  mode: 0 int8 rows, 1 fp8 rows, 2 fp8 1x128 (v1), 3 fp8 1x128 (v2)
 cudaError_t fused_quant_launch(int prod, int mode, int x_dtype, const FusedQuantArgs& a, cudaStream_t st);
@@ -45,6 +48,12 @@ cudaError_t quant_fp8_tensor(const void* x, int x_dtype, uint8_t* q, float* s, f
                              int64_t rows, int is_static, cudaStream_t st);
 cudaError_t broadcast_scales(const float* a_scale, const float* b_scale, float* as, float* bs, int m, int n,
                              cudaStream_t st);
+
+// moe.cu
+cudaError_t moe_align128(const int32_t* topk_ids, int n, int E, int32_t* sorted_ids, int32_t* tile_expert,
+                         int32_t* inv_pos, int32_t* num_post_pad, int max_padded, cudaStream_t st);
+cudaError_t moe_combine(const void* y, int64_t ldy, const int32_t* inv_pos, const float* w, void* out, int64_t ldo,
+                        int tokens, int topk, int H, int dtype, cudaStream_t st);
 
 // gemm_sm100.cu
 struct GemmArgs {
@@ -62,6 +71,10 @@ struct GemmArgs {
   int M, N, K;
   // block-wise (128x128) only
   int64_t sfa_m_stride, sfa_k_stride, sfb_n_stride, sfb_k_stride;
+  // grouped (MoE) mode: W is [num_experts * N, K], Bs is [num_experts * N]; tile_expert[b] = expert of rows
+  // [128 b, 128 b + 128) of A (expert-sorted, padded per expert), -1 = no tokens
+  const int32_t* tile_expert;
+  int num_experts;
 };
 
 enum GemmFlavor { GEMM_S8 = 0, GEMM_E4M3 = 1, GEMM_E4M3_BLOCK128 = 2 };

@@ -364,6 +364,86 @@ int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64
   return B2_OK;
 }
 
+int64_t b2_moe_max_padded(int64_t n, int num_experts) {
+  // every expert wastes at most 127 rows; rounded up to whole blocks
+  const int64_t worst = n + static_cast<int64_t>(num_experts) * 127;
+  return (worst + 127) / 128 * 128;
+}
+
+int b2_moe_align_block128(const int32_t* topk_ids, int n, int num_experts, int32_t* sorted_ids, int32_t* tile_expert,
+                          int32_t* inv_pos, int32_t* num_post_pad, int64_t max_padded, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (n < 0 || num_experts <= 0 || num_experts > 4096 || !topk_ids || !sorted_ids || !tile_expert || !inv_pos ||
+      !num_post_pad)
+    return fail(B2_ERR_ARG, "moe_align_block_size: bad arguments (n=%d experts=%d)", n, num_experts);
+  if (max_padded % 128 != 0 || max_padded < b2_moe_max_padded(n, num_experts) || max_padded > 0x7fffffffll)
+    return fail(B2_ERR_ARG, "moe_align_block_size: max_padded must be a multiple of 128 and >= %lld",
+                (long long)b2_moe_max_padded(n, num_experts));
+  if (int r = check_cuda(moe_align128(topk_ids, n, num_experts, sorted_ids, tile_expert, inv_pos, num_post_pad,
+                                      static_cast<int>(max_padded), static_cast<cudaStream_t>(stream)),
+                         "moe_align_block_size launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
+int b2_quant_int8_rows_gather(const void* x, int x_dtype, int64_t ldx, const int32_t* row_map, int row_div,
+                              int row_limit, int8_t* q, int64_t ldq, float* s, int64_t P, int K, b2_stream_t stream) {
+  const char* op = "per_token_quant_int8 (gather)";
+  if (int r = check_fused_common(op, x, x_dtype, ldx, K, q, ldq, s, B2_QMODE_INT8_ROWS, P, K)) return r;
+  if (!row_map || row_div <= 0) return fail(B2_ERR_ARG, "%s: row_map / row_div missing", op);
+  if (P == 0) return B2_OK;
+  FusedQuantArgs a{};
+  a.x = x; a.ldx = ldx; a.q = reinterpret_cast<uint8_t*>(q); a.ldq = ldq; a.s = s; a.s_row_stride = 1;
+  a.tokens_per_expert = 1; a.M = P; a.K = K; a.q_eps = 1e-10f; a.fmin = -448.f; a.fmax = 448.f;
+  a.row_map = row_map; a.row_div = row_div; a.row_limit = row_limit;
+  if (int r = check_cuda(fused_quant_launch(0, B2_QMODE_INT8_ROWS, x_dtype, a, static_cast<cudaStream_t>(stream)),
+                         "per_token_quant_int8 (gather) launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
+int b2_gemm_s8_grouped(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
+                       const int32_t* tile_expert, int num_experts, void* D, int64_t ldd, int out_dtype, int64_t P,
+                       int N, int K, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16 && out_dtype != B2_DTYPE_S32)
+    return fail(B2_ERR_ARG, "grouped int8 gemm: out_dtype must be Half or BFloat16");
+  if (P < 0 || P > 0x7fffffffll || P % 128 != 0)
+    return fail(B2_ERR_ARG, "grouped int8 gemm: the row count must be a multiple of 128 (expert-padded layout)");
+  if (!tile_expert || num_experts <= 0) return fail(B2_ERR_ARG, "grouped int8 gemm: tile_expert / num_experts missing");
+  const int ob = out_dtype == B2_DTYPE_S32 ? 4 : 2;
+  if (int r = check_gemm_common(A, lda, W, ldw, D, ldd, ob, static_cast<int>(P), N, K)) return r;
+  if (out_dtype != B2_DTYPE_S32 && (!As || !Bs || !aligned16(Bs)))
+    return fail(B2_ERR_ARG, "grouped int8 gemm: scales must not be null (Bs 16-byte aligned)");
+  if (P == 0) return B2_OK;
+  GemmArgs a{};
+  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = As; a.Bs = Bs; a.bias = nullptr; a.bias_dtype = B2_DTYPE_F32;
+  a.D = D; a.ldd = ldd; a.out_dtype = out_dtype; a.M = static_cast<int>(P); a.N = N; a.K = K;
+  a.tile_expert = tile_expert; a.num_experts = num_experts;
+  char err[256];
+  int r = gemm_launch(GEMM_S8, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err, sizeof(err));
+  if (r) return fail(r, "grouped int8 gemm: %s", err);
+  return B2_OK;
+}
+
+int b2_moe_combine(const void* y, int64_t ldy, const int32_t* inv_pos, const float* topk_weights, void* out,
+                   int64_t ldo, int tokens, int topk, int H, int dtype, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (int r = check_act_dtype(dtype, "moe combine: y")) return r;
+  if (tokens < 0 || topk <= 0 || H <= 0 || H % 8 != 0 || !y || !inv_pos || !topk_weights || !out || ldy < H || ldo < H ||
+      ldy % 8 != 0 || ldo % 8 != 0 || !aligned16(y) || !aligned16(out))
+    return fail(B2_ERR_ARG, "moe combine: bad arguments (tokens=%d topk=%d H=%d)", tokens, topk, H);
+  if (tokens == 0) return B2_OK;
+  if (int r = check_cuda(moe_combine(y, ldy, inv_pos, topk_weights, out, ldo, tokens, topk, H, dtype,
+                                     static_cast<cudaStream_t>(stream)),
+                         "moe combine launch"))
+    return r;
+  count_launch();
+  return B2_OK;
+}
+
 size_t b2_bmm_e4m3_workspace(int M, int N) {
   return (static_cast<size_t>(M > 0 ? M : 0) + static_cast<size_t>(N > 0 ? N : 0)) * sizeof(float) + 512;
 }

@@ -28,6 +28,7 @@ struct KernelParams {
   const void* bias;
   int bias_dtype;
   int out_dtype;
+  const int32_t* tile_expert;  // grouped (MoE) mode: expert of every 128-row block of A (-1 = skip), else nullptr
   int M, N, K;
   int num_m_blocks, num_n_blocks, num_kb;
   int stages;

@@ -114,8 +114,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       for (int tile = unit; tile < num_tiles; tile += num_units) {
         int m_blk, n_blk;
         tile_coords(tile, p, m_blk, n_blk);
+        const int expert = p.tile_expert ? __ldg(p.tile_expert + m_blk) : 0;  // grouped (MoE) mode: CG == 1
+        if (expert < 0) continue;  // a padding block past the last routed token
         const int m_row = (m_blk * CG + cta_rank) * BM;
-        const int n_row = n_blk * BN + cta_rank * B_ROWS;
+        const int n_row = expert * p.N + n_blk * BN + cta_rank * B_ROWS;
         for (int kb = 0; kb < p.num_kb; ++kb) {
           const long long w0 = p.prof ? clock64() : 0;
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -159,6 +161,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       uint32_t acc_phase = 0;
       long long prof_full = 0, prof_acc = 0;
       for (int tile = unit; tile < num_tiles; tile += num_units) {
+        if (p.tile_expert) {
+          int m_blk, n_blk;
+          tile_coords(tile, p, m_blk, n_blk);
+          if (__ldg(p.tile_expert + m_blk) < 0) continue;
+        }
         long long w0 = p.prof ? clock64() : 0;
         mbar_wait(&acc_empty[acc], acc_phase ^ 1);
         if (p.prof) prof_acc += clock64() - w0;
@@ -226,6 +233,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     for (int tile = unit; tile < num_tiles; tile += num_units) {
       int m_blk, n_blk;
       tile_coords(tile, p, m_blk, n_blk);
+      const int expert = p.tile_expert ? __ldg(p.tile_expert + m_blk) : 0;
+      if (expert < 0) continue;
+      const float* Bs_e = p.Bs + static_cast<size_t>(expert) * p.N;  // per-expert channel scales [E, N]
       const int row0 = (m_blk * CG + cta_rank) * BM + quarter * 32;
       const int row = row0 + lane;
       const int col_tile = n_blk * BN;
@@ -237,7 +247,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       if (!raw_out) {
         for (int c = epi_tid; c < BN; c += 128) {
           const int col = col_tile + c;
-          smem_bs[c] = col < p.N ? __ldg(p.Bs + col) : 0.f;
+          smem_bs[c] = col < p.N ? __ldg(Bs_e + col) : 0.f;
           smem_bias[c] = (has_bias && col < p.N) ? load_bias(p.bias, p.bias_dtype, col) : -0.f;  // x + (-0) == x bit for bit
         }
       }
@@ -498,14 +508,23 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   // M in (32, 64]: still ahead on layers up to ~64 rows of W per SM (profiles/r01e_m64_probe.log: 9.4 vs 12.0 us on
   // 6144 x 4096, 15.7 vs 19.9 us on 7168 x 8192), behind on the widest ones where 128 x 256 persistent tiles stream well
   // (short K -- 8 K-blocks -- leaves the decode kernel nothing to pipeline at M > 32: 8.2 vs 6.8 us on 8192 x 1024)
-  const bool decode_shape =
-      a.M <= 32 || (a.M <= 64 && a.N <= 64 * sms && a.K >= 2048) || (a.M <= BM && a.N < 32 * sms);
-  if ((forced_config & 0x80000) ? a.M <= BM : ((forced_config & 0xff) == 0 && decode_shape))
+  const bool decode_shape = a.tile_expert == nullptr && (
+      a.M <= 32 || (a.M <= 64 && a.N <= 64 * sms && a.K >= 2048) || (a.M <= BM && a.N < 32 * sms));
+  if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert) : ((forced_config & 0xff) == 0 && decode_shape))
     return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);
   const TileConfig* cfg = &pick_config(a.M, a.N, sms);
   const int forced_debug = forced_config >> 8;  // developer experiments ride in the upper bits of the forced id
   forced_config &= 0xff;
   if (forced_config >= 1 && forced_config <= kNumConfigs) cfg = &kConfigs[forced_config - 1];
+  if (a.tile_expert) {
+    // grouped (MoE) mode: every 128-row block of A belongs to ONE expert (rows sorted and padded per expert), so the
+    // tile must be one block tall: 1-CTA configurations only
+    if (cfg->cg != 1) cfg = &kConfigs[a.N >= 256 ? 3 : (a.N >= 128 ? 2 : 1)];
+    if (a.bias) {
+      snprintf(err, err_len, "grouped GEMM takes no bias");
+      return B2_ERR_ARG;
+    }
+  }
   if (used_config) *used_config = cfg->name;
   const int bn = cfg->bn;
   const int cg = cfg->cg;
@@ -522,6 +541,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   p.bias = a.bias;
   p.bias_dtype = a.bias_dtype;
   p.out_dtype = a.out_dtype;
+  p.tile_expert = a.tile_expert;
   p.M = a.M;
   p.N = a.N;
   p.K = a.K;
@@ -550,7 +570,8 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
 
   CUtensorMap ta, tb, td;
   if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, p.a_box_rows, BK) ||
-      !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, b_rows, BK) ||
+      !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W,
+                    static_cast<uint64_t>(a.N) * (a.tile_expert ? a.num_experts : 1), a.K, a.ldw, b_rows, BK) ||
       !make_tmap_2d(&td, d_dt, out_bytes, a.D, a.M, a.N, a.ldd * out_bytes, 32,
                     (128 / out_bytes) < bn ? (128 / out_bytes) : bn)) {  // 64-byte boxes use SWIZZLE_64B
     snprintf(err, err_len, "cuTensorMapEncodeTiled failed (M=%d N=%d K=%d lda=%lld ldw=%lld ldd=%lld)", a.M, a.N,

@@ -79,14 +79,23 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
   }
   const int nvec = a.K / VEC;
   const int64_t rr = active ? row : 0;
+  // gather mode (MoE): output row r reads input row row_map[r] / row_div; ids >= row_limit are padding rows, which
+  // are quantized as all-zero rows (codes 0) so that the grouped GEMM's padding outputs are exact zeros
+  int64_t src = rr;
+  bool src_ok = true;
+  if (a.row_map != nullptr) {
+    const int32_t id = active ? a.row_map[rr] : 0;
+    src_ok = id < a.row_limit;
+    src = src_ok ? id / a.row_div : 0;
+  }
 
   float f[NC][VEC];
   float sum_sq = 0.f;
-  const T* xr = static_cast<const T*>(a.x) + rr * a.ldx;
+  const T* xr = static_cast<const T*>(a.x) + src * a.ldx;
 #pragma unroll
   for (int i = 0; i < NC; ++i) {
     const int v = t + i * TPR;
-    const bool on = active && v < nvec;
+    const bool on = active && src_ok && v < nvec;
 #pragma unroll
     for (int j = 0; j < VEC; ++j) f[i][j] = 0.f;
     if (on) {
@@ -278,6 +287,7 @@ static cudaError_t dispatch_fused(int prod, int mode, const FusedQuantArgs& a, c
 #define B2_FUSED_CASE(P_, M_) \
   if (prod == static_cast<int>(P_) && mode == static_cast<int>(M_)) return dispatch_fused_tpr<T, P_, M_>(a, st);
   B2_FUSED_CASE(Prod::NONE, QM::FP8_G128_V2)
+  B2_FUSED_CASE(Prod::NONE, QM::INT8_ROWS)
   B2_FUSED_CASE(Prod::SILU_MUL, QM::INT8_ROWS)
   B2_FUSED_CASE(Prod::SILU_MUL, QM::FP8_ROWS)
   B2_FUSED_CASE(Prod::SILU_MUL, QM::FP8_G128_V2)

@@ -239,5 +239,26 @@ def per_tensor_quant_fp8(x: torch.Tensor, scale: torch.Tensor | None = None):
     return q, scale.float().reshape(1)
 
 
+def fused_experts_int8(x, w13, w2, topk_weights, topk_ids, w13_scale, w2_scale):
+    """fused_experts_int8_kernel_impl (moe_int8.cpp:585-847) restated per (token, k): quantize x rows (bit-exact
+    restatement), h = int8 linear with the expert's gate/up weight (bit-exact), act = silu_and_mul (exact tanh:
+    tolerance-pinned, see silu_and_mul), quantize, int8 linear with the expert's down weight, fp32 weighted sum over k
+    in ascending order, one rounding to bf16."""
+    _chk_cpu(x, w13, w2, topk_weights, topk_ids, w13_scale, w2_scale)
+    T, H = x.shape
+    E = w13.shape[0]
+    out = torch.zeros(T, H, dtype=torch.float32)
+    ids = topk_ids.long()
+    for e in range(E):
+        tok, kk = (ids == e).nonzero(as_tuple=True)
+        if tok.numel() == 0:
+            continue
+        h = int8_scaled_mm_with_quant(x[tok].contiguous(), w13[e].contiguous(), w13_scale[e].reshape(-1), None)
+        act = silu_and_mul(h)
+        y = int8_scaled_mm_with_quant(act.contiguous(), w2[e].contiguous(), w2_scale[e].reshape(-1), None)
+        out.index_put_((tok, ), topk_weights[tok, kk].float()[:, None] * y.float(), accumulate=True)
+    return out.to(x.dtype)
+
+
 if __name__ == "__main__":
     print(build(force=True))

@@ -67,9 +67,11 @@ from .linear import (  # noqa: E402,F401
 )
 
 from .host_api import HostW8A8Int8Linear  # noqa: E402,F401
+from . import moe  # noqa: E402,F401
+from .moe import W8A8Int8MoEMethod, fused_experts  # noqa: E402,F401
 
 __all__ = [
-    "HostW8A8Int8Linear",
+    "HostW8A8Int8Linear", "moe", "W8A8Int8MoEMethod", "fused_experts",
     "capi", "ops", "int8_scaled_mm", "fp8_scaled_mm", "fp8_blockwise_scaled_mm", "sgl_per_token_quant_fp8",
     "sgl_per_token_group_quant_8bit", "per_token_quant_int8", "per_token_quant_int8_cpu",
     "int8_scaled_mm_with_quant", "sglang_per_token_quant_fp8", "sglang_per_token_group_quant_fp8",

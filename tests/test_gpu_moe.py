@@ -54,7 +54,7 @@ def test_grouped_int8_gemm_equals_dense_per_expert_bitwise(T, E, topk, H, N):
     x = (torch.randn(T, H, generator=g) / 10).bfloat16()
     w = torch.randint(-127, 128, (E, N, H), dtype=torch.int8, generator=g)
     ws = torch.rand(E, N, generator=g) * 1e-2
-    sorted_ids, tile_expert, inv_pos, _ = moe.moe_align_block128(ids.to(DEV), E)
+    sorted_ids, tile_expert, inv_pos, npp = moe.moe_align_block128(ids.to(DEV), E)
     P = sorted_ids.numel()
     a_q = torch.empty(P, H, dtype=torch.int8, device=DEV)
     a_s = torch.empty(P, dtype=torch.float32, device=DEV)
@@ -78,9 +78,11 @@ def test_grouped_int8_gemm_equals_dense_per_expert_bitwise(T, E, topk, H, N):
         dense = b2.int8_scaled_mm_with_quant(xd[tok.to(DEV)].contiguous(), w[e].to(DEV), ws[e].to(DEV), None,
                                              torch.bfloat16, False)
         assert torch.equal(got.view(torch.int16), dense.cpu().view(torch.int16))
-    # padding rows are exact zeros (all-zero codes)
-    pad = sorted_ids.cpu() >= T * topk
-    assert bool((out[pad] == 0).all())
+    # padding rows inside the used blocks are exact zeros (all-zero codes); blocks past num_post_pad are skipped by
+    # the kernel (tile_expert == -1) and their rows are never read
+    used = int(npp.item())
+    pad = sorted_ids.cpu()[:used] >= T * topk
+    assert bool((out[:used][pad] == 0).all())
 
 
 @pytest.mark.parametrize("T,E,topk,H,I", [(1, 8, 2, 512, 256), (37, 8, 2, 1024, 512), (256, 16, 4, 2048, 768),

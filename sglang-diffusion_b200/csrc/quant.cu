@@ -325,9 +325,37 @@ __global__ void __launch_bounds__(256) quant_group128_kernel(const T* __restrict
   }
   uint8_t* qr = q + row * ldq + static_cast<int64_t>(g0) * 128;
 #pragma unroll
+  // The IEEE division amax / fmax and the reciprocal of the scale are ~25 instructions each; every thread needs them
+  // for GQ_GROUPS groups, and the 16 threads of a group would all compute the same pair.  Instead lane `sub` computes
+  // the pair of group sub % GQ_GROUPS only and the 16-lane segment exchanges them with shuffles (profiles/
+  // r02i_group_quant.md: issue_active 65 %, the kernel is latency / issue bound, not HBM bound).
+  float f[GQ_GROUPS][8], amax[GQ_GROUPS];
+#pragma unroll
   for (int i = 0; i < GQ_GROUPS; ++i) {
+    const T* e = reinterpret_cast<const T*>(&v[i]);
+    float m = eps;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      f[i][j] = to_f32(e[j]);
+      m = fmaxf(m, fabsf(f[i][j]));
+    }
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    amax[i] = m;
+  }
+  float my_amax = amax[0];
+#pragma unroll
+  for (int i = 1; i < GQ_GROUPS; ++i)
+    if ((sub & (GQ_GROUPS - 1)) == i) my_amax = amax[i];
+  const float my_ys = __fdiv_rn(my_amax, fmax);
+  const float my_r = __frcp_rn(my_ys);
+  const int seg = threadIdx.x & 16;  // first lane of my 16-lane segment inside the warp
+#pragma unroll
+  for (int i = 0; i < GQ_GROUPS; ++i) {
+    const float ys = __shfl_sync(0xffffffffu, my_ys, seg + i);
+    const float r = __shfl_sync(0xffffffffu, my_r, seg + i);
     uint2 o;
-    const float ys = group128_quantize<T>(v[i], eps, fmin, fmax, o);
+    group128_apply_v1(f[i], ys, r, fmin, fmax, o);
     if (act[i]) reinterpret_cast<uint2*>(qr + i * 128)[sub] = o;
     if (sub == 0) s_scale[i][r_in] = ys;
   }

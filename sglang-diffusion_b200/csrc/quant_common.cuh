@@ -87,17 +87,27 @@ B2_DEVICE uint8_t quant_one(float x, float inv) {
 // is computed once and each quotient is q0 = RN(x r), q = RN(q0 + r (x - q0 ys)) -- Markstein's sequence, which
 // returns RN(x / ys) whenever the significand of ys is not all ones (that case, group-uniform, takes the division).
 // `amax` is already reduced over the 16 lanes and already >= eps.  Returns the scale.
-B2_DEVICE float group128_quantize_v1(const float (&f)[8], float amax, float fmin, float fmax, uint2& out) {
-  const float ys = __fdiv_rn(amax, fmax);
-  const float r = __frcp_rn(ys);
+// the codes of 8 values given the group scale ys = amax / fmax and its correctly rounded reciprocal r = RN(1 / ys)
+B2_DEVICE void group128_apply_v1(const float (&f)[8], float ys, float r, float fmin, float fmax, uint2& out) {
   float qv[8];
   // ONE group-uniform branch (not one per element): the all-ones significand is the only case the reciprocal
   // sequence does not cover
   if ((__float_as_uint(ys) & 0x7fffffu) != 0x7fffffu) {
+    // packed fp32x2 arithmetic (two IEEE roundings per issue slot, each lane exactly the scalar mul.rn / fma.rn): the
+    // kernel is issue-bound, and these 24 scalar operations per thread were a third of its instruction stream
+    uint64_t r2, nys2;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(r2) : "f"(r));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(nys2) : "f"(-ys));
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float q0 = __fmul_rn(f[j], r);
-      qv[j] = __fmaf_rn(__fmaf_rn(-q0, ys, f[j]), r, q0);
+    for (int j = 0; j < 8; j += 2) {
+      asm("{\n\t.reg .b64 xx, q0, rem;\n\t"
+          "mov.b64 xx, {%2, %3};\n\t"
+          "mul.rn.f32x2 q0, xx, %4;\n\t"
+          "fma.rn.f32x2 rem, q0, %5, xx;\n\t"
+          "fma.rn.f32x2 q0, rem, %4, q0;\n\t"
+          "mov.b64 {%0, %1}, q0;\n\t}"
+          : "=f"(qv[j]), "=f"(qv[j + 1])
+          : "f"(f[j]), "f"(f[j + 1]), "l"(r2), "l"(nys2));
     }
   } else {
 #pragma unroll
@@ -113,6 +123,12 @@ B2_DEVICE float group128_quantize_v1(const float (&f)[8], float amax, float fmin
   }
   out.x = static_cast<uint32_t>(f32x2_to_e4m3x2(qv[0], qv[1])) | (static_cast<uint32_t>(f32x2_to_e4m3x2(qv[2], qv[3])) << 16);
   out.y = static_cast<uint32_t>(f32x2_to_e4m3x2(qv[4], qv[5])) | (static_cast<uint32_t>(f32x2_to_e4m3x2(qv[6], qv[7])) << 16);
+}
+
+B2_DEVICE float group128_quantize_v1(const float (&f)[8], float amax, float fmin, float fmax, uint2& out) {
+  const float ys = __fdiv_rn(amax, fmax);
+  const float r = __frcp_rn(ys);
+  group128_apply_v1(f, ys, r, fmin, fmax, out);
   return ys;
 }
 

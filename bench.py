@@ -348,11 +348,15 @@ def tp_leg(b2, dev, dist, world, rank, comm):
                 layer(x)
 
         res = {"M": M, "tp": world}
-        for mode in ("nccl", "b2_allreduce_symm"):
+        for mode in ("nccl", "b2_allreduce_symm", "b2_fused_push"):
             for _, par, _, _, _, layer in layers:
                 layer.symm_comm = comm if (mode != "nccl" and par == "row") else None
+                layer.symm_fused_push = mode == "b2_fused_push"
             if mode != "nccl" and (comm is None or not comm.fits(M, 8192, torch.bfloat16)):
                 res[mode] = None
+                continue
+            if mode == "b2_fused_push" and not comm.fits_push(M, 8192, torch.bfloat16):
+                res[mode] = None  # GEMM-epilogue push is built for decode shapes (M <= 128) with a multicast mapping
                 continue
             ms = _time_device(step, dev, dist, world, 200 if M == 64 else 10, graph_inner=10 if M == 64 else 0)
             per_layer = {}
@@ -378,6 +382,7 @@ def tp_leg(b2, dev, dist, world, rank, comm):
                     check["ok"] = check["ok"] and err < 6e-2
         for *_, layer in layers:
             layer.symm_comm = None
+            layer.symm_fused_push = True
         res["allreduce_bytes_per_row_layer"] = M * 8192 * 2
         rows.append(res)
     check["max_rel_err"] = round(check["max_rel_err"], 5)
@@ -422,6 +427,28 @@ def symm_allreduce_parity(dev, dist, world, rank, comm):
     if out["algo2_within_1ulp"] is not None:
         out["algo2_within_1ulp"] = bool(flags[1].item())
     out["ok"] = bool(flags.min().item())
+    # GEMM-epilogue-fused form: equal, bit for bit, to GEMM + one-shot all-reduce (same rank-ordered fp32 sum)
+    if comm.multicast_ptr:
+        from sglang_diffusion_b200 import ops
+
+        eq = True
+        for M, N, K in ((16, 8192, 1024), (64, 8192, 3584)):
+            for it in range(3):
+                g = torch.Generator(device=dev).manual_seed(77 * rank + M + it)
+                x = (torch.randn(M, K, generator=g, device=dev) / 10).bfloat16()
+                W = torch.randn(N, K, generator=g, device=dev).to(torch.float8_e4m3fn)
+                Bs = torch.rand(N, generator=g, device=dev) * 1e-2
+                q, s = ops.sglang_per_token_quant_fp8(x)
+                part = ops.scaled_mm_out(q, W.t(), s.view(-1), Bs, comm.partial(M, N, torch.bfloat16), None)
+                want = comm.all_reduce(part, 1)
+                comm.push_gemm(q, W.t(), s.view(-1), Bs, torch.bfloat16, None)
+                got = comm.reduce_gathered(M, N, torch.bfloat16)
+                torch.cuda.synchronize(dev)
+                eq = eq and torch.equal(got.view(torch.int16), want.view(torch.int16))
+        f2 = torch.tensor([int(eq)], device=dev)
+        dist.all_reduce(f2, op=dist.ReduceOp.MIN)
+        out["fused_push_equals_one_shot_bitwise"] = bool(f2.item())
+        out["ok"] = out["ok"] and out["fused_push_equals_one_shot_bitwise"]
     return out
 
 

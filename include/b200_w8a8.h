@@ -250,6 +250,28 @@ const char* b2_last_gemm_config(void);
 int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* signal_pads_dev, void* multicast_ptr, void* out,
                       int64_t numel, int dtype, int rank, int world, int algo, int max_blocks, b2_stream_t stream);
 
+/* GEMM-epilogue-fused all-reduce for decode-shape row-parallel layers (SURVEY 8f rank 2;
+ * python/sglang/srt/layers/linear.py:1467-1496, sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:204-260).
+ * Step 1, b2_gemm_{s8,e4m3}_push_symm: the scaled GEMM of b2_gemm_s8 / b2_gemm_e4m3 (M <= 128), whose epilogue stores
+ * this rank's [M,N] partial output with multimem.st through `multicast_ptr` -- the NVSwitch multicast mapping of the
+ * symmetric buffer -- into slot `rank` of EVERY rank's buffer: the partials leave for the peers tile by tile while the
+ * GEMM is still running, no separate copy or reduce-scatter step.  The buffer holds two sets of `world` slots of
+ * M*N out_dtype elements each (>= 2*world*M*N*2 bytes); the set in use alternates per call (counter in word 1544 of the
+ * local signal pad, advanced on the device, so CUDA-graph replays stay consistent).
+ * Step 2, b2_allreduce_symm_gathered: ONE barrier ("every rank's GEMM has completed") and a sum over the `world` slots
+ * of LOCAL memory in rank order (fp32, one rounding): bit-identical on every rank and equal to algo 1 of
+ * b2_allreduce_symm.  Every rank must make the same sequence of calls; the signal pads are the ones of
+ * b2_allreduce_symm (same ownership rule).  bias: added by the GEMM (give it on one rank only, linear.py:1480). */
+int b2_gemm_s8_push_symm(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
+                         const void* bias, int bias_dtype, void* multicast_ptr, uint32_t* local_signal_pad, int rank,
+                         int world, int out_dtype, int M, int N, int K, b2_stream_t stream);
+int b2_gemm_e4m3_push_symm(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* As,
+                           const float* Bs, const void* bias, int bias_dtype, void* multicast_ptr,
+                           uint32_t* local_signal_pad, int rank, int world, int out_dtype, int M, int N, int K,
+                           b2_stream_t stream);
+int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const* signal_pads_dev, void* out, int64_t numel,
+                               int dtype, int rank, int world, int max_blocks, b2_stream_t stream);
+
 /* Waits of b2_allreduce_symm on a peer.  0 (default): wait for ever -- a late peer (first-iteration skew, weight load,
  * debugger) is not an error, hangs are the host watchdog's business, as with the reference's custom all-reduce.
  * ms > 0: a wait gives up after that long (%globaltimer), stores the barrier number in word 1536 of this rank's

@@ -29,6 +29,7 @@ SYMBOLS = [
     "b2_quant_int8_rows_sum", "b2_quant_fp8_tensor", "b2_silu_mul_quant", "b2_rmsnorm_quant",
     "b2_quant_fp8_group128_v2", "b2_bmm_e4m3_workspace", "b2_bmm_e4m3",
     "b2_set_allreduce_timeout_ms", "b2_get_allreduce_timeout_ms",
+    "b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered",
     "b2_moe_max_padded", "b2_moe_align_block128", "b2_quant_int8_rows_gather", "b2_gemm_s8_grouped", "b2_moe_combine",
 ]
 
@@ -90,6 +91,12 @@ for _n in ("b2_quant_int8_rows_sum", "b2_quant_fp8_tensor", "b2_silu_mul_quant",
 lib.b2_set_allreduce_timeout_ms.argtypes = [ctypes.c_longlong]
 lib.b2_set_allreduce_timeout_ms.restype = None
 lib.b2_get_allreduce_timeout_ms.restype = ctypes.c_longlong
+_push = [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]
+lib.b2_gemm_s8_push_symm.argtypes = _push
+lib.b2_gemm_e4m3_push_symm.argtypes = _push
+lib.b2_allreduce_symm_gathered.argtypes = [_vp, _vp, _vp, _i64, _i, _i, _i, _i, _vp]
+for _n in ("b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered"):
+    getattr(lib, _n).restype = _i
 lib.b2_moe_max_padded.argtypes = [_i64, _i]
 lib.b2_moe_max_padded.restype = _i64
 lib.b2_moe_align_block128.argtypes = [_vp, _i, _i, _vp, _vp, _vp, _vp, _i64, _vp]

@@ -58,6 +58,39 @@ class SymmAllReduce:
         pad = self.handle.get_signal_pad(self.rank, (1537,), torch.uint32)
         return int(pad[1536].item())
 
+    # ---- GEMM-epilogue-fused form (b2_gemm_*_push_symm + b2_allreduce_symm_gathered) ----
+
+    def fits_push(self, M: int, N: int, dtype: torch.dtype) -> bool:
+        """The decode-shape GEMM can push its partials through the multicast mapping: needs the NVSwitch mapping, M <=
+        128 and room for two sets of `world` slots."""
+        return (self.multicast_ptr != 0 and dtype in _DT and 0 < M <= 128 and (M * N) % 8 == 0
+                and 2 * self.world * M * N * dtype.itemsize <= self.max_bytes)
+
+    def push_gemm(self, q: torch.Tensor, weight: torch.Tensor, a_scale: torch.Tensor, w_scale: torch.Tensor,
+                  out_dtype: torch.dtype, bias: Optional[torch.Tensor] = None) -> None:
+        """int8 / e4m3 scaled GEMM (chosen by q.dtype; weight is [K,N] with stride(0) == 1) whose epilogue stores this
+        rank's partial output into slot `rank` of every rank's gather buffer."""
+        M, K = q.shape
+        N = weight.shape[1]
+        assert weight.shape[0] == K and weight.stride(0) == 1 and q.stride(1) == 1
+        fn = capi.lib.b2_gemm_s8_push_symm if q.dtype == torch.int8 else capi.lib.b2_gemm_e4m3_push_symm
+        bdt = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16, torch.float32: capi.DTYPE_F32}
+        with torch.cuda.device(q.device):
+            capi.check(fn(q.data_ptr(), q.stride(0) if M > 1 else K, weight.data_ptr(), weight.stride(1) if N > 1 else K,
+                          a_scale.data_ptr(), w_scale.data_ptr(), None if bias is None else bias.data_ptr(),
+                          bdt[bias.dtype] if bias is not None else capi.DTYPE_F32, self.multicast_ptr,
+                          int(self.handle.signal_pad_ptrs[self.rank]), self.rank, self.world, _DT[out_dtype], M, N, K,
+                          torch.cuda.current_stream(q.device).cuda_stream))
+
+    def reduce_gathered(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
+        """Barrier + rank-ordered fp32 sum of the `world` pushed slots (local memory) -> fresh [M,N] tensor."""
+        out = torch.empty(M, N, dtype=dtype, device=self.device)
+        with torch.cuda.device(self.device):
+            capi.check(capi.lib.b2_allreduce_symm_gathered(self.buf.data_ptr(), self.pads_dev, out.data_ptr(), M * N,
+                                                           _DT[dtype], self.rank, self.world, self.max_blocks,
+                                                           torch.cuda.current_stream(self.device).cuda_stream))
+        return out
+
     def partial(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
         """[M,N] view of the local symmetric buffer: the GEMM's output operand."""
         nbytes = M * N * dtype.itemsize

@@ -209,9 +209,59 @@ __global__ void __launch_bounds__(512) allreduce_one_shot_kernel(uint4* const* b
   if (threadIdx.x == 0) pads[rank][kEpochWord + blockIdx.x] = epoch + 2;
 }
 
+// ---- gathered form: the GEMM epilogue has already PUSHED every rank's partials into every rank's buffer ----
+// (gemm_splitk_sm100.cu, SplitParams::mc_*: multimem.st through the NVSwitch multicast mapping, slot `rank` of set
+// counter & 1).  What is left of the all-reduce is one barrier -- "every rank's GEMM has completed" -- and a sum over
+// `world` slots of LOCAL memory in rank order (fp32, one rounding: bit-identical on every rank and equal to the
+// one-shot kernel above).  Two sets alternate so that a rank may start pushing call n+2 while a slow peer still sums
+// call n+1; call n's readers are done by then: the pusher has passed barrier n+1, which every peer only enters after
+// its call-n kernel completed.  The counter lives in the signal pad so that CUDA-graph replays advance it.
+constexpr int kGatherCounterWord = 1024 + 520;
+constexpr int kGatherDoneWord = 1024 + 521;
+
+template <bool BF16>
+__global__ void __launch_bounds__(512) allreduce_gathered_kernel(const uint4* __restrict__ local_buf,
+                                                                  uint32_t* const* pads, uint4* __restrict__ out,
+                                                                  long long nvec, int rank, int world,
+                                                                  unsigned long long timeout_ns) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // this rank's GEMM has completed: its pushes are performed
+  uint32_t* pad = pads[rank];
+  const uint32_t epoch = pad[kEpochWord + blockIdx.x];
+  const uint32_t counter = pad[kGatherCounterWord];
+  xgpu_barrier<true>(pads, rank, world, epoch + 1, timeout_ns);
+  const uint4* set = local_buf + static_cast<long long>(counter & 1u) * nvec * world;
+  const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
+  for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += stride) {
+    float acc[8];
+    unpack8<BF16>(set[v], acc);
+    for (int r = 1; r < world; ++r) {  // rank order: the same fp32 sum, bit for bit, on every rank
+      float f[8];
+      unpack8<BF16>(set[static_cast<long long>(r) * nvec + v], f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
+    }
+    out[v] = pack8<BF16>(acc);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    pad[kEpochWord + blockIdx.x] = epoch + 1;
+    __threadfence();
+    const uint32_t t = atomicAdd(&pad[kGatherDoneWord], 1u);
+    if (t == gridDim.x - 1) {  // last CTA of this call: every CTA has read the counter
+      pad[kGatherDoneWord] = 0;
+      pad[kGatherCounterWord] = counter + 1;
+    }
+  }
+}
+
 }  // namespace b2
 
 using namespace b2;
+
+extern "C" int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const* signal_pads_dev, void* out,
+                                          int64_t numel, int dtype, int rank, int world, int max_blocks,
+                                          b2_stream_t stream);
 
 #include <atomic>
 static std::atomic<long long> g_ar_timeout_ms{0};
@@ -277,3 +327,42 @@ extern "C" int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* si
   count_launch();
   return B2_OK;
 }
+
+extern "C" int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const* signal_pads_dev, void* out,
+                                          int64_t numel, int dtype, int rank, int world, int max_blocks,
+                                          b2_stream_t stream) {
+  if (!local_buf || !signal_pads_dev || !out) return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: null pointer");
+  if (dtype != B2_DTYPE_BF16 && dtype != B2_DTYPE_F16)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: dtype must be bfloat16 or float16");
+  if (world < 2 || world > 8 || rank < 0 || rank >= world)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: world size must be 2..8, rank inside it");
+  if (numel <= 0 || numel % 8 != 0) return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: numel must be a positive multiple of 8");
+  if (reinterpret_cast<uintptr_t>(out) % 16 != 0 || reinterpret_cast<uintptr_t>(local_buf) % 16 != 0)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: buffers must be 16-byte aligned");
+  const long long nvec = numel / 8;
+  const int threads = 512;
+  long long blocks = (nvec + threads - 1) / threads;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks > kEpochWord / world) blocks = kEpochWord / world;
+  if (blocks < 1) blocks = 1;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(blocks));
+  cfg.blockDim = dim3(threads);
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const unsigned long long tmo = static_cast<unsigned long long>(g_ar_timeout_ms.load()) * 1000000ull;
+  const uint4* lb = static_cast<const uint4*>(local_buf);
+  uint4* o = static_cast<uint4*>(out);
+  cudaError_t le = dtype == B2_DTYPE_BF16
+                       ? cudaLaunchKernelEx(&cfg, allreduce_gathered_kernel<true>, lb, signal_pads_dev, o, nvec, rank, world, tmo)
+                       : cudaLaunchKernelEx(&cfg, allreduce_gathered_kernel<false>, lb, signal_pads_dev, o, nvec, rank, world, tmo);
+  if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm_gathered launch: %s", cudaGetErrorString(le));
+  count_launch();
+  return B2_OK;
+}
+
+extern "C" int b2_symm_gather_counter_word(void) { return kGatherCounterWord; }

@@ -75,6 +75,11 @@ struct GemmArgs {
   // [128 b, 128 b + 128) of A (expert-sorted, padded per expert), -1 = no tokens
   const int32_t* tile_expert;
   int num_experts;
+  // decode-shape row-parallel layers: push the output through the NVSwitch multicast mapping into every rank's gather
+  // buffer instead of D (gemm_splitk_sm100.cu SplitParams::mc_*); nullptr = off
+  void* mc_slot;
+  long long mc_set_bytes;
+  const uint32_t* mc_counter;
 };
 
 enum GemmFlavor { GEMM_S8 = 0, GEMM_E4M3 = 1, GEMM_E4M3_BLOCK128 = 2 };

@@ -338,6 +338,50 @@ int b2_gemm_e4m3(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, c
   return B2_OK;
 }
 
+extern "C" int b2_symm_gather_counter_word(void);
+
+static int gemm_push_symm(GemmFlavor flavor, const char* op, const void* A, int64_t lda, const void* W, int64_t ldw,
+                          const float* As, const float* Bs, const void* bias, int bias_dtype, void* multicast_ptr,
+                          uint32_t* local_signal_pad, int rank, int world, int out_dtype, int M, int N, int K,
+                          b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16) return fail(B2_ERR_ARG, "%s: out_dtype must be Half or BFloat16", op);
+  if (!multicast_ptr || !local_signal_pad || world < 2 || world > 8 || rank < 0 || rank >= world)
+    return fail(B2_ERR_ARG, "%s: multicast pointer / signal pad / rank / world (2..8) invalid", op);
+  if (M > 128) return fail(B2_ERR_ARG, "%s: the push epilogue is built for decode shapes (M <= 128)", op);
+  if (int r = check_gemm_common(A, lda, W, ldw, multicast_ptr, N, 2, M, N, K)) return r;
+  if (!As || !Bs || !aligned16(Bs)) return fail(B2_ERR_ARG, "%s: scales must not be null (Bs 16-byte aligned)", op);
+  if (bias && !aligned16(bias)) return fail(B2_ERR_ARG, "%s: bias must be 16-byte aligned", op);
+  if ((static_cast<int64_t>(M) * N) % 8 != 0) return fail(B2_ERR_ARG, "%s: M*N must be a multiple of 8", op);
+  if (M == 0) return B2_OK;
+  GemmArgs a{};
+  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = As; a.Bs = Bs; a.bias = bias; a.bias_dtype = bias_dtype;
+  a.D = multicast_ptr; a.ldd = N; a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K;
+  const long long slot = static_cast<long long>(M) * N * 2;
+  a.mc_slot = static_cast<uint8_t*>(multicast_ptr) + slot * rank;
+  a.mc_set_bytes = slot * world;
+  a.mc_counter = local_signal_pad + b2_symm_gather_counter_word();
+  char err[256];
+  int r = gemm_launch(flavor, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err, sizeof(err));
+  if (r) return fail(r, "%s: %s", op, err);
+  return B2_OK;
+}
+
+int b2_gemm_s8_push_symm(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
+                         const void* bias, int bias_dtype, void* multicast_ptr, uint32_t* local_signal_pad, int rank,
+                         int world, int out_dtype, int M, int N, int K, b2_stream_t stream) {
+  return gemm_push_symm(GEMM_S8, "int8_scaled_mm (push)", A, lda, W, ldw, As, Bs, bias, bias_dtype, multicast_ptr,
+                        local_signal_pad, rank, world, out_dtype, M, N, K, stream);
+}
+
+int b2_gemm_e4m3_push_symm(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* As,
+                           const float* Bs, const void* bias, int bias_dtype, void* multicast_ptr,
+                           uint32_t* local_signal_pad, int rank, int world, int out_dtype, int M, int N, int K,
+                           b2_stream_t stream) {
+  return gemm_push_symm(GEMM_E4M3, "fp8_scaled_mm (push)", A, lda, W, ldw, As, Bs, bias, bias_dtype, multicast_ptr,
+                        local_signal_pad, rank, world, out_dtype, M, N, K, stream);
+}
+
 int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* sfa,
                           int64_t sfa_m_stride, int64_t sfa_k_stride, const float* sfb, int64_t sfb_n_stride,
                           int64_t sfb_k_stride, const void* bias, int bias_dtype, void* D, int64_t ldd,

@@ -510,6 +510,11 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   // (short K -- 8 K-blocks -- leaves the decode kernel nothing to pipeline at M > 32: 8.2 vs 6.8 us on 8192 x 1024)
   const bool decode_shape = a.tile_expert == nullptr && (
       a.M <= 32 || (a.M <= 64 && a.N <= 64 * sms && a.K >= 2048) || (a.M <= BM && a.N < 32 * sms));
+  if (a.mc_slot != nullptr && !(decode_shape || a.M <= BM)) {
+    snprintf(err, err_len, "multicast push epilogue is built for decode shapes (M <= 128) only");
+    return B2_ERR_ARG;
+  }
+  if (a.mc_slot != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
   if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert) : ((forced_config & 0xff) == 0 && decode_shape))
     return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);
   const TileConfig* cfg = &pick_config(a.M, a.N, sms);

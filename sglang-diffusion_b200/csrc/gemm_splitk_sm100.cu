@@ -44,7 +44,17 @@ struct SplitParams {
   uint32_t tmem_cols;   // power of two >= max(32, bn)
   uint32_t part_pitch;  // bytes per row of the partial buffer: bn rounded up to 32 words (the XOR swizzle's span)
   uint32_t bar_offset;  // byte offset of the barrier block inside the dynamic shared-memory window
+  // Row-parallel tensor-parallel layers: instead of D, the epilogue stores this rank's partial output through the
+  // NVSwitch multicast mapping into slot `rank` of EVERY rank's gather buffer (multimem.st), set (counter & 1) of two
+  // -- the reduction that follows (allreduce_symm.cu, gathered form) then only reads local memory.  nullptr = off.
+  uint8_t* mc_slot;             // multicast address of this rank's slot in set 0
+  long long mc_set_bytes;       // distance between the two sets
+  const uint32_t* mc_counter;   // device-resident call counter (local signal pad); read after griddepcontrol.wait
 };
+
+B2_DEVICE void multimem_st_v2(void* mc, uint32_t a, uint32_t b) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc), "r"(a), "r"(b) : "memory");
+}
 
 B2_DEVICE uint32_t ld_dsmem_u32(uint32_t local_addr, uint32_t cta) {
   uint32_t v;
@@ -258,6 +268,8 @@ __global__ void __launch_bounds__(NUM_THREADS)
     // loads are conflict free and the global stores of a warp cover whole contiguous row segments
     const uint32_t part_base = smem_u32(part);
     const int items = p.M * gpr;
+    uint8_t* mc_out = nullptr;
+    if (p.mc_slot != nullptr) mc_out = p.mc_slot + static_cast<long long>(__ldg(p.mc_counter) & 1u) * p.mc_set_bytes;
     for (int idx = epi_tid; idx < items; idx += 128) {
       const int row = idx / gpr;
       const int g = idx - row * gpr;
@@ -302,7 +314,8 @@ __global__ void __launch_bounds__(NUM_THREADS)
         uint2 w;
         w.x = pack16(v[0], v[1], p.out_dtype);
         w.y = pack16(v[2], v[3], p.out_dtype);
-        *reinterpret_cast<uint2*>(static_cast<uint16_t*>(p.D) + o) = w;
+        if (mc_out != nullptr) multimem_st_v2(mc_out + o * 2, w.x, w.y);
+        else *reinterpret_cast<uint2*>(static_cast<uint16_t*>(p.D) + o) = w;
       }
     }
   }
@@ -465,6 +478,9 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
   while (p.tmem_cols < static_cast<uint32_t>(bn)) p.tmem_cols *= 2;
   p.part_pitch = static_cast<uint32_t>((bn + 31) / 32 * 32) * 4u;
   p.bar_offset = static_cast<uint32_t>(plan.smem - 1024);
+  p.mc_slot = static_cast<uint8_t*>(a.mc_slot);
+  p.mc_set_bytes = a.mc_set_bytes;
+  p.mc_counter = a.mc_counter;
 
   CUtensorMap ta, tb;
   if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, a_rows, BK) ||

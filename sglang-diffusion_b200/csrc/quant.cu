@@ -324,7 +324,6 @@ __global__ void __launch_bounds__(256) quant_group128_kernel(const T* __restrict
     if (act[i]) v[i] = ld_stream(reinterpret_cast<const uint4*>(xr + i * 128) + sub);
   }
   uint8_t* qr = q + row * ldq + static_cast<int64_t>(g0) * 128;
-#pragma unroll
   // The IEEE division amax / fmax and the reciprocal of the scale are ~25 instructions each; every thread needs them
   // for GQ_GROUPS groups, and the 16 threads of a group would all compute the same pair.  Instead lane `sub` computes
   // the pair of group sub % GQ_GROUPS only and the 16-lane segment exchanges them with shuffles (profiles/

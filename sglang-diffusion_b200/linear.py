@@ -207,6 +207,16 @@ class QuantLinear(torch.nn.Module):
             return None
         x2d = x.view(-1, x.shape[-1])
         M, N = x2d.shape[0], self.weight.shape[1]
+        if getattr(self, "symm_fused_push", True) and comm.fits_push(M, N, x.dtype):
+            # decode shapes: the GEMM epilogue pushes the partials to every rank through the NVSwitch multicast
+            # mapping; what is left of the all-reduce is one barrier + a local rank-ordered sum
+            with capi.static_weights():
+                if isinstance(self.quant_method, W8A8Int8LinearMethod):
+                    q, s = ops.per_token_quant_int8(x2d)
+                else:
+                    q, s = ops.sglang_per_token_quant_fp8(x2d)
+                comm.push_gemm(q, self.weight, s.view(-1), self.weight_scale.view(-1), x.dtype, bias)
+                return comm.reduce_gathered(M, N, x.dtype).view(*x.shape[:-1], N)
         if not comm.fits(M, N, x.dtype):
             return None
         with capi.static_weights():

@@ -340,7 +340,7 @@ def tp_leg(b2, dev, dist, world, rank, comm):
         del w
         layers.append((name, par, K, N, k_loc, layer))
     rows, check = [], {"max_rel_err": 0.0, "ok": True}
-    for M in (64, 8192):
+    for M in (16, 64, 8192):
         xs = [(torch.randn(M, k_loc, generator=g, device=dev) / 10).bfloat16() for *_, k_loc, _ in layers]
 
         def step():
@@ -358,11 +358,11 @@ def tp_leg(b2, dev, dist, world, rank, comm):
             if mode == "b2_fused_push" and not comm.fits_push(M, 8192, torch.bfloat16):
                 res[mode] = None  # GEMM-epilogue push is built for decode shapes (M <= 128) with a multicast mapping
                 continue
-            ms = _time_device(step, dev, dist, world, 200 if M == 64 else 10, graph_inner=10 if M == 64 else 0)
+            ms = _time_device(step, dev, dist, world, 200 if M <= 64 else 10, graph_inner=10 if M <= 64 else 0)
             per_layer = {}
             for x, (name, par, K, N, _, layer) in zip(xs, layers):
-                per_layer[name] = round(_time_device(lambda: layer(x), dev, dist, world, 100 if M == 64 else 5,
-                                                     graph_inner=10 if M == 64 else 0) * 1e3, 1)
+                per_layer[name] = round(_time_device(lambda: layer(x), dev, dist, world, 100 if M <= 64 else 5,
+                                                     graph_inner=10 if M <= 64 else 0) * 1e3, 1)
             ops = sum(2.0 * M * N * K for _, _, K, N, _, _ in layers)
             res[mode] = {"us_per_decoder_layer_linears": round(ms * 1e3, 1), "tops_aggregate": round(ops / (ms * 1e-3) / 1e12, 1),
                          "us_per_layer": per_layer}
@@ -382,7 +382,7 @@ def tp_leg(b2, dev, dist, world, rank, comm):
                     check["ok"] = check["ok"] and err < 6e-2
         for *_, layer in layers:
             layer.symm_comm = None
-            layer.symm_fused_push = True
+            layer.symm_fused_push = None
         res["allreduce_bytes_per_row_layer"] = M * 8192 * 2
         rows.append(res)
     check["max_rel_err"] = round(check["max_rel_err"], 5)

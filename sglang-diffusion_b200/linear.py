@@ -207,7 +207,13 @@ class QuantLinear(torch.nn.Module):
             return None
         x2d = x.view(-1, x.shape[-1])
         M, N = x2d.shape[0], self.weight.shape[1]
-        if getattr(self, "symm_fused_push", True) and comm.fits_push(M, N, x.dtype):
+        # fused push moves world x the message into every rank (an all-gather of partials): measured ahead of the
+        # separate NVSwitch two-shot reduction only while that stays small (profiles/r02j_bench_{2,8}gpu.json:
+        # M = 64, N = 8192 on 8 ranks: 28.0 us pushed vs 20.9 us two-shot vs 37.4 us NCCL)
+        push = getattr(self, "symm_fused_push", None)
+        if push is None:
+            push = comm.world * M * N * x.dtype.itemsize <= (1 << 20)
+        if push and comm.fits_push(M, N, x.dtype):
             # decode shapes: the GEMM epilogue pushes the partials to every rank through the NVSwitch multicast
             # mapping; what is left of the all-reduce is one barrier + a local rank-ordered sum
             with capi.static_weights():

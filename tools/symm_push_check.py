@@ -68,8 +68,9 @@ for kind in ("int8", "fp8"):
                       f"cfg={capi.last_gemm_config()}", flush=True)
 
 # graph replay with an odd number of calls per graph
+# (int8: exact int32 accumulation, so the comparison does not depend on which kernel plan either path picks)
 M, N, K = 64, 8192, 1024
-q, s, W, Bs, bias = problem("fp8", M, N, K, 999)
+q, s, W, Bs, bias = problem("int8", M, N, K, 999)
 want = reference(q, s, W, Bs, bias, M, N)
 torch.cuda.synchronize()
 st = torch.cuda.Stream()

@@ -443,7 +443,7 @@ template <int OUT_KIND, int CG>
 static int launch_bw(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const BlockwiseParams& p,
                      int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
   auto kern = gemm_block128_kernel<OUT_KIND, CG>;
-  static int attr_dev = -1;
+  static thread_local int attr_dev = -1;
   int dev = 0;
   cudaGetDevice(&dev);
   if (attr_dev != dev) {

@@ -446,7 +446,7 @@ template <MmaKind KIND, int OUT_KIND, int BN, int CG>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const KernelParams& p,
                       int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
   auto kern = gemm_w8a8_kernel<KIND, OUT_KIND, BN, CG>;
-  static int attr_dev = -1;  // per instantiation; the attribute is per-function, per-device context
+  static thread_local int attr_dev = -1;  // per instantiation; the attribute is per-function, per-device context
   int dev = 0;
   cudaGetDevice(&dev);
   if (attr_dev != dev) {

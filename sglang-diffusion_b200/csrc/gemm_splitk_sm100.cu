@@ -351,7 +351,7 @@ static int deepest_ring(int bn, int a_rows, int kb_per) {
 
 template <MmaKind KIND>
 static void configure_kernel(char* err, size_t err_len, int* status) {
-  static int attr_dev = -1;
+  static thread_local int attr_dev = -1;
   int dev = 0;
   cudaGetDevice(&dev);
   if (attr_dev == dev) return;

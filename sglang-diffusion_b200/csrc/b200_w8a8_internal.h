@@ -80,6 +80,10 @@ struct GemmArgs {
   void* mc_slot;
   long long mc_set_bytes;
   const uint32_t* mc_counter;
+  // decode shapes (M <= 32): bf16 / f16 activations quantized inside the split-K kernel (A and As are then unused)
+  const void* x;
+  int64_t ldx;
+  int x_dtype;
 };
 
 enum GemmFlavor { GEMM_S8 = 0, GEMM_E4M3 = 1, GEMM_E4M3_BLOCK128 = 2 };

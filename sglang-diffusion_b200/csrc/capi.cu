@@ -527,11 +527,44 @@ static size_t ws_bytes(int M, int K) {
 size_t b2_linear_w8a8_int8_workspace(int M, int K) { return ws_bytes(M, K); }
 size_t b2_linear_w8a8_fp8_workspace(int M, int K) { return ws_bytes(M, K); }
 
+// M <= 32: ONE kernel -- the split-K decode GEMM quantizes its own K slice of the activations into shared memory
+// (gemm_splitk_sm100.cu, FUSEQ); codes and scales are bit-identical to the two-launch form, the workspace is unused.
+static bool fused_decode_ok(const void* x, int64_t ldx, int M, int K) {
+  static const bool enabled = [] {  // developer A/B switch: B2_FUSED_DECODE=0 keeps quantizer + GEMM as two launches
+    const char* e = getenv("B2_FUSED_DECODE");
+    return !(e && e[0] == '0');
+  }();
+  return enabled && M <= 32 && K % 16 == 0 && ldx % 8 == 0 && aligned16(x) &&
+         ((g_forced_config & 0x80000) != 0 || (g_forced_config & 0xff) == 0);
+}
+
+static int linear_fused_decode(GemmFlavor flavor, const char* op, const void* x, int x_dtype, int64_t ldx, const void* W,
+                               int64_t ldw, const float* Bs, const void* bias, int bias_dtype, void* D, int64_t ldd,
+                               int M, int N, int K, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (M < 0 || N <= 0 || K <= 0 || !x || !W || !D || !Bs) return fail(B2_ERR_ARG, "%s: bad arguments", op);
+  if (N % 8 != 0) return fail(B2_ERR_ARG, "%s: out must be multiple of 16 bytes for memory alignment (N=%d must be a multiple of 8)", op, N);
+  if (ldx < K || ldw < K || ldd < N || ldw % 16 != 0 || (ldd * 2) % 16 != 0 || !aligned16(W) || !aligned16(D) || !aligned16(Bs))
+    return fail(B2_ERR_ARG, "%s: strides / alignment", op);
+  if (bias && !aligned16(bias)) return fail(B2_ERR_ARG, "%s: bias must be 16-byte aligned", op);
+  GemmArgs a{};
+  a.A = nullptr; a.lda = K; a.W = W; a.ldw = ldw; a.As = nullptr; a.Bs = Bs; a.bias = bias; a.bias_dtype = bias_dtype;
+  a.D = D; a.ldd = ldd; a.out_dtype = x_dtype; a.M = M; a.N = N; a.K = K;
+  a.x = x; a.ldx = ldx; a.x_dtype = x_dtype;
+  char err[256];
+  int r = gemm_launch(flavor, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err, sizeof(err));
+  if (r) return fail(r, "%s: %s", op, err);
+  return B2_OK;
+}
+
 int b2_linear_w8a8_int8(const void* x, int x_dtype, int64_t ldx, const int8_t* W, int64_t ldw, const float* Bs,
                         const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
                         void* workspace, size_t workspace_bytes, b2_stream_t stream) {
   if (int r = check_act_dtype(x_dtype, "int8_scaled_mm_with_quant: mat1")) return r;
   if (M == 0) return B2_OK;
+  if (fused_decode_ok(x, ldx, M, K))
+    return linear_fused_decode(GEMM_S8, "int8_scaled_mm_with_quant", x, x_dtype, ldx, W, ldw, Bs, bias, bias_dtype, D, ldd,
+                               M, N, K, stream);
   if (!workspace || workspace_bytes < ws_bytes(M, K) || !aligned16(workspace))
     return fail(B2_ERR_ARG, "int8_scaled_mm_with_quant: workspace too small or misaligned (need %zu bytes)", ws_bytes(M, K));
   int8_t* q = static_cast<int8_t*>(workspace);
@@ -547,6 +580,9 @@ int b2_linear_w8a8_fp8(const void* x, int x_dtype, int64_t ldx, const uint8_t* W
                        void* workspace, size_t workspace_bytes, b2_stream_t stream) {
   if (int r = check_act_dtype(x_dtype, "w8a8_fp8 linear: input")) return r;
   if (M == 0) return B2_OK;
+  if (fused_decode_ok(x, ldx, M, K))
+    return linear_fused_decode(GEMM_E4M3, "w8a8_fp8 linear", x, x_dtype, ldx, W, ldw, Bs, bias, bias_dtype, D, ldd, M, N,
+                               K, stream);
   if (!workspace || workspace_bytes < ws_bytes(M, K) || !aligned16(workspace))
     return fail(B2_ERR_ARG, "w8a8_fp8 linear: workspace too small or misaligned (need %zu bytes)", ws_bytes(M, K));
   uint8_t* q = static_cast<uint8_t*>(workspace);

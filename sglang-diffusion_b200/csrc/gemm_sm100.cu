@@ -514,6 +514,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
     snprintf(err, err_len, "multicast push epilogue is built for decode shapes (M <= 128) only");
     return B2_ERR_ARG;
   }
+  if (a.x != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
   if (a.mc_slot != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
   if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert) : ((forced_config & 0xff) == 0 && decode_shape))
     return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);

@@ -22,6 +22,8 @@
 //     the fp32 sums of the fp8 path are deterministic.
 #include <cstdlib>
 
+#include <cuda_fp8.h>
+
 #include "gemm_common.cuh"
 
 namespace b2 {
@@ -47,6 +49,13 @@ struct SplitParams {
   // Row-parallel tensor-parallel layers: instead of D, the epilogue stores this rank's partial output through the
   // NVSwitch multicast mapping into slot `rank` of EVERY rank's gather buffer (multimem.st), set (counter & 1) of two
   // -- the reduction that follows (allreduce_symm.cu, gathered form) then only reads local memory.  nullptr = off.
+  // Fused activation quantizer (M <= 32; b2_linear_w8a8_int8 / _fp8): x is the bf16 / f16 activation matrix; the CTA
+  // quantizes the rows of its own K slice into a RESIDENT shared-memory copy of A (no A loads, no codes round trip
+  // through L2 / HBM, no separate launch) and keeps the row scales in shared memory.  nullptr = A comes by TMA.
+  const void* x;
+  long long ldx;       // elements
+  int x_is_bf16;
+  int a_res_blocks;    // K blocks of resident A per CTA (>= the longest K slice)
   uint8_t* mc_slot;             // multicast address of this rank's slot in set 0
   long long mc_set_bytes;       // distance between the two sets
   const uint32_t* mc_counter;   // device-resident call counter (local signal pad); read after griddepcontrol.wait
@@ -87,7 +96,100 @@ B2_DEVICE uint32_t part_offset(int row, int chunk, uint32_t pitch_bytes) {
   return static_cast<uint32_t>(row) * pitch_bytes + static_cast<uint32_t>((chunk ^ (row & 7)) << 4);
 }
 
+B2_DEVICE float x_to_f32(uint16_t bits, bool bf16) {
+  return bf16 ? __uint_as_float(static_cast<uint32_t>(bits) << 16) : __half2float(__ushort_as_half(bits));
+}
+
+// The activation quantizer of quant.cu inside the GEMM (arithmetic of sgl-kernel/csrc/cpu/vec.h:190-228 for int8,
+// sgl-kernel/csrc/gemm/per_token_quant_fp8.cu:17-121 for e4m3 -- the same IEEE divisions and roundings, so codes and
+// scales are bit-identical to the separate launch).  Called by the 128 epilogue threads.
+//   pass 1  absmax of rows [0, M) over this CTA's K slice, reduced over the S CTAs of the cluster through DSMEM
+//           (every CTA of a cluster owns a different slice of the same rows)
+//   pass 2  re-read the slice (L1 / L2 hits), quantize, store 16-byte chunks into the resident A tiles in the
+//           128-byte-swizzled K-major layout the UMMA descriptor expects (what TMA would have written)
+// `amax_part` = 32 floats of this CTA visible cluster-wide; `smem_as` receives the row scales.
 template <MmaKind KIND>
+B2_DEVICE void fused_quant_phase(const SplitParams& p, uint8_t* smem_a, uint32_t a_stage_bytes, float* amax_part,
+                                 float* smem_as, int kb0, int kb1, int S, int epi_warp, int lane) {
+  const bool bf16 = p.x_is_bf16 != 0;
+  const int L = (kb1 - kb0) * BK;  // elements of K in my slice (K % 16 == 0; the last block may be partial)
+  const int k_begin = kb0 * BK;
+  const int k_len = min(L, p.K - k_begin);
+  const uint16_t* xb = static_cast<const uint16_t*>(p.x);
+  for (int r = epi_warp; r < 32; r += 4) {
+    float m = 0.f;
+    if (r < p.M) {
+      const uint4* row = reinterpret_cast<const uint4*>(xb + static_cast<long long>(r) * p.ldx + k_begin);
+      for (int v = lane; v < k_len / 8; v += 32) {
+        const uint4 raw = __ldg(row + v);
+        const uint16_t* e = reinterpret_cast<const uint16_t*>(&raw);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m = fmaxf(m, fabsf(x_to_f32(e[j], bf16)));
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) amax_part[r] = m;
+  }
+  // every CTA's partial maxima are visible cluster-wide after this barrier (all 192 threads take part, see caller)
+  __syncwarp();
+}
+
+template <MmaKind KIND>
+B2_DEVICE void fused_quant_phase2(const SplitParams& p, uint8_t* smem_a, uint32_t a_stage_bytes, float* amax_part,
+                                  float* smem_as, int kb0, int kb1, int S, int epi_warp, int lane) {
+  const bool bf16 = p.x_is_bf16 != 0;
+  const int k_begin = kb0 * BK;
+  const int k_len = min((kb1 - kb0) * BK, p.K - k_begin);
+  const uint16_t* xb = static_cast<const uint16_t*>(p.x);
+  const uint32_t amax_addr = smem_u32(amax_part);
+  for (int r = epi_warp; r < p.a_box_rows; r += 4) {
+    float amax = 0.f;
+    if (r < p.M) {
+      if (S > 1) {
+        for (int c = 0; c < S; ++c) amax = fmaxf(amax, __uint_as_float(ld_dsmem_u32(amax_addr + r * 4, c)));
+      } else {
+        amax = amax_part[r];
+      }
+    }
+    float scale, inv;
+    if constexpr (KIND == MmaKind::I8) {
+      amax = fmaxf(amax, 1e-7f);
+      scale = __fdiv_rn(amax, 127.f);
+      inv = __fdiv_rn(127.f, amax);
+    } else {
+      scale = __fdiv_rn(amax, 448.f);
+      inv = (scale == 0.f) ? 0.f : __frcp_rn(scale);
+    }
+    if (lane == 0 && r < p.M) smem_as[r] = scale;
+    const uint4* row = reinterpret_cast<const uint4*>(xb + static_cast<long long>(r < p.M ? r : 0) * p.ldx + k_begin);
+    uint8_t* a_row = smem_a + (r >> 3) * 1024 + (r & 7) * 128;
+    for (int c = lane; c < k_len / 16; c += 32) {  // one 16-byte chunk of codes = 16 elements = two 16-byte loads
+      uint4 out = make_uint4(0, 0, 0, 0);
+      if (r < p.M) {
+        const uint4 r0 = __ldg(row + 2 * c), r1 = __ldg(row + 2 * c + 1);
+        const uint16_t* e0 = reinterpret_cast<const uint16_t*>(&r0);
+        const uint16_t* e1 = reinterpret_cast<const uint16_t*>(&r1);
+        uint8_t* o = reinterpret_cast<uint8_t*>(&out);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float a = __fmul_rn(x_to_f32(e0[j], bf16), inv), b = __fmul_rn(x_to_f32(e1[j], bf16), inv);
+          if constexpr (KIND == MmaKind::I8) {
+            o[j] = static_cast<uint8_t>(static_cast<int8_t>(__float2int_rn(a)));
+            o[8 + j] = static_cast<uint8_t>(static_cast<int8_t>(__float2int_rn(b)));
+          } else {
+            o[j] = static_cast<uint8_t>(__nv_cvt_float_to_fp8(fmaxf(fminf(a, 448.f), -448.f), __NV_SATFINITE, __NV_E4M3));
+            o[8 + j] = static_cast<uint8_t>(__nv_cvt_float_to_fp8(fmaxf(fminf(b, 448.f), -448.f), __NV_SATFINITE, __NV_E4M3));
+          }
+        }
+      }
+      const int kbl = c >> 3, c16 = c & 7;  // K block inside the slice, chunk inside its 128-byte row
+      *reinterpret_cast<uint4*>(a_row + static_cast<size_t>(kbl) * a_stage_bytes + ((c16 ^ (r & 7)) << 4)) = out;
+    }
+  }
+}
+
+template <MmaKind KIND, bool FUSEQ>
 __global__ void __launch_bounds__(NUM_THREADS)
     gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                        const SplitParams p) {
@@ -101,7 +203,7 @@ __global__ void __launch_bounds__(NUM_THREADS)
   const int stages = p.stages;
   const uint32_t a_stage_bytes = static_cast<uint32_t>(p.a_box_rows) * BK;
   uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem_a + static_cast<size_t>(stages) * a_stage_bytes;
+  uint8_t* smem_b = smem_a + static_cast<size_t>(FUSEQ ? p.a_res_blocks : stages) * a_stage_bytes;
   uint32_t* part = reinterpret_cast<uint32_t*>(smem);  // aliases the operand ring once every MMA has retired
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
@@ -117,12 +219,14 @@ __global__ void __launch_bounds__(NUM_THREADS)
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.bar_offset);
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* acc_full = empty_bar + stages;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(acc_full + 1);
+  uint64_t* a_ready = acc_full + 1;  // FUSEQ: the 128 epilogue threads have written the resident A tiles
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(a_ready + 1);
   float* smem_as = reinterpret_cast<float*>(smem + p.bar_offset + 512);  // As[0..M) staged by the epilogue warps
+  float* amax_part = smem_as + 64;  // FUSEQ (M <= 32): this CTA's partial row maxima, read by the cluster
 
   // Warp 0 initialises the barriers and puts the first ring of loads in flight BEFORE the block-wide sync: the
   // TMEM allocation and the sync are off the critical path of the first HBM round trip.
-  const uint32_t tx_bytes = a_stage_bytes + B_STAGE_BYTES;
+  const uint32_t tx_bytes = (FUSEQ ? 0u : a_stage_bytes) + B_STAGE_BYTES;
   const int first_pass = min(stages, kb1 - kb0);
   if (warp == 0) {
     if (lane == 0) {
@@ -133,6 +237,7 @@ __global__ void __launch_bounds__(NUM_THREADS)
         mbar_init(&empty_bar[i], 1);
       }
       mbar_init(acc_full, 1);
+      mbar_init(a_ready, 128);
       fence_mbar_init();
       // The weights are touched exactly once (evict-first) and -- when the caller has declared them static
       // (b2_set_weight_prefetch) -- are requested before the preceding kernel of the stream has finished; the
@@ -143,10 +248,12 @@ __global__ void __launch_bounds__(NUM_THREADS)
         tma_load_2d(smem_b + static_cast<size_t>(i) * B_STAGE_BYTES, &tmap_b, &full_bar[i], (kb0 + i) * BK, tile * BN,
                     kEvictFirst);
       }
-      pdl_wait_prior_grids();
-      for (int i = 0; i < first_pass; ++i)
-        tma_load_2d(smem_a + static_cast<size_t>(i) * a_stage_bytes, &tmap_a, &full_bar[i], (kb0 + i) * BK, 0,
-                    kEvictLast);
+      if constexpr (!FUSEQ) {
+        pdl_wait_prior_grids();
+        for (int i = 0; i < first_pass; ++i)
+          tma_load_2d(smem_a + static_cast<size_t>(i) * a_stage_bytes, &tmap_a, &full_bar[i], (kb0 + i) * BK, 0,
+                      kEvictLast);
+      }
       pdl_launch_dependents();
     }
     __syncwarp();
@@ -156,6 +263,26 @@ __global__ void __launch_bounds__(NUM_THREADS)
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
+
+  if constexpr (FUSEQ) {
+    // quantize my K slice of the activations into the resident A tiles while the first ring of weight tiles is in
+    // flight (see fused_quant_phase); the cluster barrier in the middle carries the partial row maxima
+    if (warp >= EPI_WARP0) {
+      pdl_wait_prior_grids();  // x is the output of the preceding kernel
+      fused_quant_phase<KIND>(p, smem_a, a_stage_bytes, amax_part, smem_as, kb0, kb1, S, warp - EPI_WARP0, lane);
+    }
+    if (S > 1) {
+      __syncwarp();
+      cluster_sync_all();
+    } else {
+      __syncthreads();
+    }
+    if (warp >= EPI_WARP0) {
+      fused_quant_phase2<KIND>(p, smem_a, a_stage_bytes, amax_part, smem_as, kb0, kb1, S, warp - EPI_WARP0, lane);
+      fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+      mbar_arrive(a_ready);
+    }
+  }
 
   // column slice of the tile this CTA reduces and writes (work item = row x group of 4 columns)
   const int epi_tid = (warp - EPI_WARP0) * 32 + lane;
@@ -179,8 +306,9 @@ __global__ void __launch_bounds__(NUM_THREADS)
         mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
         tma_load_2d(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES, &tmap_b, &full_bar[stage], kb * BK,
                     tile * BN, kEvictFirst);
-        tma_load_2d(smem_a + static_cast<size_t>(stage) * a_stage_bytes, &tmap_a, &full_bar[stage], kb * BK, 0,
-                    kEvictLast);
+        if constexpr (!FUSEQ)
+          tma_load_2d(smem_a + static_cast<size_t>(stage) * a_stage_bytes, &tmap_a, &full_bar[stage], kb * BK, 0,
+                      kEvictLast);
       }
       __syncwarp();
       if (++stage == stages) {
@@ -193,10 +321,12 @@ __global__ void __launch_bounds__(NUM_THREADS)
     const uint32_t idesc = make_idesc<KIND>(BM, static_cast<uint32_t>(BN));
     int stage = 0;
     uint32_t phase = 0;
+    if constexpr (FUSEQ) mbar_wait(a_ready, 0);
     for (int kb = kb0; kb < kb1; ++kb) {
       mbar_wait(&full_bar[stage], phase);
       tc_fence_after_sync();
-      const uint64_t da = make_smem_desc_sw128(smem_u32(smem_a + static_cast<size_t>(stage) * a_stage_bytes));
+      const uint64_t da = make_smem_desc_sw128(
+          smem_u32(smem_a + static_cast<size_t>(FUSEQ ? kb - kb0 : stage) * a_stage_bytes));
       const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES));
       if (elect_one()) {
 #pragma unroll
@@ -219,7 +349,7 @@ __global__ void __launch_bounds__(NUM_THREADS)
     pdl_wait_prior_grids();  // As below and D at the end belong to / may still be read by the preceding kernels
     {
       const int t = (warp - EPI_WARP0) * 32 + lane;
-      if (t < p.M && p.As != nullptr) smem_as[t] = __ldg(p.As + t);
+      if (!FUSEQ && t < p.M && p.As != nullptr) smem_as[t] = __ldg(p.As + t);
     }
     // per-column scale / bias of this thread's column group: fetched while the main loop runs
     if (fixed_group && !raw_out && epi_tid < p.M * gpr) {
@@ -331,10 +461,12 @@ struct SplitPlan {
   size_t smem;
 };
 
-static size_t splitk_smem(int bn, int a_rows, int stages) {
+// a_res > 0: the fused-quantizer layout -- `a_res` resident A tiles in front of a ring of weight stages only
+static size_t splitk_smem(int bn, int a_rows, int stages, int a_res = 0) {
   const size_t a_stage = static_cast<size_t>(a_rows) * BK, b_stage = static_cast<size_t>(bn) * BK;
-  size_t data = stages * (a_stage + b_stage);
-  const size_t mma_reach = stages * a_stage + static_cast<size_t>(BM) * BK;  // 128-row reads of the last A stage
+  size_t data = a_res > 0 ? a_res * a_stage + stages * b_stage : stages * (a_stage + b_stage);
+  // 128-row reads of the last A tile
+  const size_t mma_reach = (a_res > 0 ? (a_res - 1) * a_stage : stages * a_stage) + static_cast<size_t>(BM) * BK;
   if (mma_reach > data) data = mma_reach;
   const size_t rows_p = static_cast<size_t>((a_rows + 31) / 32) * 32;
   const size_t partial = rows_p * static_cast<size_t>((bn + 31) / 32 * 32) * 4;
@@ -343,20 +475,20 @@ static size_t splitk_smem(int bn, int a_rows, int stages) {
   return data + 1024;  // 512 B of barriers + TMEM pointer (2 * 24 + 2 slots of 8 bytes max), 512 B of staged As
 }
 
-static int deepest_ring(int bn, int a_rows, int kb_per) {
+static int deepest_ring(int bn, int a_rows, int kb_per, int a_res = 0) {
   int stages = kb_per < 24 ? kb_per : 24;
-  while (stages > 1 && splitk_smem(bn, a_rows, stages) > static_cast<size_t>(SMEM_LIMIT)) --stages;
+  while (stages > 1 && splitk_smem(bn, a_rows, stages, a_res) > static_cast<size_t>(SMEM_LIMIT)) --stages;
   return stages;
 }
 
-template <MmaKind KIND>
+template <MmaKind KIND, bool FUSEQ>
 static void configure_kernel(char* err, size_t err_len, int* status) {
   static thread_local int attr_dev = -1;
   int dev = 0;
   cudaGetDevice(&dev);
   if (attr_dev == dev) return;
   cudaError_t e =
-      cudaFuncSetAttribute(gemm_splitk_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+      cudaFuncSetAttribute(gemm_splitk_kernel<KIND, FUSEQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
   if (e != cudaSuccess) {
     snprintf(err, err_len, "cudaFuncSetAttribute(max dynamic smem): %s", cudaGetErrorString(e));
     *status = B2_ERR_CUDA;
@@ -376,7 +508,7 @@ static void configure_kernel(char* err, size_t err_len, int* status) {
 // the wide layer and 1.5x slower on the narrow ones: a CTA that owns a whole SM's shared memory leaves no room for
 // the programmatically launched successor, so nothing hides the ~4 us launch / first-round-trip / drain cost.  The
 // kernel keeps the run-time tile width (any multiple of 16) for shapes whose N is not a multiple of 128.
-static SplitPlan plan_splitk(int N, int K, int a_rows) {
+static SplitPlan plan_splitk(int N, int K, int a_rows, bool fuseq = false) {
   const int sms = device_sm_count();
   const int num_kb = (K + BK - 1) / BK;
   int bn = a_rows <= 32 ? 128 : 64;
@@ -389,24 +521,25 @@ static SplitPlan plan_splitk(int N, int K, int a_rows) {
   int s = 1;
   while (s < 8 && tiles * s < target && num_kb / (2 * s) >= 4) s *= 2;
   const int kb_per = (num_kb + s - 1) / s;
+  const int a_res = fuseq ? kb_per : 0;
   const long ctas = static_cast<long>(tiles) * s;
   const int need_occ = static_cast<int>((ctas + sms - 1) / sms);
   int stages = 4;
   if (need_occ <= 3) {
     const size_t budget = (228u * 1024u) / need_occ - 1024u;
     stages = 12;
-    while (stages > 2 && splitk_smem(bn, a_rows, stages) > budget) --stages;
+    while (stages > 2 && splitk_smem(bn, a_rows, stages, a_res) > budget) --stages;
   }
   if (stages > kb_per) stages = kb_per;
-  while (stages > 1 && splitk_smem(bn, a_rows, stages) > static_cast<size_t>(SMEM_LIMIT)) --stages;
-  return SplitPlan{bn, s, stages, splitk_smem(bn, a_rows, stages)};
+  while (stages > 1 && splitk_smem(bn, a_rows, stages, a_res) > static_cast<size_t>(SMEM_LIMIT)) --stages;
+  return SplitPlan{bn, s, stages, splitk_smem(bn, a_rows, stages, a_res)};
 }
 
-template <MmaKind KIND>
+template <MmaKind KIND, bool FUSEQ>
 static int launch_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const SplitParams& p, int grid, size_t smem,
                          bool pdl, cudaStream_t st, char* err, size_t err_len) {
   int status = B2_OK;
-  configure_kernel<KIND>(err, err_len, &status);
+  configure_kernel<KIND, FUSEQ>(err, err_len, &status);
   if (status != B2_OK) return status;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(static_cast<unsigned>(grid));
@@ -422,7 +555,7 @@ static int launch_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const Spl
   attrs[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = pdl ? 2 : 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_splitk_kernel<KIND>, ta, tb, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_splitk_kernel<KIND, FUSEQ>, ta, tb, p);
   if (e != cudaSuccess) {
     snprintf(err, err_len, "split-K gemm kernel launch (cluster %d, smem %zu): %s", p.split, smem,
              cudaGetErrorString(e));
@@ -437,17 +570,19 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
                        char* err, size_t err_len) {
   const int a_rows = ((a.M + 7) / 8) * 8;
   const int num_kb = (a.K + BK - 1) / BK;
+  const bool fuseq = a.x != nullptr;  // activations arrive as bf16 / f16 and are quantized inside the kernel
   SplitPlan plan;
   if (forced & 0x80000) {
     plan.bn = ((forced & 15) + 1) * 16;
     plan.split = ((forced >> 4) & 7) + 1;
     if (plan.split > num_kb) plan.split = num_kb;
-    plan.stages = deepest_ring(plan.bn, a_rows, (num_kb + plan.split - 1) / plan.split);
+    const int kb_per_f = (num_kb + plan.split - 1) / plan.split;
+    plan.stages = deepest_ring(plan.bn, a_rows, kb_per_f, fuseq ? kb_per_f : 0);
     const int cap = (forced >> 8) & 31;  // developer sweeps: ring depth cap in bits 8-12
     if (cap >= 1 && cap < plan.stages) plan.stages = cap;
-    plan.smem = splitk_smem(plan.bn, a_rows, plan.stages);
+    plan.smem = splitk_smem(plan.bn, a_rows, plan.stages, fuseq ? kb_per_f : 0);
   } else {
-    plan = plan_splitk(a.N, a.K, a_rows);
+    plan = plan_splitk(a.N, a.K, a_rows, fuseq);
   }
   const int bn = plan.bn;
   if (plan.smem > static_cast<size_t>(SMEM_LIMIT)) {
@@ -455,7 +590,7 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
     return B2_ERR_ARG;
   }
   static thread_local char name[64];
-  snprintf(name, sizeof(name), "splitk_%dx%d_s%d_st%d", a_rows, bn, plan.split, plan.stages);
+  snprintf(name, sizeof(name), "splitk_%dx%d_s%d_st%d%s", a_rows, bn, plan.split, plan.stages, fuseq ? "_fusedq" : "");
   if (used_config) *used_config = name;
 
   SplitParams p;
@@ -478,13 +613,18 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
   while (p.tmem_cols < static_cast<uint32_t>(bn)) p.tmem_cols *= 2;
   p.part_pitch = static_cast<uint32_t>((bn + 31) / 32 * 32) * 4u;
   p.bar_offset = static_cast<uint32_t>(plan.smem - 1024);
+  p.x = a.x;
+  p.ldx = a.ldx;
+  p.x_is_bf16 = a.x_dtype == B2_DTYPE_BF16;
+  p.a_res_blocks = fuseq ? (num_kb + plan.split - 1) / plan.split : 0;
   p.mc_slot = static_cast<uint8_t*>(a.mc_slot);
   p.mc_set_bytes = a.mc_set_bytes;
   p.mc_counter = a.mc_counter;
 
   CUtensorMap ta, tb;
-  if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, a_rows, BK) ||
-      !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, bn, BK)) {
+  if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, bn, BK) ||
+      (fuseq ? (ta = tb, false)  // no A loads in the fused form: the parameter slot carries a valid (unused) map
+             : !make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, a_rows, BK))) {
     snprintf(err, err_len, "cuTensorMapEncodeTiled failed (M=%d N=%d K=%d lda=%lld ldw=%lld)", a.M, a.N, a.K,
              (long long)a.lda, (long long)a.ldw);
     return B2_ERR_CUDA;
@@ -492,8 +632,12 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
   const int tiles = (a.N + bn - 1) / bn;
   const int grid = tiles * plan.split;
   const bool pdl = weight_prefetch_enabled();
-  if (flavor == GEMM_S8) return launch_splitk<MmaKind::I8>(ta, tb, p, grid, plan.smem, pdl, st, err, err_len);
-  return launch_splitk<MmaKind::F8>(ta, tb, p, grid, plan.smem, pdl, st, err, err_len);
+  if (fuseq) {
+    if (flavor == GEMM_S8) return launch_splitk<MmaKind::I8, true>(ta, tb, p, grid, plan.smem, pdl, st, err, err_len);
+    return launch_splitk<MmaKind::F8, true>(ta, tb, p, grid, plan.smem, pdl, st, err, err_len);
+  }
+  if (flavor == GEMM_S8) return launch_splitk<MmaKind::I8, false>(ta, tb, p, grid, plan.smem, pdl, st, err, err_len);
+  return launch_splitk<MmaKind::F8, false>(ta, tb, p, grid, plan.smem, pdl, st, err, err_len);
 }
 
 }  // namespace b2

@@ -761,10 +761,80 @@ def test_ops_are_cuda_graph_capturable_and_use_the_current_stream():
 
 
 def test_launch_counter_counts_our_kernels():
-    x, W, Bs, b = mk_int8_problem(8, 64, 128, seed=2)
+    x, W, Bs, b = mk_int8_problem(64, 64, 128, seed=2)
     capi.reset_launch_count()
     b2.int8_scaled_mm_with_quant(x.to(DEV), W.to(DEV), Bs.to(DEV), None, torch.bfloat16, False)
     assert capi.launch_count() == 2  # quantizer + GEMM
+    capi.reset_launch_count()
+    b2.int8_scaled_mm_with_quant(x[:8].to(DEV), W.to(DEV), Bs.to(DEV), None, torch.bfloat16, False)
+    assert capi.launch_count() == 1  # M <= 32: the decode GEMM quantizes its activations itself
+    assert capi.last_gemm_config().endswith("_fusedq")
+
+
+@pytest.mark.parametrize("M", [1, 2, 5, 8, 16, 17, 31, 32])
+@pytest.mark.parametrize("K,N", [(4096, 6144), (4096, 28672), (14336, 4096), (544, 384), (16, 8), (2048, 1000)])
+@pytest.mark.parametrize("has_bias", [False, True])
+def test_fused_quant_decode_linear_bitwise_vs_oracle(M, K, N, has_bias):
+    """M <= 32: ONE kernel (cluster split-K GEMM whose epilogue warps first quantize the CTA's K slice of the bf16
+    activations into the resident A tiles, row maxima exchanged over DSMEM).  Output == oracle bit for bit == the
+    two-launch form (B2_FUSED_DECODE=0 equivalent: separate quantizer + GEMM)."""
+    x, W, Bs, b = mk_int8_problem(M, N, K, seed=M + K + N, bias=has_bias)
+    x[0, ::7] *= 30  # outliers: the row maximum sits in ONE K slice, the others must learn it through the cluster
+    ref = restate.int8_scaled_mm_with_quant(x, W, Bs, b.float() if has_bias else None)
+    bd = b.to(DEV) if has_bias else None
+    with capi.static_weights():
+        out = b2.int8_scaled_mm_with_quant(x.to(DEV), W.to(DEV), Bs.to(DEV), bd, torch.bfloat16, False)
+    assert capi.last_gemm_config().endswith("_fusedq"), capi.last_gemm_config()
+    assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref))
+    q, s = b2.per_token_quant_int8(x.to(DEV))
+    two = b2.int8_scaled_mm(q, W.to(DEV).t(), s, Bs.to(DEV).view(-1, 1), torch.bfloat16, bd)
+    assert torch.equal(bf16_bits(out.cpu()), bf16_bits(two.cpu()))
+
+
+@pytest.mark.parametrize("bn,split", [(32, 1), (64, 2), (128, 4), (128, 8), (256, 3), (48, 5)])
+def test_fused_quant_decode_forced_plans_and_strided_input(bn, split):
+    M, N, K = 16, 1000, 4096
+    x, W, Bs, b = mk_int8_problem(M, N, K, seed=bn + split)
+    ref = restate.int8_scaled_mm_with_quant(x, W, Bs, b.float())
+    xs = torch.zeros(M, K + 64, dtype=torch.bfloat16, device=DEV)  # row stride != K
+    xs[:, :K] = x.to(DEV)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    Wd, Bsd, bd = W.to(DEV), Bs.to(DEV), b.to(DEV)
+    capi.set_gemm_config(splitk_cfg(0, split, bn))
+    try:
+        st = capi.lib.b2_linear_w8a8_int8(xs.data_ptr(), capi.DTYPE_BF16, K + 64, Wd.data_ptr(), K, Bsd.data_ptr(),
+                                          bd.data_ptr(), capi.DTYPE_BF16, out.data_ptr(), N, M, N, K, None, 0, _stream())
+    finally:
+        capi.set_gemm_config(0)
+    capi.check(st)
+    assert capi.last_gemm_config().endswith("_fusedq")
+    assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref))
+
+
+@pytest.mark.parametrize("M", [1, 16, 32])
+@pytest.mark.parametrize("K,N", [(8192, 1280), (1024, 8192), (3584, 8192)])
+def test_fused_quant_decode_fp8_linear(M, K, N):
+    """fp8 twin (b2_linear_w8a8_fp8): e4m3 codes are bit-identical to sgl_per_token_quant_fp8's, so the fused kernel
+    equals the two-launch form bit for bit when both take the same split-K plan (same fp32 summation order)."""
+    from conftest import mk_fp8_weight
+
+    g = torch.Generator().manual_seed(M + K)
+    x = (torch.randn(M, K, generator=g) / 10).bfloat16().to(DEV)
+    Wq, ws = mk_fp8_weight(N, K)
+    Wd, wsd = Wq.to(DEV), ws.to(DEV).view(-1).contiguous()
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    capi.check(capi.lib.b2_linear_w8a8_fp8(x.data_ptr(), capi.DTYPE_BF16, K, Wd.data_ptr(), K, wsd.data_ptr(), None, 0,
+                                           out.data_ptr(), N, M, N, K, None, 0, _stream()))
+    cfg = capi.last_gemm_config()
+    assert cfg.endswith("_fusedq")
+    q, s = b2.sglang_per_token_quant_fp8(x)
+    two = b2.fp8_scaled_mm(q, Wd.t(), s, wsd.view(-1, 1), torch.bfloat16, None)
+    if capi.last_gemm_config() + "_fusedq" == cfg:
+        assert torch.equal(bf16_bits(out.cpu()), bf16_bits(two.cpu()))
+    q_ref, s_ref = restate.per_token_quant_fp8(x.cpu())
+    ref = restate.fp8_scaled_mm(q_ref, Wq.view(torch.uint8), s_ref, ws, None)
+    o = out.float().cpu()
+    assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 1e-6 * ref.abs().max())
 
 
 # ====================================================== host-buffer pipeline ====

@@ -53,7 +53,8 @@ class W8A8Int8LinearMethod:
         # layer.weight is a loaded parameter, never the output of the kernel before the GEMM: decode-shape GEMMs
         # may fetch it under the quantizer's tail (b2_set_weight_prefetch, include/b200_w8a8.h)
         with capi.static_weights():
-            if self.fused:
+            if self.fused or (x.is_cuda and x.numel() // x.shape[-1] <= 32 and x.is_contiguous()):
+                # decode shapes (M <= 32) always take the single entry: the library runs it as ONE kernel
                 x2d = x.view(-1, x.shape[-1])
                 out = ops.int8_scaled_mm_with_quant(x2d, layer.weight.t(), layer.weight_scale, bias, x.dtype, False)
                 return out.view(*x.shape[:-1], layer.weight.shape[1])
@@ -80,6 +81,9 @@ def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: to
     if input_scale is not None:
         assert input_scale.numel() == 1
         qinput, x_scale = ops.static_quant_fp8(input_2d.contiguous(), input_scale, repeat_scale=True)
+    elif input_2d.is_cuda and input_2d.shape[0] <= 32 and input_2d.is_contiguous() and weight.stride(0) == 1:
+        # decode shapes: one kernel (b2_linear_w8a8_fp8: the split-K GEMM quantizes its own activations)
+        return ops.fp8_linear_fused(input_2d, weight, weight_scale, bias).view(*output_shape)
     else:
         qinput, x_scale = ops.sglang_per_token_quant_fp8(input_2d)
     output = ops.fp8_scaled_mm(qinput, weight, x_scale, weight_scale, out_dtype=input.dtype, bias=bias)

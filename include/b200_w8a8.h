@@ -209,6 +209,14 @@ int b2_linear_w8a8_int8(const void* x, int x_dtype, int64_t ldx, const int8_t* W
                         const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
                         void* workspace, size_t workspace_bytes, b2_stream_t stream);
 
+/* One-kernel form of the two entries above for M <= 32 (calling thread; default 0 = off, or B2_FUSED_DECODE=1 in the
+ * environment): the cluster split-K decode GEMM quantizes its own K slice of the activations into resident
+ * shared-memory A tiles (row maxima exchanged over DSMEM) -- no quantizer launch, no codes round trip, workspace
+ * unused; results bit-identical.  Measured SLOWER than the two programmatically chained launches on every decode
+ * shape, hence off by default. */
+void b2_set_fused_decode(int enabled);
+int b2_get_fused_decode(void);
+
 /* Same composition for per-token fp8 (W8A8Fp8LinearMethod.apply ->
  * apply_fp8_linear, python/sglang/srt/layers/quantization/fp8_utils.py:1194-1276). */
 size_t b2_linear_w8a8_fp8_workspace(int M, int K);

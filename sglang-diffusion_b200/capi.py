@@ -29,6 +29,7 @@ SYMBOLS = [
     "b2_quant_int8_rows_sum", "b2_quant_fp8_tensor", "b2_silu_mul_quant", "b2_rmsnorm_quant",
     "b2_quant_fp8_group128_v2", "b2_bmm_e4m3_workspace", "b2_bmm_e4m3",
     "b2_set_allreduce_timeout_ms", "b2_get_allreduce_timeout_ms",
+    "b2_set_fused_decode", "b2_get_fused_decode",
     "b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered",
     "b2_moe_max_padded", "b2_moe_align_block128", "b2_quant_int8_rows_gather", "b2_gemm_s8_grouped", "b2_moe_combine",
 ]
@@ -149,6 +150,27 @@ def set_weight_prefetch(enabled: bool) -> None:
     """b2_set_weight_prefetch: promise that W operands are static (not written by the preceding kernel), so that
     decode-shape GEMMs launch programmatically and fetch weights under the tail of the preceding kernel."""
     lib.b2_set_weight_prefetch(1 if enabled else 0)
+
+
+lib.b2_set_fused_decode.argtypes = [_i]
+lib.b2_set_fused_decode.restype = None
+lib.b2_get_fused_decode.restype = _i
+
+
+class fused_decode:
+    """`with capi.fused_decode(): ...` -- M <= 32 linears run as ONE kernel (b2_set_fused_decode; off by default)."""
+
+    def __init__(self, enabled: bool = True):
+        self._on = 1 if enabled else 0
+
+    def __enter__(self):
+        self._prev = int(lib.b2_get_fused_decode())
+        lib.b2_set_fused_decode(self._on)
+        return self
+
+    def __exit__(self, *exc):
+        lib.b2_set_fused_decode(self._prev)
+        return False
 
 
 class static_weights:

@@ -140,6 +140,8 @@ void b2_set_gemm_config(int config_id) { g_forced_config = config_id; }
 const char* b2_last_gemm_config(void) { return g_last_config; }
 void b2_set_profile_buffer(void* device_buffer) { g_prof = device_buffer; }
 void b2_set_weight_prefetch(int enabled) { g_weight_prefetch = enabled; }
+void b2_set_fused_decode(int enabled);
+int b2_get_fused_decode(void);
 int b2_get_weight_prefetch(void) { return g_weight_prefetch; }
 
 int b2_quant_int8_rows(const void* x, int x_dtype, int64_t ldx, int8_t* q, int64_t ldq, float* s, int M, int K,
@@ -529,11 +531,18 @@ size_t b2_linear_w8a8_fp8_workspace(int M, int K) { return ws_bytes(M, K); }
 
 // M <= 32: ONE kernel -- the split-K decode GEMM quantizes its own K slice of the activations into shared memory
 // (gemm_splitk_sm100.cu, FUSEQ); codes and scales are bit-identical to the two-launch form, the workspace is unused.
+// OFF by default: measured slower than the two programmatically chained launches on every decode shape
+// (profiles/r02k_decode_fused_ab.log: M = 16 gate_up 35.8 vs 24.1 us, qkv 14.2 vs 9.0 us, even M = 1 10.0 vs 8.4 us) --
+// the separate quantizer already runs under the GEMM's first weight round trip, while the fused form serialises two
+// L2 passes over the activations in front of the first MMA in EVERY CTA and gives up ring depth for the resident A.
+// b2_set_fused_decode(1) (or B2_FUSED_DECODE=1 in the environment) turns it on.
+static thread_local int g_fused_decode = [] {
+  const char* e = getenv("B2_FUSED_DECODE");
+  return (e && e[0] == '1') ? 1 : 0;
+}();
+
 static bool fused_decode_ok(const void* x, int64_t ldx, int M, int K) {
-  static const bool enabled = [] {  // developer A/B switch: B2_FUSED_DECODE=0 keeps quantizer + GEMM as two launches
-    const char* e = getenv("B2_FUSED_DECODE");
-    return !(e && e[0] == '0');
-  }();
+  const bool enabled = g_fused_decode != 0;
   return enabled && M <= 32 && K % 16 == 0 && ldx % 8 == 0 && aligned16(x) &&
          ((g_forced_config & 0x80000) != 0 || (g_forced_config & 0xff) == 0);
 }
@@ -556,6 +565,9 @@ static int linear_fused_decode(GemmFlavor flavor, const char* op, const void* x,
   if (r) return fail(r, "%s: %s", op, err);
   return B2_OK;
 }
+
+void b2_set_fused_decode(int enabled) { g_fused_decode = enabled; }
+int b2_get_fused_decode(void) { return g_fused_decode; }
 
 int b2_linear_w8a8_int8(const void* x, int x_dtype, int64_t ldx, const int8_t* W, int64_t ldw, const float* Bs,
                         const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,

@@ -120,11 +120,17 @@ B2_DEVICE void fused_quant_phase(const SplitParams& p, uint8_t* smem_a, uint32_t
     float m = 0.f;
     if (r < p.M) {
       const uint4* row = reinterpret_cast<const uint4*>(xb + static_cast<long long>(r) * p.ldx + k_begin);
-      for (int v = lane; v < k_len / 8; v += 32) {
-        const uint4 raw = __ldg(row + v);
-        const uint16_t* e = reinterpret_cast<const uint16_t*>(&raw);
+      const int nv = k_len / 8;
+      for (int v0 = lane; v0 < nv; v0 += 32 * 8) {  // eight independent 16-byte loads in flight per thread
+        uint4 raw[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) m = fmaxf(m, fabsf(x_to_f32(e[j], bf16)));
+        for (int u = 0; u < 8; ++u) raw[u] = v0 + 32 * u < nv ? __ldg(row + v0 + 32 * u) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const uint16_t* e = reinterpret_cast<const uint16_t*>(&raw[u]);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) m = fmaxf(m, fabsf(x_to_f32(e[j], bf16)));
+        }
       }
     }
 #pragma unroll
@@ -164,10 +170,22 @@ B2_DEVICE void fused_quant_phase2(const SplitParams& p, uint8_t* smem_a, uint32_
     if (lane == 0 && r < p.M) smem_as[r] = scale;
     const uint4* row = reinterpret_cast<const uint4*>(xb + static_cast<long long>(r < p.M ? r : 0) * p.ldx + k_begin);
     uint8_t* a_row = smem_a + (r >> 3) * 1024 + (r & 7) * 128;
-    for (int c = lane; c < k_len / 16; c += 32) {  // one 16-byte chunk of codes = 16 elements = two 16-byte loads
+    const int nc = k_len / 16;
+    for (int c0 = lane; c0 < nc; c0 += 32 * 4) {  // four chunks (eight 16-byte loads) in flight per thread
+      uint4 ra[4], rb[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const bool on = r < p.M && c0 + 32 * u < nc;
+        ra[u] = on ? __ldg(row + 2 * (c0 + 32 * u)) : make_uint4(0, 0, 0, 0);
+        rb[u] = on ? __ldg(row + 2 * (c0 + 32 * u) + 1) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+      const int c = c0 + 32 * u;
+      if (c >= nc) break;
       uint4 out = make_uint4(0, 0, 0, 0);
       if (r < p.M) {
-        const uint4 r0 = __ldg(row + 2 * c), r1 = __ldg(row + 2 * c + 1);
+        const uint4 r0 = ra[u], r1 = rb[u];
         const uint16_t* e0 = reinterpret_cast<const uint16_t*>(&r0);
         const uint16_t* e1 = reinterpret_cast<const uint16_t*>(&r1);
         uint8_t* o = reinterpret_cast<uint8_t*>(&out);
@@ -185,6 +203,7 @@ B2_DEVICE void fused_quant_phase2(const SplitParams& p, uint8_t* smem_a, uint32_
       }
       const int kbl = c >> 3, c16 = c & 7;  // K block inside the slice, chunk inside its 128-byte row
       *reinterpret_cast<uint4*>(a_row + static_cast<size_t>(kbl) * a_stage_bytes + ((c16 ^ (r & 7)) << 4)) = out;
+      }
     }
   }
 }

@@ -54,7 +54,7 @@ class W8A8Int8LinearMethod:
         # may fetch it under the quantizer's tail (b2_set_weight_prefetch, include/b200_w8a8.h)
         with capi.static_weights():
             if self.fused or (x.is_cuda and x.numel() // x.shape[-1] <= 32 and x.is_contiguous()):
-                # decode shapes (M <= 32) always take the single entry: the library runs it as ONE kernel
+                # decode shapes (M <= 32) always take the single entry (quantizer + GEMM chained inside the library)
                 x2d = x.view(-1, x.shape[-1])
                 out = ops.int8_scaled_mm_with_quant(x2d, layer.weight.t(), layer.weight_scale, bias, x.dtype, False)
                 return out.view(*x.shape[:-1], layer.weight.shape[1])
@@ -82,7 +82,7 @@ def apply_fp8_linear(input: torch.Tensor, weight: torch.Tensor, weight_scale: to
         assert input_scale.numel() == 1
         qinput, x_scale = ops.static_quant_fp8(input_2d.contiguous(), input_scale, repeat_scale=True)
     elif input_2d.is_cuda and input_2d.shape[0] <= 32 and input_2d.is_contiguous() and weight.stride(0) == 1:
-        # decode shapes: one kernel (b2_linear_w8a8_fp8: the split-K GEMM quantizes its own activations)
+        # decode shapes: the single C-ABI entry (b2_linear_w8a8_fp8: quantizer + GEMM chained inside the library)
         return ops.fp8_linear_fused(input_2d, weight, weight_scale, bias).view(*output_shape)
     else:
         qinput, x_scale = ops.sglang_per_token_quant_fp8(input_2d)

@@ -86,8 +86,8 @@ def fp8_blockwise_scaled_mm_bias(mat_a, mat_b, scales_a, scales_b, out_dtype, bi
 
 def fp8_linear_fused(x: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor, bias=None) -> torch.Tensor:
     """W8A8-fp8 linear with dynamic per-token activation scales in ONE call of the C ABI (b2_linear_w8a8_fp8): x [M,K]
-    bf16/f16, weight [K,N] e4m3 with stride(0) == 1 (the linear method's layout), weight_scale [N(,1)].  For M <= 32 the
-    library runs it as one kernel; larger M needs the workspace and takes quantizer + GEMM."""
+    bf16/f16, weight [K,N] e4m3 with stride(0) == 1 (the linear method's layout), weight_scale [N(,1)].  With
+    capi.fused_decode() and M <= 32 the library runs it as one kernel; otherwise quantizer + GEMM through a workspace."""
     from . import capi
 
     M, K = x.shape
@@ -95,7 +95,7 @@ def fp8_linear_fused(x: torch.Tensor, weight: torch.Tensor, weight_scale: torch.
     assert weight.shape[0] == K and weight.stride(0) == 1 and x.stride(1) == 1 and weight_scale.numel() == N
     out = torch.empty(M, N, dtype=x.dtype, device=x.device)
     dt = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16, torch.float32: capi.DTYPE_F32}
-    ws_bytes = int(capi.lib.b2_linear_w8a8_fp8_workspace(M, K)) if M > 32 else 0
+    ws_bytes = int(capi.lib.b2_linear_w8a8_fp8_workspace(M, K))
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device) if ws_bytes else None
     with torch.cuda.device(x.device):
         capi.check(capi.lib.b2_linear_w8a8_fp8(x.data_ptr(), dt[x.dtype], x.stride(0) if M > 1 else K, weight.data_ptr(),

@@ -766,8 +766,9 @@ def test_launch_counter_counts_our_kernels():
     b2.int8_scaled_mm_with_quant(x.to(DEV), W.to(DEV), Bs.to(DEV), None, torch.bfloat16, False)
     assert capi.launch_count() == 2  # quantizer + GEMM
     capi.reset_launch_count()
-    b2.int8_scaled_mm_with_quant(x[:8].to(DEV), W.to(DEV), Bs.to(DEV), None, torch.bfloat16, False)
-    assert capi.launch_count() == 1  # M <= 32: the decode GEMM quantizes its activations itself
+    with capi.fused_decode():
+        b2.int8_scaled_mm_with_quant(x[:8].to(DEV), W.to(DEV), Bs.to(DEV), None, torch.bfloat16, False)
+    assert capi.launch_count() == 1  # M <= 32, opt-in: the decode GEMM quantizes its activations itself
     assert capi.last_gemm_config().endswith("_fusedq")
 
 
@@ -782,7 +783,7 @@ def test_fused_quant_decode_linear_bitwise_vs_oracle(M, K, N, has_bias):
     x[0, ::7] *= 30  # outliers: the row maximum sits in ONE K slice, the others must learn it through the cluster
     ref = restate.int8_scaled_mm_with_quant(x, W, Bs, b.float() if has_bias else None)
     bd = b.to(DEV) if has_bias else None
-    with capi.static_weights():
+    with capi.static_weights(), capi.fused_decode():
         out = b2.int8_scaled_mm_with_quant(x.to(DEV), W.to(DEV), Bs.to(DEV), bd, torch.bfloat16, False)
     assert capi.last_gemm_config().endswith("_fusedq"), capi.last_gemm_config()
     assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref))
@@ -801,11 +802,13 @@ def test_fused_quant_decode_forced_plans_and_strided_input(bn, split):
     out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
     Wd, Bsd, bd = W.to(DEV), Bs.to(DEV), b.to(DEV)
     capi.set_gemm_config(splitk_cfg(0, split, bn))
+    capi.lib.b2_set_fused_decode(1)
     try:
         st = capi.lib.b2_linear_w8a8_int8(xs.data_ptr(), capi.DTYPE_BF16, K + 64, Wd.data_ptr(), K, Bsd.data_ptr(),
                                           bd.data_ptr(), capi.DTYPE_BF16, out.data_ptr(), N, M, N, K, None, 0, _stream())
     finally:
         capi.set_gemm_config(0)
+        capi.lib.b2_set_fused_decode(0)
     capi.check(st)
     assert capi.last_gemm_config().endswith("_fusedq")
     assert torch.equal(bf16_bits(out.cpu()), bf16_bits(ref))
@@ -823,8 +826,9 @@ def test_fused_quant_decode_fp8_linear(M, K, N):
     Wq, ws = mk_fp8_weight(N, K)
     Wd, wsd = Wq.to(DEV), ws.to(DEV).view(-1).contiguous()
     out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
-    capi.check(capi.lib.b2_linear_w8a8_fp8(x.data_ptr(), capi.DTYPE_BF16, K, Wd.data_ptr(), K, wsd.data_ptr(), None, 0,
-                                           out.data_ptr(), N, M, N, K, None, 0, _stream()))
+    with capi.fused_decode():
+        capi.check(capi.lib.b2_linear_w8a8_fp8(x.data_ptr(), capi.DTYPE_BF16, K, Wd.data_ptr(), K, wsd.data_ptr(), None,
+                                               0, out.data_ptr(), N, M, N, K, None, 0, _stream()))
     cfg = capi.last_gemm_config()
     assert cfg.endswith("_fusedq")
     q, s = b2.sglang_per_token_quant_fp8(x)

@@ -497,6 +497,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-decode", action="store_true", help="skip the M = 16 decode companion (profiling runs)")
     ap.add_argument("--no-multi", action="store_true", help="N > 1: skip the strong / tp / multi_gpu_parity legs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -558,7 +559,7 @@ def main():
     flush = None
     if sum(K * N for _, K, N in layers) <= 126e6:
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    decode = decode_companion(b2, dev, layers, probs, load_peaks())
+    decode = None if args.no_decode else decode_companion(b2, dev, layers, probs, load_peaks())
 
     def step():
         outs = []

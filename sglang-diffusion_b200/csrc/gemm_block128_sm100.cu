@@ -43,6 +43,8 @@ struct BlockwiseParams {
   int band_n;
   uint64_t policy_a, policy_b;
   int a_box_rows;
+  void* D;      // narrow tiles (BN < 128) store straight from registers
+  int64_t ldd;  // elements
   unsigned long long* prof;  // see KernelParams::prof ([0] MMA/full [1] MMA/slot [2] producer [3] promotion/partial [4] life)
   int debug_flags;           // 1 = no MMAs, 2 = no promotion arithmetic (handshakes only)
 };
@@ -51,7 +53,7 @@ struct BlockwiseParams {
 // each lane is exactly that of a scalar fma.rn, so the promotion arithmetic is unchanged).  The promotion warps are
 // issue-bound -- 64 FMAs per thread per K block against a 256-clock MMA -- and this halves their FMA slots.
 template <int N>
-B2_DEVICE void promote_fma2(float (&acc)[64], int base, const uint32_t (&x)[32], float scale) {
+B2_DEVICE void promote_fma2(float* acc, int base, const uint32_t* x, float scale) {
   uint64_t s2;
   asm("mov.b64 %0, {%1, %1};" : "=l"(s2) : "f"(scale));
 #pragma unroll
@@ -80,11 +82,15 @@ B2_DEVICE void bw_tile_coords(int tile, const BlockwiseParams& p, int& m_blk, in
   n_blk = p.band_n ? f : s;
 }
 
-template <int OUT_KIND, int CG>
+// BN = 128: the prefill tile.  BN = 64 / 32 (CG = 1 only): decode shapes -- a 128-wide tile leaves N/128 CTAs for the
+// whole weight matrix (32 of 148 SMs for N = 4096); narrow tiles inside ONE 128-column scale block put a CTA on every
+// SM.  Each promotion warp then owns BN/2 columns and stores them straight from registers.
+template <int OUT_KIND, int CG, int BN>
 __global__ void __launch_bounds__(BW_THREADS, 1)
     gemm_block128_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                          const __grid_constant__ CUtensorMap tmap_d, const BlockwiseParams p) {
-  constexpr int BN = BW_BN;
+  constexpr int HC = BN / 2;  // columns per promotion warp
+  static_assert(BN == 128 || (CG == 1 && (BN == 64 || BN == 32)), "narrow tiles are 1-CTA");
   constexpr int B_ROWS = BN / CG;
   constexpr uint32_t A_STAGE_BYTES = BM * BK;
   constexpr uint32_t B_STAGE_BYTES = B_ROWS * BK;
@@ -266,7 +272,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
     const bool has_bias = p.bias != nullptr;
     uint32_t it = 0;
     long long prof_part = 0, prof_sc = 0, prof_ld = 0, prof_body = 0;
-    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(half * 64);
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(half * HC);
 
     // Scales travel through shared memory in chunks of BW_SC K blocks (SFA: 128 rows x BW_SC, SFB: BW_SC),
     // double-buffered and fetched with cp.async one chunk ahead -- across tile boundaries too -- so no
@@ -287,7 +293,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
       if (ptid < BW_SC) {
         const int kb = chunk * BW_SC + ptid;
         if (kb < p.num_kb)
-          cp_async_4(dst_b + ptid, p.sfb + static_cast<int64_t>(n_blk_) * p.sfb_n_stride +
+          cp_async_4(dst_b + ptid, p.sfb + static_cast<int64_t>(n_blk_ * BN / 128) * p.sfb_n_stride +
                                        static_cast<int64_t>(kb) * p.sfb_k_stride);
       }
       cp_async_commit();
@@ -303,11 +309,11 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
       int m_blk, n_blk;
       bw_tile_coords(tile, p, m_blk, n_blk);
       const int row0 = (m_blk * CG + cta_rank) * BM + quarter * 32;
-      const int col0 = n_blk * BN + half * 64;
+      const int col0 = n_blk * BN + half * HC;
 
-      float acc[64];
+      float acc[HC];
 #pragma unroll
-      for (int i = 0; i < 64; ++i) acc[i] = 0.f;
+      for (int i = 0; i < HC; ++i) acc[i] = 0.f;
       uint32_t r0[32], r1[32];
 
       for (int chunk = 0; chunk < nchunks; ++chunk) {
@@ -344,36 +350,58 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
           }
           tc_fence_after_sync();
           const long long wb0 = p.prof ? clock64() : 0;
-          tmem_ld_32x32b_x32(t_lane + col_a, r0);
-          tmem_ld_32x32b_x32(t_lane + col_a + 32, r1);
-          tmem_ld_wait();
-          if (p.prof) prof_ld += clock64() - wb0;
-          // slot a is in registers: hand it back
-          tc_fence_before_sync();
-          __syncwarp();
-          if (lane == 0) {
-            if constexpr (CG == 1) mbar_arrive(&part_empty[ita & (BW_SLOTS - 1)]);
-            else mbar_arrive_cluster(&part_empty[ita & (BW_SLOTS - 1)], 0);
-          }
-          if (!(p.debug_flags & 2)) {
-            promote_fma2<32>(acc, 0, r0, scale_a);
-          }
-          if (two) tmem_ld_32x32b_x32(t_lane + col_b, r0);
-          if (!(p.debug_flags & 2)) {
-            promote_fma2<32>(acc, 32, r1, scale_a);
-          }
-          if (two) {
-            tmem_ld_32x32b_x32(t_lane + col_b + 32, r1);
+          if constexpr (HC == 64) {
+            tmem_ld_32x32b_x32(t_lane + col_a, r0);
+            tmem_ld_32x32b_x32(t_lane + col_a + 32, r1);
             tmem_ld_wait();
+            if (p.prof) prof_ld += clock64() - wb0;
+            // slot a is in registers: hand it back
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) {
-              if constexpr (CG == 1) mbar_arrive(&part_empty[itb & (BW_SLOTS - 1)]);
-              else mbar_arrive_cluster(&part_empty[itb & (BW_SLOTS - 1)], 0);
+              if constexpr (CG == 1) mbar_arrive(&part_empty[ita & (BW_SLOTS - 1)]);
+              else mbar_arrive_cluster(&part_empty[ita & (BW_SLOTS - 1)], 0);
             }
             if (!(p.debug_flags & 2)) {
-              promote_fma2<32>(acc, 0, r0, scale_b);
-              promote_fma2<32>(acc, 32, r1, scale_b);
+              promote_fma2<32>(acc, 0, r0, scale_a);
+            }
+            if (two) tmem_ld_32x32b_x32(t_lane + col_b, r0);
+            if (!(p.debug_flags & 2)) {
+              promote_fma2<32>(acc, 32, r1, scale_a);
+            }
+            if (two) {
+              tmem_ld_32x32b_x32(t_lane + col_b + 32, r1);
+              tmem_ld_wait();
+              tc_fence_before_sync();
+              __syncwarp();
+              if (lane == 0) {
+                if constexpr (CG == 1) mbar_arrive(&part_empty[itb & (BW_SLOTS - 1)]);
+                else mbar_arrive_cluster(&part_empty[itb & (BW_SLOTS - 1)], 0);
+              }
+              if (!(p.debug_flags & 2)) {
+                promote_fma2<32>(acc, 0, r0, scale_b);
+                promote_fma2<32>(acc, 32, r1, scale_b);
+              }
+            }
+          } else {
+            // narrow tile: both partial products of the step in one TMEM round trip (HC = 32 or 16 columns each)
+            uint32_t(&r0lo)[16] = *reinterpret_cast<uint32_t(*)[16]>(&r0[0]);
+            uint32_t(&r1lo)[16] = *reinterpret_cast<uint32_t(*)[16]>(&r1[0]);
+            if constexpr (HC == 32) {
+              tmem_ld_32x32b_x32(t_lane + col_a, r0);
+              if (two) tmem_ld_32x32b_x32(t_lane + col_b, r1);
+            } else {
+              tmem_ld_32x32b_x16(t_lane + col_a, r0lo);
+              if (two) tmem_ld_32x32b_x16(t_lane + col_b, r1lo);
+            }
+            tmem_ld_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&part_empty[ita & (BW_SLOTS - 1)]);
+            else if (lane == 1 && two) mbar_arrive(&part_empty[itb & (BW_SLOTS - 1)]);
+            if (!(p.debug_flags & 2)) {
+              promote_fma2<HC>(acc, 0, r0, scale_a);
+              if (two) promote_fma2<HC>(acc, 0, r1, scale_b);
             }
           }
           it += two ? 2 : 1;
@@ -382,34 +410,61 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
         sbuf ^= 1;
       }
 
-      // ---- write the warp's 32 x 64 block: bias, cast, swizzled staging, one TMA store ----
-      tma_store_wait_read<0>();  // the previous tile's store has long drained the staging buffer
-      __syncwarp();
-#pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        const int col = col0 + g * 8;
-        float v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j];
-        if (has_bias && col < p.N) {
-          float bi[8];
-          load_bias8(p.bias, p.bias_dtype, col, bi);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = __fadd_rn(v[j], bi[j]);
+      if constexpr (HC == 64) {
+        // ---- write the warp's 32 x 64 block: bias, cast, swizzled staging, one TMA store ----
+        tma_store_wait_read<0>();  // the previous tile's store has long drained the staging buffer
+        __syncwarp();
+  #pragma unroll
+        for (int g = 0; g < 8; ++g) {
+          const int col = col0 + g * 8;
+          float v[8];
+  #pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j];
+          if (has_bias && col < p.N) {
+            float bi[8];
+            load_bias8(p.bias, p.bias_dtype, col, bi);
+  #pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __fadd_rn(v[j], bi[j]);
+          }
+          uint4 o;
+          o.x = pack16<OUT_KIND>(v[0], v[1]);
+          o.y = pack16<OUT_KIND>(v[2], v[3]);
+          o.z = pack16<OUT_KIND>(v[4], v[5]);
+          o.w = pack16<OUT_KIND>(v[6], v[7]);
+          const int chunk16 = g ^ (lane & 7);
+          *reinterpret_cast<uint4*>(stage_buf + lane * 128 + chunk16 * 16) = o;
         }
-        uint4 o;
-        o.x = pack16<OUT_KIND>(v[0], v[1]);
-        o.y = pack16<OUT_KIND>(v[2], v[3]);
-        o.z = pack16<OUT_KIND>(v[4], v[5]);
-        o.w = pack16<OUT_KIND>(v[6], v[7]);
-        const int chunk16 = g ^ (lane & 7);
-        *reinterpret_cast<uint4*>(stage_buf + lane * 128 + chunk16 * 16) = o;
-      }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (row0 < p.M && col0 < p.N && elect_one()) {
-        tma_store_2d(&tmap_d, stage_buf, col0, row0);
-        tma_store_commit();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (row0 < p.M && col0 < p.N && elect_one()) {
+          tma_store_2d(&tmap_d, stage_buf, col0, row0);
+          tma_store_commit();
+        }
+
+      } else {
+        // narrow tile: each thread owns HC consecutive columns (64 or 32 bytes) of one row -> 16-byte global stores
+        const int row = row0 + lane;
+        if (row < p.M && col0 < p.N) {
+          uint8_t* drow = static_cast<uint8_t*>(p.D) + (static_cast<int64_t>(row) * p.ldd + col0) * 2;
+#pragma unroll
+          for (int g = 0; g < HC / 8; ++g) {
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j];
+            if (has_bias) {
+              float bi[8];
+              load_bias8(p.bias, p.bias_dtype, col0 + g * 8, bi);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = __fadd_rn(v[j], bi[j]);
+            }
+            uint4 o;
+            o.x = pack16<OUT_KIND>(v[0], v[1]);
+            o.y = pack16<OUT_KIND>(v[2], v[3]);
+            o.z = pack16<OUT_KIND>(v[4], v[5]);
+            o.w = pack16<OUT_KIND>(v[6], v[7]);
+            *reinterpret_cast<uint4*>(drow + g * 16) = o;
+          }
+        }
       }
     }
     tma_store_wait_all<0>();
@@ -439,10 +494,10 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
 
 static int bw_fixed_smem() { return BW_EPI_WARPS * EPI_BUF_BYTES + 2 * BW_SC * BM * 4 + 2 * BW_SC * 4 + 256; }
 
-template <int OUT_KIND, int CG>
+template <int OUT_KIND, int CG, int BN>
 static int launch_bw(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const BlockwiseParams& p,
                      int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
-  auto kern = gemm_block128_kernel<OUT_KIND, CG>;
+  auto kern = gemm_block128_kernel<OUT_KIND, CG, BN>;
   static thread_local int attr_dev = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -475,21 +530,40 @@ static int launch_bw(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
   return B2_OK;
 }
 
-// forced_config (low byte): 0 = automatic, 1 = 1-CTA 128x128 tiles, 2 = 2-CTA 256x128 tiles
+// forced_config (low byte): 0 = automatic, 1 = 1-CTA 128x128 tiles, 2 = 2-CTA 256x128 tiles, 7 / 8 = 1-CTA 128x64 /
+// 128x32 tiles (decode shapes)
 int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** used_config, cudaStream_t st,
                           char* err, size_t err_len) {
   const int forced_debug = forced_config >> 8;
   forced_config &= 0xff;
   const int sms = device_sm_count();
   int cg = a.M > BM ? 2 : 1;  // a pair needs more than one 128-row block to fill
-  if (forced_config == 1) cg = 1;
-  if (forced_config == 2) cg = 2;
+  int bn = BW_BN;
+  if (cg == 1) {
+    // M <= 128 is a stream of the weight bytes: pick the tile width that minimises (waves x bytes per CTA); ties go
+    // to the wider tile (fewer MMAs and hand-shakes per byte).  N = 4096: 32 / 64 / 128 tiles of 128 / 64 / 32 -> 32.
+    long best = -1;
+    for (int cand : {128, 64, 32}) {
+      const long tiles = (a.N + cand - 1) / cand;
+      const long cost = ((tiles + sms - 1) / sms) * cand;
+      if (best < 0 || cost < best) {
+        best = cost;
+        bn = cand;
+      }
+    }
+  }
+  if (forced_config == 1) { cg = 1; bn = 128; }
+  if (forced_config == 2) { cg = 2; bn = 128; }
+  if (forced_config == 7) { cg = 1; bn = 64; }
+  if (forced_config == 8) { cg = 1; bn = 32; }
   static const int dbg_env = [] {
     const char* e = getenv("B2_GEMM_DEBUG");
     return e ? atoi(e) : 0;
   }();
-  if (used_config) *used_config = cg == 2 ? "2cta_256x128_block128" : "1cta_128x128_block128";
-  const int b_rows = BW_BN / cg;
+  if (used_config)
+    *used_config = cg == 2 ? "2cta_256x128_block128"
+                           : (bn == 128 ? "1cta_128x128_block128" : (bn == 64 ? "1cta_128x64_block128" : "1cta_128x32_block128"));
+  const int b_rows = bn / cg;
 
   BlockwiseParams p;
   p.sfa = a.As;
@@ -503,13 +577,15 @@ int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** use
   p.M = a.M;
   p.N = a.N;
   p.K = a.K;
+  p.D = a.D;
+  p.ldd = a.ldd;
   p.num_m_blocks = (a.M + BM * cg - 1) / (BM * cg);
-  p.num_n_blocks = (a.N + BW_BN - 1) / BW_BN;
+  p.num_n_blocks = (a.N + bn - 1) / bn;
   p.num_kb = (a.K + BK - 1) / BK;
   int stages = (SMEM_LIMIT - bw_fixed_smem()) / (BM * BK + b_rows * BK);
   if (stages > 10) stages = 10;
   p.stages = stages;
-  choose_raster(a.M, a.N, a.K, BM * cg, BW_BN, p.num_m_blocks, p.num_n_blocks, &p.group_m, &p.band_n, &p.policy_a,
+  choose_raster(a.M, a.N, a.K, BM * cg, bn, p.num_m_blocks, p.num_n_blocks, &p.group_m, &p.band_n, &p.policy_a,
                 &p.policy_b);
   p.a_box_rows = (a.M >= BM || cg == 2) ? BM : ((a.M + 7) / 8) * 8;
   p.prof = static_cast<unsigned long long*>(profile_buffer());
@@ -530,11 +606,19 @@ int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** use
   const size_t smem = static_cast<size_t>(stages) * (BM * BK + b_rows * BK) + bw_fixed_smem();
   const bool f16 = a.out_dtype == B2_DTYPE_F16;
   if (cg == 2) {
-    if (f16) return launch_bw<1, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
-    return launch_bw<0, 2>(ta, tb, td, p, grid, smem, st, err, err_len);
+    if (f16) return launch_bw<1, 2, 128>(ta, tb, td, p, grid, smem, st, err, err_len);
+    return launch_bw<0, 2, 128>(ta, tb, td, p, grid, smem, st, err, err_len);
   }
-  if (f16) return launch_bw<1, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
-  return launch_bw<0, 1>(ta, tb, td, p, grid, smem, st, err, err_len);
+  if (bn == 64) {
+    if (f16) return launch_bw<1, 1, 64>(ta, tb, td, p, grid, smem, st, err, err_len);
+    return launch_bw<0, 1, 64>(ta, tb, td, p, grid, smem, st, err, err_len);
+  }
+  if (bn == 32) {
+    if (f16) return launch_bw<1, 1, 32>(ta, tb, td, p, grid, smem, st, err, err_len);
+    return launch_bw<0, 1, 32>(ta, tb, td, p, grid, smem, st, err, err_len);
+  }
+  if (f16) return launch_bw<1, 1, 128>(ta, tb, td, p, grid, smem, st, err, err_len);
+  return launch_bw<0, 1, 128>(ta, tb, td, p, grid, smem, st, err, err_len);
 }
 
 }  // namespace b2

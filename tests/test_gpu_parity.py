@@ -674,6 +674,33 @@ def test_fp8_blockwise_c3_shape_m4096_sampled(N, K):
     assert bool(torch.isfinite(out).all())
 
 
+@pytest.mark.parametrize("cfg,name", [(1, "1cta_128x128"), (7, "1cta_128x64"), (8, "1cta_128x32"), (2, "2cta_256x128")])
+@pytest.mark.parametrize("M,N,K", [(1, 4096, 7168), (16, 4096, 7168), (128, 7168, 2048), (5, 1536, 640), (300, 512, 1152)])
+def test_fp8_blockwise_every_tile_width(cfg, name, M, N, K):
+    """128 / 64 / 32-wide 1-CTA tiles (the narrow ones are the decode-shape schedule: a CTA on every SM, each inside one
+    128-column scale block, stores straight from registers) and the 2-CTA tile: all within 1 ulp of the restatement,
+    and the narrow tiles bit-identical to the 128-wide one (same per-element arithmetic, K blocks in order)."""
+    g = torch.Generator().manual_seed(M + N + K)
+    x = (torch.randn(M, K, generator=g) / 10).bfloat16()
+    Wq, sfb = mk_fp8_block_weight(N, K)
+    bias = torch.randn(N, generator=g).bfloat16()
+    q_ref, sfa_ref = restate.per_token_group_quant_fp8(x, 128, 1e-10, True)
+    ref = restate.fp8_blockwise_scaled_mm(q_ref, Wq.view(torch.uint8), sfa_ref, sfb) + bias.float()
+    outs = {}
+    for c in (cfg, 1):
+        capi.set_gemm_config(c)
+        try:
+            outs[c] = b2.cutlass_w8a8_block_fp8_linear_with_fallback(x.to(DEV), Wq.to(DEV), [128, 128], sfb.to(DEV),
+                                                                     bias=bias.to(DEV))
+            if c == cfg:
+                assert capi.last_gemm_config().startswith(name), capi.last_gemm_config()
+        finally:
+            capi.set_gemm_config(0)
+    o = outs[cfg].float().cpu()
+    assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 2e-6 * ref.abs().max())
+    assert torch.equal(outs[cfg].view(torch.int16), outs[1].view(torch.int16))
+
+
 @pytest.mark.parametrize("K", [128, 384, 640, 1664, 2176])
 @pytest.mark.parametrize("M,N", [(1, 128), (5, 512), (127, 256), (300, 1536), (1024, 2048)])
 def test_fp8_blockwise_odd_k_block_counts(M, N, K):

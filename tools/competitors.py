@@ -211,6 +211,9 @@ def main():
     if "block" in want:
         shapes = [(4096, 24576, 1536), (4096, 32768, 512), (4096, 7168, 16384), (4096, 36864, 7168), (4096, 7168, 18432),
                   (4096, 4096, 7168), (4096, 7168, 2048), (16, 4096, 7168), (128, 7168, 2048)]
+        if "--decode" in sys.argv:  # decode-shape block-wise only (the narrow-tile schedule)
+            shapes = [(1, 4096, 7168), (16, 4096, 7168), (16, 7168, 2048), (16, 24576, 1536), (64, 7168, 16384),
+                      (128, 7168, 2048), (128, 4096, 7168)]
         if QUICK:
             shapes = [shapes[3], shapes[0]]
         for M, N, K in shapes:

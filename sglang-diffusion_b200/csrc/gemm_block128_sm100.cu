@@ -43,6 +43,7 @@ struct BlockwiseParams {
   int band_n;
   uint64_t policy_a, policy_b;
   int a_box_rows;
+  int ksplit;   // CG == 1 only: K split over the CTAs of a {ksplit,1,1} cluster (decode shapes), 1 = off
   void* D;      // narrow tiles (BN < 128) store straight from registers
   int64_t ldd;  // elements
   unsigned long long* prof;  // see KernelParams::prof ([0] MMA/full [1] MMA/slot [2] producer [3] promotion/partial [4] life)
@@ -66,6 +67,15 @@ B2_DEVICE void promote_fma2(float* acc, int base, const uint32_t* x, float scale
         : "+f"(acc[base + j]), "+f"(acc[base + j + 1])
         : "r"(x[j]), "r"(x[j + 1]), "l"(s2));
   }
+}
+
+B2_DEVICE void st_dsmem_v4(uint32_t local_addr, uint32_t cta, float a, float b, float c, float d) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "st.shared::cluster.v4.f32 [ra], {%2, %3, %4, %5};\n\t}" ::"r"(local_addr),
+      "r"(cta), "f"(a), "f"(b), "f"(c), "f"(d)
+      : "memory");
 }
 
 B2_DEVICE void bw_tile_coords(int tile, const BlockwiseParams& p, int& m_blk, int& n_blk) {
@@ -103,7 +113,10 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem_a + static_cast<size_t>(stages) * A_STAGE_BYTES;
   uint8_t* smem_epi = smem_b + static_cast<size_t>(stages) * B_STAGE_BYTES;  // 8 warps x 4 KB
-  float* smem_sfa = reinterpret_cast<float*>(smem_epi + BW_EPI_WARPS * EPI_BUF_BYTES);  // [2][BW_SC][128]
+  // K split: the partial sums of ranks 1..S-1, pushed into rank 0's shared memory ([S-1][256 threads][HC] fp32)
+  float* smem_x = reinterpret_cast<float*>(smem_epi + BW_EPI_WARPS * EPI_BUF_BYTES);
+  const int S = CG == 1 ? p.ksplit : 1;
+  float* smem_sfa = smem_x + static_cast<size_t>(S - 1) * 256 * HC;  // [2][BW_SC][128]
   float* smem_sfb = smem_sfa + 2 * BW_SC * BM;                                           // [2][BW_SC]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_sfb + 2 * BW_SC);
   uint64_t* empty_bar = full_bar + stages;
@@ -116,8 +129,11 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
   const long long t_start = p.prof ? clock64() : 0;
   const int num_tiles = p.num_m_blocks * p.num_n_blocks;  // tiles of (BM*CG) x BN
   const int cta_rank = CG == 1 ? 0 : static_cast<int>(cluster_ctarank());
-  const int unit = CG == 1 ? static_cast<int>(blockIdx.x) : static_cast<int>(blockIdx.x >> 1);
-  const int num_units = CG == 1 ? static_cast<int>(gridDim.x) : static_cast<int>(gridDim.x >> 1);
+  const int unit = CG == 1 ? static_cast<int>(blockIdx.x) / S : static_cast<int>(blockIdx.x >> 1);
+  const int num_units = CG == 1 ? static_cast<int>(gridDim.x) / S : static_cast<int>(gridDim.x >> 1);
+  const int krank = (CG == 1 && S > 1) ? static_cast<int>(cluster_ctarank()) : 0;
+  const int kb0 = static_cast<int>(static_cast<long long>(krank) * p.num_kb / S);      // my K blocks: [kb0, kb1)
+  const int kb1 = static_cast<int>(static_cast<long long>(krank + 1) * p.num_kb / S);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -156,8 +172,8 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
       bw_tile_coords(tile, p, m_blk, n_blk);
       const int m_row = (m_blk * CG + cta_rank) * BM;
       const int n_row = n_blk * BN + cta_rank * B_ROWS;
-      for (int kb = 0; kb < p.num_kb; kb += 2) {
-        const int n2 = kb + 1 < p.num_kb ? 2 : 1;
+      for (int kb = kb0; kb < kb1; kb += 2) {
+        const int n2 = kb + 1 < kb1 ? 2 : 1;
         const int stage1 = stage + 1 == stages ? 0 : stage + 1;
         const uint32_t phase1 = stage + 1 == stages ? phase ^ 1 : phase;
         const long long w0 = p.prof ? clock64() : 0;
@@ -191,6 +207,11 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
           }
         }
       }
+      if (S > 1) {  // the two cluster barriers of the tile's K-split reduction (see the promotion warps)
+        __syncwarp();
+        cluster_sync_all();
+        cluster_sync_all();
+      }
     }
     if (p.prof && lane == 0) p.prof[blockIdx.x * 8 + 2] = static_cast<unsigned long long>(prof_wait);
   } else if (warp == 1) {
@@ -205,8 +226,8 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
       long long prof_full = 0, prof_issue = 0;
       const int mma_step = (p.debug_flags & 4) ? 1 : 2;  // experiment: one K block per MMA hand-shake
       for (int tile = unit; tile < num_tiles; tile += num_units) {
-        for (int kb = 0; kb < p.num_kb; kb += mma_step) {
-          const int n2 = (mma_step == 2 && kb + 1 < p.num_kb) ? 2 : 1;
+        for (int kb = kb0; kb < kb1; kb += mma_step) {
+          const int n2 = (mma_step == 2 && kb + 1 < kb1) ? 2 : 1;
           const int stage1 = stage + 1 == stages ? 0 : stage + 1;
           const uint32_t phase1 = stage + 1 == stages ? phase ^ 1 : phase;
           {
@@ -256,6 +277,11 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
             }
           }
         }
+        if (S > 1) {
+          __syncwarp();
+          cluster_sync_all();
+          cluster_sync_all();
+        }
       }
       if (p.prof && lane == 0) {
         p.prof[blockIdx.x * 8 + 0] = static_cast<unsigned long long>(prof_full);
@@ -287,18 +313,19 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
 #pragma unroll
       for (int i = 0; i < BW_SC / 2; ++i) {
         const int kl = (ptid >> 7) + 2 * i;
-        const int kb = chunk * BW_SC + kl;
-        if (r_ok && kb < p.num_kb) cp_async_4(dst_a + kl * BM + r, src_row + static_cast<int64_t>(kb) * p.sfa_k_stride);
+        const int kb = kb0 + chunk * BW_SC + kl;
+        if (r_ok && kb < kb1) cp_async_4(dst_a + kl * BM + r, src_row + static_cast<int64_t>(kb) * p.sfa_k_stride);
       }
       if (ptid < BW_SC) {
-        const int kb = chunk * BW_SC + ptid;
-        if (kb < p.num_kb)
+        const int kb = kb0 + chunk * BW_SC + ptid;
+        if (kb < kb1)
           cp_async_4(dst_b + ptid, p.sfb + static_cast<int64_t>(n_blk_ * BN / 128) * p.sfb_n_stride +
                                        static_cast<int64_t>(kb) * p.sfb_k_stride);
       }
       cp_async_commit();
     };
-    const int nchunks = (p.num_kb + BW_SC - 1) / BW_SC;
+    const int nkb = kb1 - kb0;
+    const int nchunks = (nkb + BW_SC - 1) / BW_SC;
     int sbuf = 0;
     if (unit < num_tiles) {
       int m0, n0;
@@ -333,7 +360,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
         const float* sa_s = smem_sfa + sbuf * (BW_SC * BM) + quarter * 32 + lane;
         const float* sb_s = smem_sfb + sbuf * BW_SC;
         const int kb_begin = chunk * BW_SC;
-        const int kb_end = min(p.num_kb, kb_begin + BW_SC);
+        const int kb_end = min(nkb, kb_begin + BW_SC);
         for (int kb = kb_begin; kb < kb_end; kb += 2) {
           const bool two = kb + 1 < kb_end;
           const uint32_t ita = it, itb = it + 1;
@@ -410,6 +437,34 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
         sbuf ^= 1;
       }
 
+      if (S > 1) {
+        // K-split reduction: ranks 1..S-1 push their partial sums into rank 0's shared memory (DSMEM stores), one
+        // cluster barrier, rank 0 adds them in rank order (deterministic) and owns the store; a second barrier keeps
+        // the next tile's pushes behind rank 0's reads.  The producer and MMA warps take part in both barriers.
+        if (krank != 0) {
+          const uint32_t dst = smem_u32(smem_x + (static_cast<size_t>(krank - 1) * 256 + ptid) * HC);
+#pragma unroll
+          for (int j = 0; j < HC; j += 4) st_dsmem_v4(dst + j * 4, 0, acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+        }
+        __syncwarp();
+        cluster_sync_all();
+        if (krank == 0) {
+          for (int r = 1; r < S; ++r) {
+            const float4* src = reinterpret_cast<const float4*>(smem_x + (static_cast<size_t>(r - 1) * 256 + ptid) * HC);
+#pragma unroll
+            for (int j = 0; j < HC / 4; ++j) {
+              const float4 v4 = src[j];
+              acc[4 * j] = __fadd_rn(acc[4 * j], v4.x);
+              acc[4 * j + 1] = __fadd_rn(acc[4 * j + 1], v4.y);
+              acc[4 * j + 2] = __fadd_rn(acc[4 * j + 2], v4.z);
+              acc[4 * j + 3] = __fadd_rn(acc[4 * j + 3], v4.w);
+            }
+          }
+        }
+        __syncwarp();
+        cluster_sync_all();
+      }
+      if (S > 1 && krank != 0) continue;  // rank 0 owns the tile's store
       if constexpr (HC == 64) {
         // ---- write the warp's 32 x 64 block: bias, cast, swizzled staging, one TMA store ----
         tma_store_wait_read<0>();  // the previous tile's store has long drained the staging buffer
@@ -492,7 +547,9 @@ __global__ void __launch_bounds__(BW_THREADS, 1)
 
 // ------------------------------------------------------------------ host ----
 
-static int bw_fixed_smem() { return BW_EPI_WARPS * EPI_BUF_BYTES + 2 * BW_SC * BM * 4 + 2 * BW_SC * 4 + 256; }
+static int bw_fixed_smem(int xbytes = 0) {
+  return BW_EPI_WARPS * EPI_BUF_BYTES + xbytes + 2 * BW_SC * BM * 4 + 2 * BW_SC * 4 + 256;
+}
 
 template <int OUT_KIND, int CG, int BN>
 static int launch_bw(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const BlockwiseParams& p,
@@ -516,7 +573,7 @@ static int launch_bw(const CUtensorMap& ta, const CUtensorMap& tb, const CUtenso
   cfg.stream = st;
   cudaLaunchAttribute attrs[1];
   attrs[0].id = cudaLaunchAttributeClusterDimension;
-  attrs[0].val.clusterDim.x = CG;
+  attrs[0].val.clusterDim.x = CG == 2 ? 2 : p.ksplit;
   attrs[0].val.clusterDim.y = 1;
   attrs[0].val.clusterDim.z = 1;
   cfg.attrs = attrs;
@@ -538,31 +595,58 @@ int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** use
   forced_config &= 0xff;
   const int sms = device_sm_count();
   int cg = a.M > BM ? 2 : 1;  // a pair needs more than one 128-row block to fill
-  int bn = BW_BN;
+  int bn = BW_BN, ks = 1;
+  const int num_kb_h = (a.K + BK - 1) / BK;
+  auto stages_of = [&](int bn_, int ks_) {
+    const int x = (ks_ - 1) * 256 * (bn_ / 2) * 4;
+    return (SMEM_LIMIT - bw_fixed_smem(x)) / (BM * BK + bn_ * BK);
+  };
   if (cg == 1) {
-    // M <= 128 is a stream of the weight bytes: pick the tile width that minimises (waves x bytes per CTA); ties go
-    // to the wider tile (fewer MMAs and hand-shakes per byte).  N = 4096: 32 / 64 / 128 tiles of 128 / 64 / 32 -> 32.
+    // M <= 128 is a stream of the weight bytes through a per-K-block hand-shake loop (~600 clocks per K block, or the
+    // HBM time of the block's bytes on one SM if that is longer).  Pick (tile width, K split) minimising
+    //   waves x K blocks per CTA x time per K block (+ ~1500 clocks for the split's two cluster barriers):
+    // narrow tiles put a CTA on every SM, the split shortens the serial loop.  N = 4096, K = 7168: 128x64 tiles, split 2.
     long best = -1;
     for (int cand : {128, 64, 32}) {
-      const long tiles = (a.N + cand - 1) / cand;
-      const long cost = ((tiles + sms - 1) / sms) * cand;
-      if (best < 0 || cost < best) {
-        best = cost;
-        bn = cand;
+      for (int s_ : {1, 2, 4, 8}) {
+        if (s_ > 1 && (num_kb_h / s_ < 4 || stages_of(cand, s_) < 4)) continue;
+        const long tiles = (a.N + cand - 1) / cand;
+        const long waves = (tiles * s_ + sms - 1) / sms;
+        const long per_kb = cand * 56 / 10 > 600 ? cand * 56 / 10 : 600;
+        const long cost = waves * ((num_kb_h + s_ - 1) / s_) * per_kb + (s_ > 1 ? 1500 : 0);
+        if (best < 0 || cost < best) {
+          best = cost;
+          bn = cand;
+          ks = s_;
+        }
       }
     }
   }
-  if (forced_config == 1) { cg = 1; bn = 128; }
-  if (forced_config == 2) { cg = 2; bn = 128; }
-  if (forced_config == 7) { cg = 1; bn = 64; }
-  if (forced_config == 8) { cg = 1; bn = 32; }
+  // forced ids: 1 / 7 / 8 = 1-CTA 128 / 64 / 32 wide, unsplit; 2 = 2-CTA; 9 + 16*b + s: b = 0/1/2 -> 128/64/32 wide,
+  // split 2^(s+1) (s = 0..2)  -- e.g. 9 = 128 wide split 2, 26 = 64 wide split 4
+  if (forced_config == 1) { cg = 1; bn = 128; ks = 1; }
+  if (forced_config == 2) { cg = 2; bn = 128; ks = 1; }
+  if (forced_config == 7) { cg = 1; bn = 64; ks = 1; }
+  if (forced_config == 8) { cg = 1; bn = 32; ks = 1; }
+  if (forced_config >= 9 && forced_config < 9 + 48) {
+    const int b = (forced_config - 9) / 16, sidx = (forced_config - 9) % 16;
+    cg = 1;
+    bn = 128 >> b;
+    ks = 2 << sidx;
+    if (b > 2 || sidx > 2 || num_kb_h / ks < 1 || stages_of(bn, ks) < 2) {
+      snprintf(err, err_len, "block-wise forced config %d does not fit (bn=%d split=%d)", forced_config, bn, ks);
+      return B2_ERR_ARG;
+    }
+  }
   static const int dbg_env = [] {
     const char* e = getenv("B2_GEMM_DEBUG");
     return e ? atoi(e) : 0;
   }();
-  if (used_config)
-    *used_config = cg == 2 ? "2cta_256x128_block128"
-                           : (bn == 128 ? "1cta_128x128_block128" : (bn == 64 ? "1cta_128x64_block128" : "1cta_128x32_block128"));
+  static thread_local char cfg_name[64];
+  if (cg == 2) snprintf(cfg_name, sizeof(cfg_name), "2cta_256x128_block128");
+  else if (ks == 1) snprintf(cfg_name, sizeof(cfg_name), "1cta_128x%d_block128", bn);
+  else snprintf(cfg_name, sizeof(cfg_name), "1cta_128x%d_block128_ks%d", bn, ks);
+  if (used_config) *used_config = cfg_name;
   const int b_rows = bn / cg;
 
   BlockwiseParams p;
@@ -579,10 +663,12 @@ int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** use
   p.K = a.K;
   p.D = a.D;
   p.ldd = a.ldd;
+  p.ksplit = ks;
   p.num_m_blocks = (a.M + BM * cg - 1) / (BM * cg);
   p.num_n_blocks = (a.N + bn - 1) / bn;
   p.num_kb = (a.K + BK - 1) / BK;
-  int stages = (SMEM_LIMIT - bw_fixed_smem()) / (BM * BK + b_rows * BK);
+  const int xbytes = (ks - 1) * 256 * (bn / 2) * 4;
+  int stages = (SMEM_LIMIT - bw_fixed_smem(xbytes)) / (BM * BK + b_rows * BK);
   if (stages > 10) stages = 10;
   p.stages = stages;
   choose_raster(a.M, a.N, a.K, BM * cg, bn, p.num_m_blocks, p.num_n_blocks, &p.group_m, &p.band_n, &p.policy_a,
@@ -601,9 +687,9 @@ int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** use
     return B2_ERR_CUDA;
   }
   const int tiles = p.num_m_blocks * p.num_n_blocks;
-  const int units = sms / cg;
-  const int grid = (tiles < units ? tiles : units) * cg;
-  const size_t smem = static_cast<size_t>(stages) * (BM * BK + b_rows * BK) + bw_fixed_smem();
+  const int units = sms / (cg * ks);
+  const int grid = (tiles < units ? tiles : units) * cg * ks;
+  const size_t smem = static_cast<size_t>(stages) * (BM * BK + b_rows * BK) + bw_fixed_smem(xbytes);
   const bool f16 = a.out_dtype == B2_DTYPE_F16;
   if (cg == 2) {
     if (f16) return launch_bw<1, 2, 128>(ta, tb, td, p, grid, smem, st, err, err_len);

@@ -701,6 +701,32 @@ def test_fp8_blockwise_every_tile_width(cfg, name, M, N, K):
     assert torch.equal(outs[cfg].view(torch.int16), outs[1].view(torch.int16))
 
 
+@pytest.mark.parametrize("cfg", [9, 10, 25, 26, 27, 41, 42])
+@pytest.mark.parametrize("M,N,K", [(1, 4096, 7168), (16, 4096, 7168), (128, 1536, 2048), (37, 512, 1664)])
+def test_fp8_blockwise_k_split_cluster(cfg, M, N, K):
+    """K split over a {2,4,8}-CTA cluster for the decode tiles (partial sums pushed to rank 0 over DSMEM, added in rank
+    order): within 1 ulp of the restatement, deterministic.  cfg = 9 + 16*b + s: width 128 >> b, split 2 << s."""
+    b, sidx = (cfg - 9) // 16, (cfg - 9) % 16
+    g = torch.Generator().manual_seed(M + N + K + cfg)
+    x = (torch.randn(M, K, generator=g) / 10).bfloat16()
+    Wq, sfb = mk_fp8_block_weight(N, K)
+    bias = torch.randn(N, generator=g).bfloat16()
+    q_ref, sfa_ref = restate.per_token_group_quant_fp8(x, 128, 1e-10, True)
+    ref = restate.fp8_blockwise_scaled_mm(q_ref, Wq.view(torch.uint8), sfa_ref, sfb) + bias.float()
+    outs = []
+    for _ in range(2):
+        capi.set_gemm_config(cfg)
+        try:
+            outs.append(b2.cutlass_w8a8_block_fp8_linear_with_fallback(x.to(DEV), Wq.to(DEV), [128, 128], sfb.to(DEV),
+                                                                       bias=bias.to(DEV)))
+            assert capi.last_gemm_config() == f"1cta_128x{128 >> b}_block128_ks{2 << sidx}", capi.last_gemm_config()
+        finally:
+            capi.set_gemm_config(0)
+    assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))
+    o = outs[0].float().cpu()
+    assert torch.all((o - ref).abs() <= 1.01 * _ulp_bf16(ref) + 4e-6 * ref.abs().max())
+
+
 @pytest.mark.parametrize("K", [128, 384, 640, 1664, 2176])
 @pytest.mark.parametrize("M,N", [(1, 128), (5, 512), (127, 256), (300, 1536), (1024, 2048)])
 def test_fp8_blockwise_odd_k_block_counts(M, N, K):

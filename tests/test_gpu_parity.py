@@ -701,7 +701,7 @@ def test_fp8_blockwise_every_tile_width(cfg, name, M, N, K):
     assert torch.equal(outs[cfg].view(torch.int16), outs[1].view(torch.int16))
 
 
-@pytest.mark.parametrize("cfg", [9, 10, 25, 26, 27, 41, 42])
+@pytest.mark.parametrize("cfg", [9, 25, 26, 41, 42, 43])
 @pytest.mark.parametrize("M,N,K", [(1, 4096, 7168), (16, 4096, 7168), (128, 1536, 2048), (37, 512, 1664)])
 def test_fp8_blockwise_k_split_cluster(cfg, M, N, K):
     """K split over a {2,4,8}-CTA cluster for the decode tiles (partial sums pushed to rank 0 over DSMEM, added in rank

@@ -608,8 +608,9 @@ int gemm_launch_blockwise(const GemmArgs& a, int forced_config, const char** use
     // narrow tiles put a CTA on every SM, the split shortens the serial loop.  N = 4096, K = 7168: 128x64 tiles, split 2.
     long best = -1;
     for (int cand : {128, 64, 32}) {
-      for (int s_ : {1, 2, 4, 8}) {
+      for (int s_ : {1, 2}) {  // measured (profiles/r02m_block_decode_plans.log): splits of 4 / 8 lose to their barriers
         if (s_ > 1 && (num_kb_h / s_ < 4 || stages_of(cand, s_) < 4)) continue;
+        if (s_ > 1 && ((a.N + cand - 1) / cand) * s_ > sms) continue;  // the split only pays inside ONE wave
         const long tiles = (a.N + cand - 1) / cand;
         const long waves = (tiles * s_ + sms - 1) / sms;
         const long per_kb = cand * 56 / 10 > 600 ? cand * 56 / 10 : 600;

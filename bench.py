@@ -716,10 +716,39 @@ def main():
         # check the host result of the last step against the device-resident path (bitwise)
         ref_out = step()
         same = all(torch.equal(oh.view(torch.int16), o.cpu().view(torch.int16)) for (_, _, oh), o in zip(host_layers, ref_out))
+        # what the box's host <-> device links give at best: every rank copies 256 MiB pinned buffers in both directions
+        # at once, all ranks together (the e2e pipeline above is bound by exactly this on one GPU and by the shared host
+        # memory / PCIe root on 8)
+        hb = torch.empty(256 << 20, dtype=torch.uint8).pin_memory()
+        hb2 = torch.empty(256 << 20, dtype=torch.uint8).pin_memory()
+        db, db2 = torch.empty(256 << 20, dtype=torch.uint8, device=dev), torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+        s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        for it in range(2):
+            barrier()
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record()
+            s_in.wait_event(c0)
+            s_out.wait_event(c0)
+            for _ in range(4):
+                with torch.cuda.stream(s_in):
+                    db.copy_(hb, non_blocking=True)
+                with torch.cuda.stream(s_out):
+                    hb2.copy_(db2, non_blocking=True)
+            torch.cuda.current_stream(dev).wait_stream(s_in)
+            torch.cuda.current_stream(dev).wait_stream(s_out)
+            c1.record()
+            torch.cuda.synchronize(dev)
+            ceil_ms = c0.elapsed_time(c1)
+        ceil_ms = _max_over_ranks(ceil_ms, dev, dist, world)
+        ceil_gbs = 8 * (256 << 20) / (ceil_ms * 1e-3) / 1e9  # per rank, both directions together
+        del hb, hb2, db, db2
         e2e = {"value": round(world * ops_step / (e2e_ms * 1e-3) / 1e12, 2), "unit": "TOPS",
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": round(e2e_ms, 3),
                "steps": e2e_steps, "host_wall_ms_per_step": round(wall_ms / e2e_steps, 3),
-               "pcie_gbs": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1), "matches_device_path_bitwise": bool(same)}
+               "pcie_gbs": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1), "matches_device_path_bitwise": bool(same),
+               "link_ceiling_gbs_per_rank": round(ceil_gbs, 1),
+               "link_ceiling_note": "concurrent pinned H2D + D2H copies of 256 MiB on every rank at once, slowest rank",
+               "frac_of_link_ceiling": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9 / ceil_gbs, 3)}
         del host_layers
 
     # -- cpu baseline (rank 0, N = 1 only)

@@ -201,6 +201,31 @@ if "fused" in want:
         line("per_tensor dynamic", M, 0, K, t, 0.0, 5 * M * K)
         t = timed([(lambda x=x: b2.sglang_per_token_group_quant_fp8(x, 128, column_major_scales=True, enable_v2=True)) for x in xs])
         line("group128 v2", M, 0, K, t, 0.0, 3 * M * K + 4 * M * K // 128)
+def moe(T, E, topk, H, I):
+    """fused_experts (W8A8-int8 MoE): six launches; TOPS over the routed MACs 2 * T * topk * 3 * I * H."""
+    g = torch.Generator(device=dev).manual_seed(T + E)
+    x = (torch.randn(T, H, generator=g, device=dev) / 10).bfloat16()
+    w13 = torch.randint(-127, 128, (E, 2 * I, H), dtype=torch.int8, generator=g, device=dev)
+    w2 = torch.randint(-127, 128, (E, H, I), dtype=torch.int8, generator=g, device=dev)
+    s13 = torch.rand(E, 2 * I, 1, generator=g, device=dev) * 2e-3
+    s2 = torch.rand(E, H, 1, generator=g, device=dev) * 2e-3
+    tw, ids = torch.topk(torch.softmax(torch.randn(T, E, generator=g, device=dev), -1), topk, dim=-1)
+    ids = ids.to(torch.int32)
+    t = timed([lambda: b2.fused_experts(x, w13, w2, tw, ids, s13, s2)])
+    ops = 2.0 * T * topk * 3 * I * H
+    byts = E * 3 * I * H + 2 * T * H * 2  # every expert weight once + activations in / out
+    tops = ops / t / 1e12
+    print(f"fused_experts int8     T={T:<6d} E={E:<4d} topk={topk} H={H:<5d} I={I:<5d} {t*1e6:9.1f} us  {tops:8.1f} TOPS "
+          f"({100*tops/TENSOR:5.1f}% of {TENSOR:.0f})  {byts/t/1e9:8.1f} GB/s of weights+io", flush=True)
+
+
+if "moe" in want:
+    print("# W8A8-int8 MoE (fused_experts): Qwen1.5-MoE-A2.7B-like (E=60->64, topk 4, H 2048, I 1408), DeepSeek-V2-Lite-like (E=64, topk 6)")
+    for T in (16, 256, 4096, 16384):
+        moe(T, 64, 4, 2048, 1408)
+        moe(T, 64, 6, 2048, 1408)
+    moe(4096, 8, 2, 4096, 14336)  # Mixtral-8x7B
+    sys.exit(0)
 if "splitk" in want:
     # decode kernel (gemm_splitk_sm100.cu): the planner's pick, then every forced (BN, S), per C2 decode shape
     for K, N in ((4096, 6144), (4096, 28672), (14336, 4096), (8192, 1280), (1024, 8192)):

@@ -57,8 +57,13 @@ B2_DEVICE __half from_f32<__half>(float v) {
 
 template <typename T, Prod PROD, QM MODE, int TPR, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
-  constexpr int NC = 4;   // 16-byte vectors cached per thread
-  constexpr int VEC = 8;  // elements per vector
+  // The row lives in registers between the producer and the quantizer.  SILU_MUL / NONE keep the T-rounded values
+  // PACKED (8 per uint4, 16 registers instead of 32: ncu on the fp32-cached form shows issue_active 48 % and
+  // long_scoreboard 5.5 warps per issue -- latency-bound at 50 % occupancy).  RMSNORM needs the unrounded fp32 sums
+  // for the norm and keeps four fp32 vectors.
+  constexpr bool PACKED = PROD != Prod::RMSNORM;
+  constexpr int NC = 4;               // 16-byte vectors cached per thread (8 was measured: worse below K = 8192)
+  constexpr int VEC = 8;              // elements per vector
   constexpr int ROWS = BLOCK / TPR;
   constexpr int WPR = (TPR + 31) / 32;  // warps per row
   constexpr bool GROUPS = MODE == QM::FP8_G128_V1 || MODE == QM::FP8_G128_V2;
@@ -89,21 +94,25 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
     src = src_ok ? id / a.row_div : 0;
   }
 
-  float f[NC][VEC];
+  float f[PACKED ? 1 : NC][VEC];
+  uint4 yc[PACKED ? NC : 1];
   float sum_sq = 0.f;
   const T* xr = static_cast<const T*>(a.x) + src * a.ldx;
 #pragma unroll
   for (int i = 0; i < NC; ++i) {
     const int v = t + i * TPR;
     const bool on = active && src_ok && v < nvec;
+    if constexpr (PACKED) {
+      yc[i] = make_uint4(0, 0, 0, 0);
+    } else {
 #pragma unroll
-    for (int j = 0; j < VEC; ++j) f[i][j] = 0.f;
+      for (int j = 0; j < VEC; ++j) f[i][j] = 0.f;
+    }
     if (on) {
       const uint4 raw = ld_stream(reinterpret_cast<const uint4*>(xr) + v);
       const T* e = reinterpret_cast<const T*>(&raw);
       if constexpr (PROD == Prod::NONE) {
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) f[i][j] = to_f32(e[j]);
+        yc[i] = raw;
       } else if constexpr (PROD == Prod::SILU_MUL) {
         const uint4 raw2 = ld_stream(reinterpret_cast<const uint4*>(xr + a.K) + v);
         const T* u = reinterpret_cast<const T*>(&raw2);
@@ -113,8 +122,8 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
         for (int j = 0; j < VEC; ++j) {
           const T act = from_f32<T>(silu_sm100(to_f32(e[j])));
           yo[j] = from_f32<T>(__fmul_rn(to_f32(act), to_f32(u[j])));  // T * T (operator* of the reference's types)
-          f[i][j] = to_f32(yo[j]);
         }
+        yc[i] = yv;
         if (a.y != nullptr) reinterpret_cast<uint4*>(static_cast<T*>(a.y) + rr * a.ldy)[v] = yv;
       } else {  // RMSNORM, first pass: s = x + residual, residual <- T(s), sum of squares of the unrounded s
         if (a.residual != nullptr) {
@@ -172,23 +181,35 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
     }
   }
 
-  // ---- quantizer over the T-rounded row held in f ----
+  // ---- quantizer over the T-rounded row held in registers ----
+  auto load8 = [&](int i, float (&o)[VEC]) {
+    if constexpr (PACKED) {
+      const T* e = reinterpret_cast<const T*>(&yc[i]);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) o[j] = to_f32(e[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) o[j] = f[i][j];
+    }
+  };
   uint8_t* qr = a.q + rr * a.ldq;
   if constexpr (GROUPS) {
 #pragma unroll
     for (int i = 0; i < NC; ++i) {
       const int v = t + i * TPR;
+      float g8[VEC];
+      load8(i, g8);
       float amax = a.q_eps;
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) amax = fmaxf(amax, fabsf(f[i][j]));
+      for (int j = 0; j < VEC; ++j) amax = fmaxf(amax, fabsf(g8[j]));
 #pragma unroll
       for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
       uint2 out;
       float sc;
       if constexpr (MODE == QM::FP8_G128_V1) {
-        sc = group128_quantize_v1(f[i], amax, a.fmin, a.fmax, out);
+        sc = group128_quantize_v1(g8, amax, a.fmin, a.fmax, out);
       } else {
-        sc = group128_quantize_v2(f[i], amax, out);
+        sc = group128_quantize_v2(g8, amax, out);
       }
       if (active && v < nvec) {
         reinterpret_cast<uint2*>(qr)[v] = out;
@@ -199,9 +220,12 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
   } else {
     float amax = 0.f;
 #pragma unroll
-    for (int i = 0; i < NC; ++i)
+    for (int i = 0; i < NC; ++i) {
+      float g8[VEC];
+      load8(i, g8);
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) amax = fmaxf(amax, fabsf(f[i][j]));
+      for (int j = 0; j < VEC; ++j) amax = fmaxf(amax, fabsf(g8[j]));
+    }
 #pragma unroll
     for (int o = SHFL_W / 2; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
     if constexpr (WPR > 1) {
@@ -228,16 +252,18 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
       const int v = t + i * TPR;
       if (v < nvec) {
         uint2 out;
+        float g8[VEC];
+        load8(i, g8);
         if constexpr (MODE == QM::INT8_ROWS) {
           uint8_t* o = reinterpret_cast<uint8_t*>(&out);
 #pragma unroll
-          for (int j = 0; j < VEC; ++j) o[j] = quant_one<QMode::INT8>(f[i][j], inv);
+          for (int j = 0; j < VEC; ++j) o[j] = quant_one<QMode::INT8>(g8[j], inv);
         } else {
           uint16_t* o2 = reinterpret_cast<uint16_t*>(&out);
 #pragma unroll
           for (int j = 0; j < VEC; j += 2) {
-            const float p = fmaxf(fminf(__fmul_rn(f[i][j], inv), 448.f), -448.f);
-            const float r = fmaxf(fminf(__fmul_rn(f[i][j + 1], inv), 448.f), -448.f);
+            const float p = fmaxf(fminf(__fmul_rn(g8[j], inv), 448.f), -448.f);
+            const float r = fmaxf(fminf(__fmul_rn(g8[j + 1], inv), 448.f), -448.f);
             o2[j >> 1] = f32x2_to_e4m3x2(p, r);
           }
         }
@@ -268,8 +294,9 @@ static cudaError_t launch_fused(const FusedQuantArgs& a, cudaStream_t st) {
 template <typename T, Prod PROD, QM MODE>
 static cudaError_t dispatch_fused_tpr(const FusedQuantArgs& a, cudaStream_t st) {
   const int nvec = a.K / 8;
+  constexpr int NCH = 4;  // vectors a thread caches (fused_rows_kernel::NC)
   int tpr = 32;
-  while (tpr < 1024 && nvec > tpr * 4) tpr *= 2;
+  while (tpr < 1024 && nvec > tpr * NCH) tpr *= 2;
   // few rows (decode): spread a row over more threads as long as every thread keeps a vector
   while (tpr < 1024 && a.M * static_cast<int64_t>(tpr) < 148 * 1024 && nvec >= tpr * 2) tpr *= 2;
   switch (tpr) {

@@ -185,59 +185,8 @@ static inline EncodeTiledFn get_encode_fn() {
 
 // 2-D row-major tensor [rows, cols] of `esize`-byte elements, row stride `ld_bytes`;
 // box = {box_cols elements (128 bytes), box_rows}, 128-byte swizzle.
-// cuTensorMapEncodeTiled costs ~1-2 us of host time and a GEMM launch needs two or three maps; eager decode loops
-// call the same layers with the same weight / activation buffers every step, so the encoded maps are kept in a small
-// thread-local direct-mapped cache keyed by everything that goes into the encoding (the map holds no device state:
-// same key -> same 128 bytes).  B2_TMAP_CACHE=0 turns it off (A/B in profiles/r02q_host_overhead.log).
-struct TmapKey {
-  const void* base;
-  uint64_t rows, cols, ld_bytes;
-  uint32_t box_rows, box_cols;
-  int dt, esize;
-  bool operator==(const TmapKey& o) const {
-    return base == o.base && rows == o.rows && cols == o.cols && ld_bytes == o.ld_bytes && box_rows == o.box_rows &&
-           box_cols == o.box_cols && dt == o.dt && esize == o.esize;
-  }
-};
-struct TmapSlot {
-  TmapKey key;
-  CUtensorMap map;
-  bool valid;
-};
-
-static inline bool make_tmap_2d_uncached(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* base,
-                                         uint64_t rows, uint64_t cols, uint64_t ld_bytes, uint32_t box_rows,
-                                         uint32_t box_cols);
-
 static inline bool make_tmap_2d(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* base, uint64_t rows,
-                                uint64_t cols, uint64_t ld_bytes, uint32_t box_rows, uint32_t box_cols) {
-  static const bool enabled = [] {
-    const char* e = getenv("B2_TMAP_CACHE");
-    return !(e && e[0] == '0');
-  }();
-  if (!enabled) return make_tmap_2d_uncached(m, dt, esize, base, rows, cols, ld_bytes, box_rows, box_cols);
-  constexpr int kSlots = 64;
-  static thread_local TmapSlot cache[kSlots] = {};
-  const TmapKey key{base, rows, cols, ld_bytes, box_rows, box_cols, static_cast<int>(dt), esize};
-  uint64_t h = reinterpret_cast<uintptr_t>(base) >> 8;
-  h ^= rows * 0x9E3779B97F4A7C15ull ^ (cols << 17) ^ (static_cast<uint64_t>(box_rows) << 40) ^ (static_cast<uint64_t>(box_cols) << 52) ^
-       (ld_bytes << 7) ^ static_cast<uint64_t>(dt);
-  h ^= h >> 29;
-  TmapSlot& slot = cache[h % kSlots];
-  if (slot.valid && slot.key == key) {
-    *m = slot.map;
-    return true;
-  }
-  if (!make_tmap_2d_uncached(m, dt, esize, base, rows, cols, ld_bytes, box_rows, box_cols)) return false;
-  slot.key = key;
-  slot.map = *m;
-  slot.valid = true;
-  return true;
-}
-
-static inline bool make_tmap_2d_uncached(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* base,
-                                         uint64_t rows, uint64_t cols, uint64_t ld_bytes, uint32_t box_rows,
-                                         uint32_t box_cols) {
+                         uint64_t cols, uint64_t ld_bytes, uint32_t box_rows, uint32_t box_cols) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return false;
   cuuint64_t dims[2] = {cols, rows};

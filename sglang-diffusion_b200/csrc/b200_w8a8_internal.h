@@ -84,6 +84,10 @@ struct GemmArgs {
   const void* x;
   int64_t ldx;
   int x_dtype;
+  // batched mode (bmm_fp8): `batch` independent problems, strides in BYTES for A / W and in ELEMENTS for D; As / Bs
+  // are shared by every batch entry
+  int batch;
+  int64_t a_batch_stride, w_batch_stride, d_batch_stride;
 };
 
 enum GemmFlavor { GEMM_S8 = 0, GEMM_E4M3 = 1, GEMM_E4M3_BLOCK128 = 2 };

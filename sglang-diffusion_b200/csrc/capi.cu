@@ -511,12 +511,19 @@ int b2_bmm_e4m3(const uint8_t* A, int64_t lda, int64_t a_batch_stride, const uin
                          "bmm_fp8 scale broadcast launch"))
     return r;
   count_launch();
+  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16 && out_dtype != B2_DTYPE_F32)
+    return fail(B2_ERR_ARG, "bmm_fp8: out_dtype must be Half or BFloat16");
   const int ob = out_dtype == B2_DTYPE_F32 ? 4 : 2;
-  for (int b = 0; b < batch; ++b) {
-    if (int r = b2_gemm_e4m3(A + b * a_batch_stride, lda, W + b * w_batch_stride, ldw, as, bs, nullptr, B2_DTYPE_BF16,
-                             static_cast<uint8_t*>(D) + b * d_batch_stride * ob, ldd, out_dtype, M, N, K, stream))
-      return r;
-  }
+  if (int r = check_gemm_common(A, lda, W, ldw, D, ldd, ob, M, N, K)) return r;
+  // ONE launch: the persistent GEMM in batched mode (3-D tensor maps, tiles enumerate batch-major)
+  GemmArgs a{};
+  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = as; a.Bs = bs; a.bias = nullptr; a.bias_dtype = B2_DTYPE_BF16;
+  a.D = D; a.ldd = ldd; a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K;
+  a.batch = batch; a.a_batch_stride = a_batch_stride; a.w_batch_stride = w_batch_stride; a.d_batch_stride = d_batch_stride;
+  char err[256];
+  int r = gemm_launch(GEMM_E4M3, a, batch > 1 ? (g_forced_config & 0xff) : g_forced_config, &g_last_config,
+                      static_cast<cudaStream_t>(stream), err, sizeof(err));
+  if (r) return fail(r, "bmm_fp8: %s", err);
   return B2_OK;
 }
 

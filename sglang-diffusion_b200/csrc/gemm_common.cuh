@@ -29,6 +29,7 @@ struct KernelParams {
   int bias_dtype;
   int out_dtype;
   const int32_t* tile_expert;  // grouped (MoE) mode: expert of every 128-row block of A (-1 = skip), else nullptr
+  int batch;                   // batched mode (bmm_fp8): > 1 = the tensor maps are 3-D, tiles enumerate batch-major
   int M, N, K;
   int num_m_blocks, num_n_blocks, num_kb;
   int stages;
@@ -201,6 +202,27 @@ static inline bool make_tmap_2d(CUtensorMap* m, CUtensorMapDataType dt, int esiz
   CUresult r = enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+// 3-D tensor [batch, rows, cols] (batch stride `batch_bytes`); box = {box_cols, box_rows, 1}: the same shared-memory
+// image as the 2-D box, with per-batch clipping of rows (a tile never reads or writes into the next batch entry).
+static inline bool make_tmap_3d(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* base, uint64_t batch,
+                                uint64_t rows, uint64_t cols, uint64_t ld_bytes, uint64_t batch_bytes, uint32_t box_rows,
+                                uint32_t box_cols) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return false;
+  cuuint64_t dims[3] = {cols, rows, batch};
+  cuuint64_t strides[2] = {ld_bytes, batch > 1 ? batch_bytes : ld_bytes * rows};
+  cuuint32_t box[3] = {box_cols, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  const uint32_t box_bytes = box_cols * static_cast<uint32_t>(esize);
+  const CUtensorMapSwizzle swz = box_bytes == 128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                                 : box_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                   : CU_TENSOR_MAP_SWIZZLE_NONE;
+  if (swz == CU_TENSOR_MAP_SWIZZLE_NONE) return false;
+  CUresult r = enc(m, dt, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }
 

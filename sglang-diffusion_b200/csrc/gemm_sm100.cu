@@ -70,7 +70,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const long long t_start = p.prof ? clock64() : 0;
-  const int num_tiles = p.num_m_blocks * p.num_n_blocks;  // tiles of (BM*CG) x BN
+  const int tiles_pb = p.num_m_blocks * p.num_n_blocks;  // tiles of (BM*CG) x BN per batch entry
+  const int num_tiles = tiles_pb * (p.batch > 1 ? p.batch : 1);
   const int cta_rank = CG == 1 ? 0 : static_cast<int>(cluster_ctarank());
   const int unit = CG == 1 ? static_cast<int>(blockIdx.x) : static_cast<int>(blockIdx.x >> 1);
   const int num_units = CG == 1 ? static_cast<int>(gridDim.x) : static_cast<int>(gridDim.x >> 1);
@@ -113,7 +114,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       long long prof_wait = 0;
       for (int tile = unit; tile < num_tiles; tile += num_units) {
         int m_blk, n_blk;
-        tile_coords(tile, p, m_blk, n_blk);
+        const int bidx = p.batch > 1 ? tile / tiles_pb : 0;  // batched mode: tiles enumerate batch-major
+        tile_coords(tile - bidx * tiles_pb, p, m_blk, n_blk);
         const int expert = p.tile_expert ? __ldg(p.tile_expert + m_blk) : 0;  // grouped (MoE) mode: CG == 1
         if (expert < 0) continue;  // a padding block past the last routed token
         const int m_row = (m_blk * CG + cta_rank) * BM;
@@ -129,16 +131,26 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           } else if constexpr (CG == 1) {
             if (elect_one()) {
               mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-              tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kb * BK, m_row, p.policy_a);
-              tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * BK, n_row, p.policy_b);
+              if (p.batch > 1) {
+                tma_load_3d(a_dst, &tmap_a, &full_bar[stage], kb * BK, m_row, bidx, p.policy_a);
+                tma_load_3d(b_dst, &tmap_b, &full_bar[stage], kb * BK, n_row, bidx, p.policy_b);
+              } else {
+                tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kb * BK, m_row, p.policy_a);
+                tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * BK, n_row, p.policy_b);
+              }
             }
           } else {
             // both CTAs' bytes are expected on (and complete on) the leader CTA's barrier
             if (elect_one()) {
               if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
               const uint32_t bar0 = smem_u32(&full_bar[stage]) & kPeerBitMask;
-              tma_load_2d_cg2(smem_u32(a_dst), &tmap_a, bar0, kb * BK, m_row, p.policy_a);
-              tma_load_2d_cg2(smem_u32(b_dst), &tmap_b, bar0, kb * BK, n_row, p.policy_b);
+              if (p.batch > 1) {
+                tma_load_3d_cg2(smem_u32(a_dst), &tmap_a, bar0, kb * BK, m_row, bidx, p.policy_a);
+                tma_load_3d_cg2(smem_u32(b_dst), &tmap_b, bar0, kb * BK, n_row, bidx, p.policy_b);
+              } else {
+                tma_load_2d_cg2(smem_u32(a_dst), &tmap_a, bar0, kb * BK, m_row, p.policy_a);
+                tma_load_2d_cg2(smem_u32(b_dst), &tmap_b, bar0, kb * BK, n_row, p.policy_b);
+              }
             }
           }
           __syncwarp();
@@ -161,7 +173,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       uint32_t acc_phase = 0;
       long long prof_full = 0, prof_acc = 0;
       for (int tile = unit; tile < num_tiles; tile += num_units) {
-        if (p.tile_expert) {
+        if (p.tile_expert) {  // (never together with the batched mode)
           int m_blk, n_blk;
           tile_coords(tile, p, m_blk, n_blk);
           if (__ldg(p.tile_expert + m_blk) < 0) continue;
@@ -232,7 +244,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     const int swz = BOX_BYTES == 128 ? (lane & 7) : ((lane >> 1) & 3);
     for (int tile = unit; tile < num_tiles; tile += num_units) {
       int m_blk, n_blk;
-      tile_coords(tile, p, m_blk, n_blk);
+      const int bidx = p.batch > 1 ? tile / tiles_pb : 0;
+      tile_coords(tile - bidx * tiles_pb, p, m_blk, n_blk);
       const int expert = p.tile_expert ? __ldg(p.tile_expert + m_blk) : 0;
       if (expert < 0) continue;
       const float* Bs_e = p.Bs + static_cast<size_t>(expert) * p.N;  // per-expert channel scales [E, N]
@@ -352,7 +365,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
               fence_proxy_async_smem();
               __syncwarp();
               if (row0 < p.M && col_box < p.N && elect_one()) {  // the same lane every time
-                tma_store_2d(&tmap_d, stage_buf, col_box, row0);
+                if (p.batch > 1) tma_store_3d(&tmap_d, stage_buf, col_box, row0, bidx);
+                else tma_store_2d(&tmap_d, stage_buf, col_box, row0);
                 tma_store_commit();
               }
               buf ^= 1;
@@ -508,7 +522,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   // M in (32, 64]: still ahead on layers up to ~64 rows of W per SM (profiles/r01e_m64_probe.log: 9.4 vs 12.0 us on
   // 6144 x 4096, 15.7 vs 19.9 us on 7168 x 8192), behind on the widest ones where 128 x 256 persistent tiles stream well
   // (short K -- 8 K-blocks -- leaves the decode kernel nothing to pipeline at M > 32: 8.2 vs 6.8 us on 8192 x 1024)
-  const bool decode_shape = a.tile_expert == nullptr && (
+  const bool decode_shape = a.tile_expert == nullptr && a.batch <= 1 && (
       a.M <= 32 || (a.M <= 64 && a.N <= 64 * sms && a.K >= 2048) || (a.M <= BM && a.N < 32 * sms));
   if (a.mc_slot != nullptr && !(decode_shape || a.M <= BM)) {
     snprintf(err, err_len, "multicast push epilogue is built for decode shapes (M <= 128) only");
@@ -516,7 +530,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   }
   if (a.x != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
   if (a.mc_slot != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
-  if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert) : ((forced_config & 0xff) == 0 && decode_shape))
+  if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert && a.batch <= 1) : ((forced_config & 0xff) == 0 && decode_shape))
     return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);
   const TileConfig* cfg = &pick_config(a.M, a.N, sms);
   const int forced_debug = forced_config >> 8;  // developer experiments ride in the upper bits of the forced id
@@ -548,6 +562,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   p.bias_dtype = a.bias_dtype;
   p.out_dtype = a.out_dtype;
   p.tile_expert = a.tile_expert;
+  p.batch = a.batch > 1 ? a.batch : 1;
   p.M = a.M;
   p.N = a.N;
   p.K = a.K;
@@ -575,6 +590,18 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   p.a_box_rows = (a.M >= BM || cg == 2) ? BM : ((a.M + 7) / 8) * 8;
 
   CUtensorMap ta, tb, td;
+  const uint32_t d_box_cols = (128 / out_bytes) < bn ? (128 / out_bytes) : bn;
+  if (a.batch > 1) {
+    // batched (bmm_fp8): 3-D maps, one depth-1 box per tile; rows are clipped per batch entry
+    if (a.tile_expert || !make_tmap_3d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.batch, a.M, a.K, a.lda,
+                                       a.a_batch_stride, p.a_box_rows, BK) ||
+        !make_tmap_3d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.batch, a.N, a.K, a.ldw, a.w_batch_stride, b_rows, BK) ||
+        !make_tmap_3d(&td, d_dt, out_bytes, a.D, a.batch, a.M, a.N, a.ldd * out_bytes, a.d_batch_stride * out_bytes, 32,
+                      d_box_cols)) {
+      snprintf(err, err_len, "cuTensorMapEncodeTiled failed (batched, batch=%d M=%d N=%d K=%d)", a.batch, a.M, a.N, a.K);
+      return B2_ERR_CUDA;
+    }
+  } else
   if (!make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, p.a_box_rows, BK) ||
       !make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W,
                     static_cast<uint64_t>(a.N) * (a.tile_expert ? a.num_experts : 1), a.K, a.ldw, b_rows, BK) ||
@@ -584,7 +611,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
              a.K, (long long)a.lda, (long long)a.ldw, (long long)a.ldd);
     return B2_ERR_CUDA;
   }
-  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  const int tiles = p.num_m_blocks * p.num_n_blocks * p.batch;
   const int units = sms / cg;
   const int grid = (tiles < units ? tiles : units) * cg;
   const size_t smem = smem_bytes_for(bn, b_rows, p.stages);

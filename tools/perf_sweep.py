@@ -219,6 +219,18 @@ def moe(T, E, topk, H, I):
           f"({100*tops/TENSOR:5.1f}% of {TENSOR:.0f})  {byts/t/1e9:8.1f} GB/s of weights+io", flush=True)
 
 
+if "bmm" in want:
+    print("# bmm_fp8 (MLA absorbed BMMs, per-tensor scales): one batched launch; cuBLAS bf16 bmm of the dequantized operands beside it")
+    for b, m, k, n in ((128, 16, 128, 512), (128, 16, 512, 128), (16, 4096, 128, 512), (16, 4096, 512, 128), (128, 256, 128, 512)):
+        A = torch.randn(b, m, k, device=dev).to(torch.float8_e4m3fn)
+        W = torch.randn(b, n, k, device=dev).to(torch.float8_e4m3fn)
+        sa, sb = torch.tensor([0.01], device=dev), torch.tensor([0.02], device=dev)
+        t = timed([lambda: b2.bmm_fp8(A, W.transpose(-2, -1), sa, sb, torch.bfloat16)])
+        Ab, Wb = A.bfloat16(), W.bfloat16().transpose(-2, -1)
+        t2 = timed([lambda: torch.bmm(Ab, Wb)])
+        print(f"bmm_fp8 b={b:<4d} m={m:<5d} k={k:<4d} n={n:<4d} {t*1e6:8.1f} us  {2.0*b*m*n*k/t/1e12:7.1f} TFLOPS   "
+              f"[{b2.capi.last_gemm_config()}]   torch.bmm bf16 {t2*1e6:8.1f} us", flush=True)
+    sys.exit(0)
 if "moe" in want:
     print("# W8A8-int8 MoE (fused_experts): Qwen1.5-MoE-A2.7B-like (E=60->64, topk 4, H 2048, I 1408), DeepSeek-V2-Lite-like (E=64, topk 6)")
     for T in (16, 256, 4096, 16384):

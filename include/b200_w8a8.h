@@ -157,7 +157,9 @@ int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64
 /* bmm_fp8 (sgl-kernel/csrc/gemm/bmm_fp8.cu; flashinfer bmm_fp8_internal_cublaslt): for every batch b,
  *     D[b] = out_t( a_scale * b_scale * f32(A[b] . W[b]^T) ),  A [batch, M, K] e4m3, W [batch, N, K] e4m3 (the
  * reference passes B = W.transpose(-2,-1), "column major"), per-tensor fp32 device scalars a_scale / b_scale.
- * workspace (>= b2_bmm_e4m3_workspace(M, N) bytes) holds the broadcast scale vectors of the shared epilogue. */
+ * ONE launch: the persistent tcgen05 GEMM in batched mode (3-D tensor maps clip every tile to its own batch entry,
+ * tiles enumerate batch-major, the epilogue reads the two scalars).  Batch strides: A / W in bytes, D in elements.
+ * The workspace arguments mirror the reference's cuBLASLt workspace and are unused (b2_bmm_e4m3_workspace() == 0). */
 size_t b2_bmm_e4m3_workspace(int M, int N);
 int b2_bmm_e4m3(const uint8_t* A, int64_t lda, int64_t a_batch_stride, const uint8_t* W, int64_t ldw,
                 int64_t w_batch_stride, const float* a_scale, const float* b_scale, void* D, int64_t ldd,

@@ -46,8 +46,6 @@ struct FusedQuantArgs {
 cudaError_t fused_quant_launch(int prod, int mode, int x_dtype, const FusedQuantArgs& a, cudaStream_t st);
 cudaError_t quant_fp8_tensor(const void* x, int x_dtype, uint8_t* q, float* s, float* s_repeat, int64_t n,
                              int64_t rows, int is_static, cudaStream_t st);
-cudaError_t broadcast_scales(const float* a_scale, const float* b_scale, float* as, float* bs, int m, int n,
-                             cudaStream_t st);
 
 // moe.cu
 cudaError_t moe_align128(const int32_t* topk_ids, int n, int E, int32_t* sorted_ids, int32_t* tile_expert,
@@ -88,6 +86,7 @@ struct GemmArgs {
   // are shared by every batch entry
   int batch;
   int64_t a_batch_stride, w_batch_stride, d_batch_stride;
+  int scalar_scales;  // As / Bs are single per-tensor values (persistent kernel only)
 };
 
 enum GemmFlavor { GEMM_S8 = 0, GEMM_E4M3 = 1, GEMM_E4M3_BLOCK128 = 2 };

@@ -490,9 +490,7 @@ int b2_moe_combine(const void* y, int64_t ldy, const int32_t* inv_pos, const flo
   return B2_OK;
 }
 
-size_t b2_bmm_e4m3_workspace(int M, int N) {
-  return (static_cast<size_t>(M > 0 ? M : 0) + static_cast<size_t>(N > 0 ? N : 0)) * sizeof(float) + 512;
-}
+size_t b2_bmm_e4m3_workspace(int, int) { return 0; }
 
 int b2_bmm_e4m3(const uint8_t* A, int64_t lda, int64_t a_batch_stride, const uint8_t* W, int64_t ldw,
                 int64_t w_batch_stride, const float* a_scale, const float* b_scale, void* D, int64_t ldd,
@@ -501,27 +499,23 @@ int b2_bmm_e4m3(const uint8_t* A, int64_t lda, int64_t a_batch_stride, const uin
   if (int r = check_arch()) return r;
   if (batch < 0 || !a_scale || !b_scale) return fail(B2_ERR_ARG, "bmm_fp8: bad arguments");
   if (batch == 0 || M == 0) return B2_OK;
-  if (!workspace || workspace_bytes < b2_bmm_e4m3_workspace(M, N) || !aligned16(workspace))
-    return fail(B2_ERR_ARG, "bmm_fp8: workspace too small or misaligned (need %zu bytes)", b2_bmm_e4m3_workspace(M, N));
+  (void)workspace;
+  (void)workspace_bytes;  // kept in the signature (the reference op passes a cuBLASLt workspace); unused
   if (a_batch_stride % 16 != 0 || w_batch_stride % 16 != 0 || (d_batch_stride * 2) % 16 != 0)
     return fail(B2_ERR_ARG, "bmm_fp8: batch strides must keep every matrix 16-byte aligned");
-  float* as = static_cast<float*>(workspace);
-  float* bs = as + ((M + 63) & ~63);
-  if (int r = check_cuda(broadcast_scales(a_scale, b_scale, as, bs, M, N, static_cast<cudaStream_t>(stream)),
-                         "bmm_fp8 scale broadcast launch"))
-    return r;
-  count_launch();
   if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16 && out_dtype != B2_DTYPE_F32)
     return fail(B2_ERR_ARG, "bmm_fp8: out_dtype must be Half or BFloat16");
   const int ob = out_dtype == B2_DTYPE_F32 ? 4 : 2;
   if (int r = check_gemm_common(A, lda, W, ldw, D, ldd, ob, M, N, K)) return r;
   // ONE launch: the persistent GEMM in batched mode (3-D tensor maps, tiles enumerate batch-major)
   GemmArgs a{};
-  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = as; a.Bs = bs; a.bias = nullptr; a.bias_dtype = B2_DTYPE_BF16;
+  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = a_scale; a.Bs = b_scale; a.bias = nullptr;
+  a.bias_dtype = B2_DTYPE_BF16;
   a.D = D; a.ldd = ldd; a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K;
+  a.scalar_scales = 1;  // the epilogue reads the two per-tensor scales directly: no broadcast launch, no workspace
   a.batch = batch; a.a_batch_stride = a_batch_stride; a.w_batch_stride = w_batch_stride; a.d_batch_stride = d_batch_stride;
   char err[256];
-  int r = gemm_launch(GEMM_E4M3, a, batch > 1 ? (g_forced_config & 0xff) : g_forced_config, &g_last_config,
+  int r = gemm_launch(GEMM_E4M3, a, g_forced_config & 0xff, &g_last_config,
                       static_cast<cudaStream_t>(stream), err, sizeof(err));
   if (r) return fail(r, "bmm_fp8: %s", err);
   return B2_OK;

@@ -30,6 +30,7 @@ struct KernelParams {
   int out_dtype;
   const int32_t* tile_expert;  // grouped (MoE) mode: expert of every 128-row block of A (-1 = skip), else nullptr
   int batch;                   // batched mode (bmm_fp8): > 1 = the tensor maps are 3-D, tiles enumerate batch-major
+  int scalar_scales;           // As / Bs point at ONE fp32 value each (per-tensor scales: bmm_fp8)
   int M, N, K;
   int num_m_blocks, num_n_blocks, num_kb;
   int stages;

@@ -260,13 +260,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       if (!raw_out) {
         for (int c = epi_tid; c < BN; c += 128) {
           const int col = col_tile + c;
-          smem_bs[c] = col < p.N ? __ldg(Bs_e + col) : 0.f;
+          smem_bs[c] = col < p.N ? __ldg(Bs_e + (p.scalar_scales ? 0 : col)) : 0.f;
           smem_bias[c] = (has_bias && col < p.N) ? load_bias(p.bias, p.bias_dtype, col) : -0.f;  // x + (-0) == x bit for bit
         }
       }
       epi_bar_sync();
       float as = 0.f;
-      if (!raw_out && row < p.M) as = __ldg(p.As + row);
+      if (!raw_out && row < p.M) as = __ldg(p.As + (p.scalar_scales ? 0 : row));
 
       const long long w0 = p.prof ? clock64() : 0;
       mbar_wait(&acc_full[acc], acc_phase);
@@ -436,14 +436,15 @@ static size_t smem_bytes_for(int bn, int b_rows, int stages) {
   return static_cast<size_t>(stages) * (BM * BK + b_rows * BK) + fixed_smem(bn);
 }
 
-static const TileConfig& pick_config(int M, int N, int sms) {
+static const TileConfig& pick_config(int M, int N, int sms, int batch = 1) {
   int best = 3;
   double best_score = -1;
   for (int i = 0; i < kNumConfigs; ++i) {
     const TileConfig& c = kConfigs[i];
     if (c.cg == 2 && M <= BM) continue;  // the second CTA of the pair would only see padding rows
     const int units = sms / c.cg;
-    const long tiles = static_cast<long>((M + BM * c.cg - 1) / (BM * c.cg)) * ((N + c.bn - 1) / c.bn);
+    if (c.bn > 32 && c.bn / 2 >= N) continue;  // a tile more than twice as wide as the problem is mostly padding
+    const long tiles = static_cast<long>((M + BM * c.cg - 1) / (BM * c.cg)) * ((N + c.bn - 1) / c.bn) * batch;
     const long waves = (tiles + units - 1) / units;
     // fraction of useful rows in the M tiles (a 256-row tile on M = 300 is 41 % padding)
     const double m_fill = static_cast<double>(M) / (static_cast<double>((M + BM * c.cg - 1) / (BM * c.cg)) * BM * c.cg);
@@ -522,7 +523,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   // M in (32, 64]: still ahead on layers up to ~64 rows of W per SM (profiles/r01e_m64_probe.log: 9.4 vs 12.0 us on
   // 6144 x 4096, 15.7 vs 19.9 us on 7168 x 8192), behind on the widest ones where 128 x 256 persistent tiles stream well
   // (short K -- 8 K-blocks -- leaves the decode kernel nothing to pipeline at M > 32: 8.2 vs 6.8 us on 8192 x 1024)
-  const bool decode_shape = a.tile_expert == nullptr && a.batch <= 1 && (
+  const bool decode_shape = a.tile_expert == nullptr && a.batch <= 1 && !a.scalar_scales && (
       a.M <= 32 || (a.M <= 64 && a.N <= 64 * sms && a.K >= 2048) || (a.M <= BM && a.N < 32 * sms));
   if (a.mc_slot != nullptr && !(decode_shape || a.M <= BM)) {
     snprintf(err, err_len, "multicast push epilogue is built for decode shapes (M <= 128) only");
@@ -530,9 +531,9 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   }
   if (a.x != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
   if (a.mc_slot != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
-  if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert && a.batch <= 1) : ((forced_config & 0xff) == 0 && decode_shape))
+  if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert && a.batch <= 1 && !a.scalar_scales) : ((forced_config & 0xff) == 0 && decode_shape))
     return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);
-  const TileConfig* cfg = &pick_config(a.M, a.N, sms);
+  const TileConfig* cfg = &pick_config(a.M, a.N, sms, a.batch > 1 ? a.batch : 1);
   const int forced_debug = forced_config >> 8;  // developer experiments ride in the upper bits of the forced id
   forced_config &= 0xff;
   if (forced_config >= 1 && forced_config <= kNumConfigs) cfg = &kConfigs[forced_config - 1];
@@ -563,6 +564,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   p.out_dtype = a.out_dtype;
   p.tile_expert = a.tile_expert;
   p.batch = a.batch > 1 ? a.batch : 1;
+  p.scalar_scales = a.scalar_scales;
   p.M = a.M;
   p.N = a.N;
   p.K = a.K;

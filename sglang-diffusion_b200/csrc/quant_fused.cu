@@ -418,19 +418,4 @@ cudaError_t quant_fp8_tensor(const void* x, int x_dtype, uint8_t* q, float* s, f
   return tensor_quant_t<__half>(x, q, s, s_repeat, n, rows, is_static, st);
 }
 
-// fill As[m] = *a_scale, Bs[n] = *b_scale (bmm_fp8: per-tensor scales feeding the per-row / per-column epilogue)
-__global__ void broadcast_scales_kernel(const float* __restrict__ a_scale, const float* __restrict__ b_scale,
-                                        float* __restrict__ as, float* __restrict__ bs, int m, int n) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < m) as[i] = *a_scale;
-  if (i < n) bs[i] = *b_scale;
-}
-
-cudaError_t broadcast_scales(const float* a_scale, const float* b_scale, float* as, float* bs, int m, int n,
-                             cudaStream_t st) {
-  const int mx = m > n ? m : n;
-  broadcast_scales_kernel<<<(mx + 255) / 256, 256, 0, st>>>(a_scale, b_scale, as, bs, m, n);
-  return cudaGetLastError();
-}
-
 }  // namespace b2

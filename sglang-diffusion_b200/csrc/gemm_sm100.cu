@@ -518,7 +518,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   if (flavor == GEMM_E4M3_BLOCK128) return gemm_launch_blockwise(a, forced_config, used_config, st, err, err_len);
   const int sms = device_sm_count();
   // decode shapes (HBM-bound on the weight bytes): cluster split-K kernel of gemm_splitk_sm100.cu
-  // (measured, profiles/r01c_sweep_splitk.log: it wins whenever the activation box is small, and for any M <= 128
+  // (measured, profiles/r01c_sweep_splitk_planned.log: it wins whenever the activation box is small, and for any M <= 128
   // when N is too narrow to give the persistent kernel one tile per SM)
   // M in (32, 64]: still ahead on layers up to ~64 rows of W per SM (profiles/r01e_m64_probe.log: 9.4 vs 12.0 us on
   // 6144 x 4096, 15.7 vs 19.9 us on 7168 x 8192), behind on the widest ones where 128 x 256 persistent tiles stream well

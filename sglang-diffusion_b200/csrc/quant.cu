@@ -388,7 +388,7 @@ cudaError_t quant_fp8_group128(const void* x, int x_dtype, int64_t ldx, uint8_t*
     const char* e = getenv("B2_GQ_GROUPS");
     return e ? atoi(e) : 0;
   }();
-  int gq = (gpr >= 4 && static_cast<int64_t>((M + 15) / 16) * (gpr / 4) >= 2 * 148) ? 4 : 2;  // measured (profiles/r01c_group_quant.md): 8 costs registers and occupancy
+  int gq = (gpr >= 4 && static_cast<int64_t>((M + 15) / 16) * (gpr / 4) >= 2 * 148) ? 4 : 2;  // measured (profiles/r02i_group_quant.md): 2 and 8 groups per thread are both slower
   if (forced == 2 || forced == 4 || forced == 8) gq = forced;
 #define B2_GQ_CASE(T_)                                                                                             \
   switch (gq) {                                                                                                    \

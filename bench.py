@@ -682,7 +682,7 @@ def main():
     if not args.no_e2e:
         host_layers = []
         for (x, W, Bs, b) in probs:
-            hl = b2.HostW8A8Int8Linear(W, Bs, b, device=dev, chunk_rows=min(1024, M))
+            hl = b2.HostW8A8Int8Linear(W, Bs, b, device=dev, chunk_rows=min(int(os.environ.get("B2_E2E_CHUNK", "2048")), M))
             xh = torch.empty(x.shape, dtype=torch.bfloat16).pin_memory()
             xh.copy_(x)
             oh = torch.empty(M, W.shape[0], dtype=torch.bfloat16).pin_memory()

@@ -20,7 +20,7 @@ from . import capi
 
 class HostW8A8Int8Linear:
     def __init__(self, weight: torch.Tensor, weight_scale: torch.Tensor, bias: Optional[torch.Tensor] = None,
-                 device: Optional[torch.device] = None, chunk_rows: int = 1024,
+                 device: Optional[torch.device] = None, chunk_rows: int = 2048,
                  act_dtype: torch.dtype = torch.bfloat16):
         """weight: int8 [N,K] (checkpoint layout), weight_scale: fp32 [N] / [N,1], bias: [N] or None."""
         assert weight.dtype == torch.int8 and weight.dim() == 2

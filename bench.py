@@ -354,6 +354,7 @@ def tp_leg(b2, dev, dist, world, rank, comm):
             for _, par, _, _, _, layer in layers:
                 layer.symm_comm = comm if (mode != "nccl" and par == "row") else None
                 layer.symm_fused_push = mode == "b2_fused_push"
+                layer.symm_force = mode != "nccl"  # measure the named path even where the layer's own policy prefers NCCL
             if mode != "nccl" and (comm is None or not comm.fits(M, 8192, torch.bfloat16)):
                 res[mode] = None
                 continue
@@ -385,6 +386,7 @@ def tp_leg(b2, dev, dist, world, rank, comm):
         for *_, layer in layers:
             layer.symm_comm = None
             layer.symm_fused_push = None
+            layer.symm_force = False
         res["allreduce_bytes_per_row_layer"] = M * 8192 * 2
         rows.append(res)
     check["max_rel_err"] = round(check["max_rel_err"], 5)

@@ -229,6 +229,10 @@ class QuantLinear(torch.nn.Module):
                 return comm.reduce_gathered(M, N, x.dtype).view(*x.shape[:-1], N)
         if not comm.fits(M, N, x.dtype):
             return None
+        # prefill-sized messages: the NVSwitch two-shot kernel is ahead of NCCL on 8 ranks (1407 vs 1471 us per decoder
+        # layer at M = 8192) and behind it on 2 and 4 (profiles/r02j_bench_2gpu.json, r02t_bench_4gpu.json)
+        if (M * N * x.dtype.itemsize > (8 << 20) and comm.world < 8 and not getattr(self, "symm_force", False)):
+            return None
         with capi.static_weights():
             if isinstance(self.quant_method, W8A8Int8LinearMethod):
                 q, s = ops.per_token_quant_int8(x2d)

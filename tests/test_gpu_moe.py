@@ -141,3 +141,20 @@ def test_moe_method_mirror_and_graph_capture():
     graph.replay()
     torch.cuda.synchronize()
     assert torch.equal(out.view(torch.int16), eager.view(torch.int16))
+
+
+def test_fused_experts_f16_activations():
+    """f16 hidden states (the other activation dtype of the linear methods): same routing and weights as a bf16 run,
+    outputs agree to the activation rounding."""
+    T, E, topk, H, I = 200, 8, 2, 1024, 512
+    tw, ids = _routing(T, E, topk, 11)
+    g = torch.Generator().manual_seed(4)
+    x = (torch.randn(T, H, generator=g) / 10)
+    w13 = torch.randint(-127, 128, (E, 2 * I, H), dtype=torch.int8, generator=g).to(DEV)
+    w2 = torch.randint(-127, 128, (E, H, I), dtype=torch.int8, generator=g).to(DEV)
+    s13 = (torch.rand(E, 2 * I, 1, generator=g) * 2e-3).to(DEV)
+    s2 = (torch.rand(E, H, 1, generator=g) * 2e-3).to(DEV)
+    o16 = b2.fused_experts(x.half().to(DEV), w13, w2, tw.to(DEV), ids.to(DEV), s13, s2)
+    obf = b2.fused_experts(x.bfloat16().to(DEV), w13, w2, tw.to(DEV), ids.to(DEV), s13, s2)
+    assert o16.dtype == torch.float16 and bool(torch.isfinite(o16).all())
+    assert ((o16.float() - obf.float()).norm() / obf.float().norm()).item() < 2e-2

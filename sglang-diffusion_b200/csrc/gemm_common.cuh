@@ -31,6 +31,7 @@ struct KernelParams {
   const int32_t* tile_expert;  // grouped (MoE) mode: expert of every 128-row block of A (-1 = skip), else nullptr
   int batch;                   // batched mode (bmm_fp8): > 1 = the tensor maps are 3-D, tiles enumerate batch-major
   int scalar_scales;           // As / Bs point at ONE fp32 value each (per-tensor scales: bmm_fp8)
+  int tail_tiles;              // BN = 256: tiles of the ragged last wave that are issued as two half-width work items
   int M, N, K;
   int num_m_blocks, num_n_blocks, num_kb;
   int stages;
@@ -43,7 +44,7 @@ struct KernelParams {
   // for an accumulator (warp 2), [4]=CTA lifetime, [5]=epilogue waits for a staging buffer (TMA store read),
   // [6]=epilogue waits for tcgen05.ld, [7]=epilogue tile bodies in total; all in SM clocks
   unsigned long long* prof;
-  int debug_flags;  // developer experiments (env B2_GEMM_DEBUG): 1 = skip the MMAs, 2 = skip the epilogue body, 4 = skip the loads
+  int debug_flags;  // developer experiments (env B2_GEMM_DEBUG): 1 = skip the MMAs, 2 = skip the epilogue body, 4 = skip the loads, 8 = no tail split
 };
 
 B2_DEVICE void tile_coords(int tile, const KernelParams& p, int& m_blk, int& n_blk) {

@@ -71,7 +71,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   const int lane = threadIdx.x & 31;
   const long long t_start = p.prof ? clock64() : 0;
   const int tiles_pb = p.num_m_blocks * p.num_n_blocks;  // tiles of (BM*CG) x BN per batch entry
-  const int num_tiles = tiles_pb * (p.batch > 1 ? p.batch : 1);
+  const int num_tiles_full = tiles_pb * (p.batch > 1 ? p.batch : 1);
+  // Tail split (BN = 256 only): the last `tail_tiles` tiles of the raster order -- the ragged last wave -- are issued
+  // as two half-width (BN/2) work items each, so a last wave that would occupy less than half of the CTAs for a whole
+  // tile time takes half a tile time instead.  Work item i >= full_items is half (i - full_items) & 1 of tile
+  // full_items + (i - full_items) / 2.  The B box is still loaded whole (row offset shifted), the MMA runs with N/2.
+  const int full_items = num_tiles_full - p.tail_tiles;
+  const int num_tiles = num_tiles_full + p.tail_tiles;  // work items
   const int cta_rank = CG == 1 ? 0 : static_cast<int>(cluster_ctarank());
   const int unit = CG == 1 ? static_cast<int>(blockIdx.x) : static_cast<int>(blockIdx.x >> 1);
   const int num_units = CG == 1 ? static_cast<int>(gridDim.x) : static_cast<int>(gridDim.x >> 1);
@@ -114,12 +120,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       long long prof_wait = 0;
       for (int tile = unit; tile < num_tiles; tile += num_units) {
         int m_blk, n_blk;
-        const int bidx = p.batch > 1 ? tile / tiles_pb : 0;  // batched mode: tiles enumerate batch-major
-        tile_coords(tile - bidx * tiles_pb, p, m_blk, n_blk);
+        const int half = tile >= full_items ? ((tile - full_items) & 1) : -1;
+        const int tidx = tile >= full_items ? full_items + ((tile - full_items) >> 1) : tile;
+        const int bidx = p.batch > 1 ? tidx / tiles_pb : 0;  // batched mode: tiles enumerate batch-major
+        tile_coords(tidx - bidx * tiles_pb, p, m_blk, n_blk);
         const int expert = p.tile_expert ? __ldg(p.tile_expert + m_blk) : 0;  // grouped (MoE) mode: CG == 1
         if (expert < 0) continue;  // a padding block past the last routed token
         const int m_row = (m_blk * CG + cta_rank) * BM;
-        const int n_row = expert * p.N + n_blk * BN + cta_rank * B_ROWS;
+        const int n_row = half < 0 ? expert * p.N + n_blk * BN + cta_rank * B_ROWS
+                                   : n_blk * BN + half * (BN / 2) + cta_rank * (B_ROWS / 2);
         for (int kb = 0; kb < p.num_kb; ++kb) {
           const long long w0 = p.prof ? clock64() : 0;
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -166,14 +175,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     // ======================================================= MMA issuer ====
     // whole warp in the loop, one elected lane (always the same one) issues every MMA and commit
     if (cta_rank == 0) {
-      constexpr uint32_t idesc = make_idesc<KIND>(BM * CG, BN);
+      constexpr uint32_t idesc_full = make_idesc<KIND>(BM * CG, BN);
+      constexpr uint32_t idesc_half = make_idesc<KIND>(BM * CG, BN >= 64 ? BN / 2 : BN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
       long long prof_full = 0, prof_acc = 0;
       for (int tile = unit; tile < num_tiles; tile += num_units) {
-        if (p.tile_expert) {  // (never together with the batched mode)
+        const uint32_t idesc = tile >= full_items ? idesc_half : idesc_full;
+        if (p.tile_expert) {  // (never together with the batched mode or the tail split)
           int m_blk, n_blk;
           tile_coords(tile, p, m_blk, n_blk);
           if (__ldg(p.tile_expert + m_blk) < 0) continue;
@@ -244,21 +255,24 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     const int swz = BOX_BYTES == 128 ? (lane & 7) : ((lane >> 1) & 3);
     for (int tile = unit; tile < num_tiles; tile += num_units) {
       int m_blk, n_blk;
-      const int bidx = p.batch > 1 ? tile / tiles_pb : 0;
-      tile_coords(tile - bidx * tiles_pb, p, m_blk, n_blk);
+      const int half = tile >= full_items ? ((tile - full_items) & 1) : -1;
+      const int tidx = tile >= full_items ? full_items + ((tile - full_items) >> 1) : tile;
+      const int bidx = p.batch > 1 ? tidx / tiles_pb : 0;
+      tile_coords(tidx - bidx * tiles_pb, p, m_blk, n_blk);
       const int expert = p.tile_expert ? __ldg(p.tile_expert + m_blk) : 0;
       if (expert < 0) continue;
       const float* Bs_e = p.Bs + static_cast<size_t>(expert) * p.N;  // per-expert channel scales [E, N]
       const int row0 = (m_blk * CG + cta_rank) * BM + quarter * 32;
       const int row = row0 + lane;
-      const int col_tile = n_blk * BN;
+      const int col_tile = n_blk * BN + (half > 0 ? BN / 2 : 0);
+      const int nch = half < 0 ? NCH : NCH / 2;  // 32-column chunks of this work item
 
       // Per-column scale and bias of this tile -> shared memory, once, while the main loop of the tile is
       // still running (the four warps read them back as conflict-free broadcasts).  Columns beyond N get 0;
       // the TMA store clips them.
       epi_bar_sync();  // every warp is done with the previous tile's values
       if (!raw_out) {
-        for (int c = epi_tid; c < BN; c += 128) {
+        for (int c = epi_tid; c < nch * 32; c += 128) {
           const int col = col_tile + c;
           smem_bs[c] = col < p.N ? __ldg(Bs_e + (p.scalar_scales ? 0 : col)) : 0.f;
           smem_bias[c] = (has_bias && col < p.N) ? load_bias(p.bias, p.bias_dtype, col) : -0.f;  // x + (-0) == x bit for bit
@@ -280,11 +294,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         // while chunk c is scaled, cast and staged.  The loop over PAIRS of chunks stays rolled -- fully unrolled
         // the body is ~40 KB of SASS and the four epilogue warps stall on instruction fetch.
         uint32_t r[2][32];
-        constexpr int NPAIR = NCH >= 2 ? NCH / 2 : 1;
         constexpr int CH_PER_PAIR = NCH >= 2 ? 2 : 1;
+        const int npair = nch >= 2 ? nch / 2 : 1;
         tmem_ld_32x32b_x32(t_row, r[0]);
 #pragma unroll 1
-        for (int pr = 0; pr < NPAIR; ++pr) {
+        for (int pr = 0; pr < npair; ++pr) {
 #pragma unroll
           for (int hh = 0; hh < CH_PER_PAIR; ++hh) {
             const int c = pr * CH_PER_PAIR + hh;      // chunk index inside the tile
@@ -295,7 +309,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
               tmem_ld_wait();
               if (p.prof) prof_ld += clock64() - l0;
             }
-            if (c + 1 < NCH) {
+            if (c + 1 < nch) {
               tmem_ld_32x32b_x32(t_row + static_cast<uint32_t>((c + 1) * 32), r[(hh + 1) & 1]);
             } else {
               // accumulator fully read: hand the TMEM buffer back to the MMA warp before the last chunk's math
@@ -565,6 +579,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   p.tile_expert = a.tile_expert;
   p.batch = a.batch > 1 ? a.batch : 1;
   p.scalar_scales = a.scalar_scales;
+  p.tail_tiles = 0;
   p.M = a.M;
   p.N = a.N;
   p.K = a.K;
@@ -615,7 +630,20 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   }
   const int tiles = p.num_m_blocks * p.num_n_blocks * p.batch;
   const int units = sms / cg;
-  const int grid = (tiles < units ? tiles : units) * cg;
+  {
+    // tail split: when the ragged last wave has at most half a wave of 256-wide tiles, issue them as twice as many
+    // 128-wide work items (see the kernel).  N = 5120, K = 13824, M = 4096: 320 tiles on 74 CTA pairs = 4 waves + 24 ->
+    // 48 half tiles: 4.5 tile times instead of 5.
+    static const bool tail_on = [] {
+      const char* e = getenv("B2_GEMM_TAIL_SPLIT");
+      return !(e && e[0] == '0');
+    }();
+    const int rem = tiles % units;
+    if (tail_on && !(p.debug_flags & 8) && bn == 256 && !a.tile_expert && p.batch == 1 && rem > 0 && rem * 2 <= units && a.N % 128 == 0)
+      p.tail_tiles = rem;
+  }
+  const int items = tiles + p.tail_tiles;
+  const int grid = (items < units ? items : units) * cg;
   const size_t smem = smem_bytes_for(bn, b_rows, p.stages);
   const int out_kind = a.out_dtype == B2_DTYPE_BF16 ? 0 : (a.out_dtype == B2_DTYPE_F16 ? 1 : 2);
   if (flavor == GEMM_S8) {

@@ -387,6 +387,41 @@ def tp_leg(b2, dev, dist, world, rank, comm):
             layer.symm_comm = None
             layer.symm_fused_push = None
             layer.symm_force = False
+        if M >= 32 * world and M % (32 * world) == 0:
+            # prefill, row-sharded sum (RowParallelLinear(skip_all_reduce) + LayerCommunicator._tp_reduce_scatter of the
+            # reference): GEMM + NCCL reduce_scatter_tensor against the GEMM's scatter epilogue + one local sum
+            def step_rs():
+                for x, (_, par, _, _, _, layer) in zip(xs, layers):
+                    layer.forward_reduce_scatter(x) if par == "row" else layer(x)
+
+            for mode in ("nccl_reduce_scatter", "b2_fused_reduce_scatter"):
+                fused = mode == "b2_fused_reduce_scatter"
+                if fused and (comm is None or not comm.fits_scatter(M, 8192, torch.bfloat16)):
+                    res[mode] = None
+                    continue
+                for _, par, _, _, _, layer in layers:
+                    layer.symm_comm = comm if (fused and par == "row") else None
+                ms = _time_device(step_rs, dev, dist, world, 10)
+                per_layer = {}
+                for x, (name, par, K, N, _, layer) in zip(xs, layers):
+                    if par == "row":
+                        per_layer[name] = round(_time_device(lambda: layer.forward_reduce_scatter(x), dev, dist, world, 5) * 1e3, 1)
+                res[mode] = {"us_per_decoder_layer_linears": round(ms * 1e3, 1), "us_per_row_layer": per_layer}
+                if fused:
+                    # against the NCCL reduce-scatter of the same partials (different summation order: one bf16 ulp)
+                    for x, (name, par, K, N, _, layer) in zip(xs, layers):
+                        if par != "row":
+                            continue
+                        got = layer.forward_reduce_scatter(x).float()
+                        layer.symm_comm = None
+                        want = layer.forward_reduce_scatter(x).float()
+                        layer.symm_comm = comm
+                        err = ((got - want).abs().max() / want.abs().max()).item()
+                        check["fused_reduce_scatter_vs_nccl_max_rel_err"] = max(check.get("fused_reduce_scatter_vs_nccl_max_rel_err", 0.0), round(err, 5))
+                        check["ok"] = check["ok"] and err < 1.6e-2
+            for *_, layer in layers:
+                layer.symm_comm = None
+            res["nvlink_bytes_out_per_rank_per_row_layer_reduce_scatter"] = (world - 1) * M * 8192 * 2 // world
         res["allreduce_bytes_per_row_layer"] = M * 8192 * 2
         rows.append(res)
     check["max_rel_err"] = round(check["max_rel_err"], 5)
@@ -767,7 +802,7 @@ def main():
         try:
             from sglang_diffusion_b200.comm import SymmAllReduce
 
-            comm = SymmAllReduce(max_bytes=128 << 20, device=dev)
+            comm = SymmAllReduce(max_bytes=256 << 20, device=dev)  # two sets of M = 8192 x N = 8192 bf16 partials
             SymmAllReduce.set_timeout_ms(20000)  # a lost rank must not hang the box; checked below
         except Exception as e:  # noqa: BLE001
             comm = None

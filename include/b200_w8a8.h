@@ -271,16 +271,43 @@ int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* signal_pads_d
  * Step 2, b2_allreduce_symm_gathered: ONE barrier ("every rank's GEMM has completed") and a sum over the `world` slots
  * of LOCAL memory in rank order (fp32, one rounding): bit-identical on every rank and equal to algo 1 of
  * b2_allreduce_symm.  Every rank must make the same sequence of calls; the signal pads are the ones of
- * b2_allreduce_symm (same ownership rule).  bias: added by the GEMM (give it on one rank only, linear.py:1480). */
+ * b2_allreduce_symm (same ownership rule).  bias: added by the GEMM (give it on one rank only, linear.py:1480).
+ * set_stride_bytes: distance of the two sets inside the gather buffer, the same on every call that shares the buffer
+ * (half of it; a multiple of 16; 0 = world * M * N * 2, only safe when every call has the same size). */
 int b2_gemm_s8_push_symm(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
-                         const void* bias, int bias_dtype, void* multicast_ptr, uint32_t* local_signal_pad, int rank,
-                         int world, int out_dtype, int M, int N, int K, b2_stream_t stream);
+                         const void* bias, int bias_dtype, void* multicast_ptr, uint32_t* local_signal_pad,
+                         int64_t set_stride_bytes, int rank, int world, int out_dtype, int M, int N, int K,
+                         b2_stream_t stream);
 int b2_gemm_e4m3_push_symm(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* As,
                            const float* Bs, const void* bias, int bias_dtype, void* multicast_ptr,
-                           uint32_t* local_signal_pad, int rank, int world, int out_dtype, int M, int N, int K,
-                           b2_stream_t stream);
+                           uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world, int out_dtype,
+                           int M, int N, int K, b2_stream_t stream);
 int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const* signal_pads_dev, void* out, int64_t numel,
-                               int dtype, int rank, int world, int max_blocks, b2_stream_t stream);
+                               int64_t set_stride_bytes, int dtype, int rank, int world, int max_blocks,
+                               b2_stream_t stream);
+
+/* Prefill form (M >= 32 * world): GEMM with a SCATTER epilogue + the same gathered sum = a fused reduce-scatter.
+ * The sum of a row-parallel layer is only needed row-sharded when the next operation is token-wise (sequence-parallel
+ * norm / quantizer, or an all-gather later): each rank then keeps rows [rank * M/world, (rank+1) * M/world).  The
+ * persistent GEMM stores every 32-row output box straight into slot `rank` of the OWNING rank's gather buffer (TMA
+ * store over NVLink to the peer mapping, tile by tile under the main loop of the next tile), so after ONE barrier
+ * b2_allreduce_symm_gathered(local_buf, pads, out, (M/world)*N, set_stride_bytes, ...) sums `world` slots of local memory
+ * into out[M/world, N] -- fp32 in rank order, one rounding: equal bit for bit to rows of algo 1 of b2_allreduce_symm.
+ * NVLink traffic per rank: (world-1)/world * M*N*2 bytes out, the same in; no separate pass over the partials.
+ * peer_bufs_host: HOST array of the `world` ranks' gather buffers as mapped into this process (symmetric memory
+ * buffer_ptrs); each holds 2 sets set_stride_bytes apart of `world` slots of (M/world)*N 16-bit elements.
+ * Needs M % (32 * world) == 0, N % 8 == 0.  Replaces: RowParallelLinear.forward(skip_all_reduce=True)
+ * (python/sglang/srt/layers/linear.py:1467-1490) followed by LayerCommunicator._tp_reduce_scatter
+ * (python/sglang/srt/layers/communicator.py:542-560 -> GroupCoordinator.reduce_scatter_tensor,
+ * python/sglang/srt/distributed/parallel_state.py:758-762). */
+int b2_gemm_s8_scatter_symm(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As,
+                            const float* Bs, const void* bias, int bias_dtype, void* const* peer_bufs_host,
+                            uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world, int out_dtype,
+                            int M, int N, int K, b2_stream_t stream);
+int b2_gemm_e4m3_scatter_symm(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* As,
+                              const float* Bs, const void* bias, int bias_dtype, void* const* peer_bufs_host,
+                              uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world,
+                              int out_dtype, int M, int N, int K, b2_stream_t stream);
 
 /* Waits of b2_allreduce_symm on a peer.  0 (default): wait for ever -- a late peer (first-iteration skew, weight load,
  * debugger) is not an error, hangs are the host watchdog's business, as with the reference's custom all-reduce.

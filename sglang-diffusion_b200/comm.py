@@ -44,6 +44,10 @@ class SymmAllReduce:
         # word 1536 the time-out record.  The pad of this handle is owned by b2_allreduce_symm (barrier numbers only
         # grow and are never reset): do not call handle.barrier() / put_signal() / wait_signal() on it.
         self.max_blocks = min(128, 1024 // self.world)
+        # gather form (push / scatter epilogues): two sets, a fixed half buffer apart whatever the size of the call
+        self.set_stride = (self.max_bytes // 2) // 16 * 16
+        import ctypes
+        self._peer_bufs_host = (ctypes.c_void_p * self.world)(*[int(p) for p in self.handle.buffer_ptrs])
         need = 4 * (1536 + 1)
         if int(self.handle.signal_pad_size) < need:
             raise ValueError(f"signal pad of {self.handle.signal_pad_size} bytes is smaller than the {need} b2_allreduce_symm needs")
@@ -64,7 +68,7 @@ class SymmAllReduce:
         """The decode-shape GEMM can push its partials through the multicast mapping: needs the NVSwitch mapping, M <=
         128 and room for two sets of `world` slots."""
         return (self.multicast_ptr != 0 and dtype in _DT and 0 < M <= 128 and (M * N) % 8 == 0
-                and 2 * self.world * M * N * dtype.itemsize <= self.max_bytes)
+                and self.world * M * N * dtype.itemsize <= self.set_stride)
 
     def push_gemm(self, q: torch.Tensor, weight: torch.Tensor, a_scale: torch.Tensor, w_scale: torch.Tensor,
                   out_dtype: torch.dtype, bias: Optional[torch.Tensor] = None) -> None:
@@ -79,17 +83,45 @@ class SymmAllReduce:
             capi.check(fn(q.data_ptr(), q.stride(0) if M > 1 else K, weight.data_ptr(), weight.stride(1) if N > 1 else K,
                           a_scale.data_ptr(), w_scale.data_ptr(), None if bias is None else bias.data_ptr(),
                           bdt[bias.dtype] if bias is not None else capi.DTYPE_F32, self.multicast_ptr,
-                          int(self.handle.signal_pad_ptrs[self.rank]), self.rank, self.world, _DT[out_dtype], M, N, K,
-                          torch.cuda.current_stream(q.device).cuda_stream))
+                          int(self.handle.signal_pad_ptrs[self.rank]), self.set_stride, self.rank, self.world,
+                          _DT[out_dtype], M, N, K, torch.cuda.current_stream(q.device).cuda_stream))
 
     def reduce_gathered(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
         """Barrier + rank-ordered fp32 sum of the `world` pushed slots (local memory) -> fresh [M,N] tensor."""
         out = torch.empty(M, N, dtype=dtype, device=self.device)
         with torch.cuda.device(self.device):
             capi.check(capi.lib.b2_allreduce_symm_gathered(self.buf.data_ptr(), self.pads_dev, out.data_ptr(), M * N,
-                                                           _DT[dtype], self.rank, self.world, self.max_blocks,
+                                                           self.set_stride, _DT[dtype], self.rank, self.world,
+                                                           self.max_blocks,
                                                            torch.cuda.current_stream(self.device).cuda_stream))
         return out
+
+    # ---- prefill: scatter epilogue + gathered sum = fused reduce-scatter (b2_gemm_*_scatter_symm) ----
+
+    def fits_scatter(self, M: int, N: int, dtype: torch.dtype) -> bool:
+        """The persistent GEMM can store every rank's rows straight into that rank's gather buffer."""
+        return (dtype in _DT and M > 0 and M % (32 * self.world) == 0 and N % 8 == 0
+                and M * N * dtype.itemsize <= self.set_stride)
+
+    def scatter_gemm(self, q: torch.Tensor, weight: torch.Tensor, a_scale: torch.Tensor, w_scale: torch.Tensor,
+                     out_dtype: torch.dtype, bias: Optional[torch.Tensor] = None) -> None:
+        """int8 / e4m3 scaled GEMM whose epilogue stores rows [r*M/world, (r+1)*M/world) of this rank's partial output
+        into slot `rank` of rank r's gather buffer (TMA stores to the peer mappings)."""
+        M, K = q.shape
+        N = weight.shape[1]
+        assert weight.shape[0] == K and weight.stride(0) == 1 and q.stride(1) == 1
+        fn = capi.lib.b2_gemm_s8_scatter_symm if q.dtype == torch.int8 else capi.lib.b2_gemm_e4m3_scatter_symm
+        bdt = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16, torch.float32: capi.DTYPE_F32}
+        with torch.cuda.device(q.device):
+            capi.check(fn(q.data_ptr(), q.stride(0), weight.data_ptr(), weight.stride(1) if N > 1 else K,
+                          a_scale.data_ptr(), w_scale.data_ptr(), None if bias is None else bias.data_ptr(),
+                          bdt[bias.dtype] if bias is not None else capi.DTYPE_F32, self._peer_bufs_host,
+                          int(self.handle.signal_pad_ptrs[self.rank]), self.set_stride, self.rank, self.world,
+                          _DT[out_dtype], M, N, K, torch.cuda.current_stream(q.device).cuda_stream))
+
+    def reduce_scattered(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
+        """Barrier + rank-ordered fp32 sum of the `world` slots of this rank's rows -> fresh [M / world, N] tensor."""
+        return self.reduce_gathered(M // self.world, N, dtype)
 
     def partial(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
         """[M,N] view of the local symmetric buffer: the GEMM's output operand."""

@@ -216,23 +216,49 @@ __global__ void __launch_bounds__(512) allreduce_one_shot_kernel(uint4* const* b
 // one-shot kernel above).  Two sets alternate so that a rank may start pushing call n+2 while a slow peer still sums
 // call n+1; call n's readers are done by then: the pusher has passed barrier n+1, which every peer only enters after
 // its call-n kernel completed.  The counter lives in the signal pad so that CUDA-graph replays advance it.
+// The two sets sit a FIXED stride apart (set_vec, half the buffer on the Python side): with a size-dependent stride a
+// call of a different size could land its set (n+1)&1 inside the region a slow peer is still summing for call n.
+// The same kernel finishes the scatter epilogue of the prefill GEMM (gemm_sm100.cu, RS): there every rank's slots hold
+// only the rows it owns, and `out` is this rank's [M / world, N] share of the sum (a reduce-scatter).
 constexpr int kGatherCounterWord = 1024 + 520;
 constexpr int kGatherDoneWord = 1024 + 521;
 
 template <bool BF16>
 __global__ void __launch_bounds__(512) allreduce_gathered_kernel(const uint4* __restrict__ local_buf,
                                                                   uint32_t* const* pads, uint4* __restrict__ out,
-                                                                  long long nvec, int rank, int world,
-                                                                  unsigned long long timeout_ns) {
+                                                                  long long nvec, long long set_vec, int rank,
+                                                                  int world, unsigned long long timeout_ns) {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");  // this rank's GEMM has completed: its pushes are performed
   uint32_t* pad = pads[rank];
   const uint32_t epoch = pad[kEpochWord + blockIdx.x];
   const uint32_t counter = pad[kGatherCounterWord];
   xgpu_barrier<true>(pads, rank, world, epoch + 1, timeout_ns);
-  const uint4* set = local_buf + static_cast<long long>(counter & 1u) * nvec * world;
+  const uint4* set = local_buf + static_cast<long long>(counter & 1u) * set_vec;
   const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
-  for (long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += stride) {
+  long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  // prefill-sized sums (the scatter form): four vectors per thread, 4 x world independent 16-byte loads in flight --
+  // with one vector per thread 128 CTAs keep ~2 MB in flight, a third of what HBM needs
+  for (; v + 3 * stride < nvec; v += 4 * stride) {
+    float acc[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) unpack8<BF16>(__ldcs(set + v + u * stride), acc[u]);
+    for (int r = 1; r < world; ++r) {
+      uint4 t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) t[u] = __ldcs(set + static_cast<long long>(r) * nvec + v + u * stride);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+        unpack8<BF16>(t[u], f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[u][i] = __fadd_rn(acc[u][i], f[i]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) out[v + u * stride] = pack8<BF16>(acc[u]);
+  }
+  for (; v < nvec; v += stride) {
     float acc[8];
     unpack8<BF16>(set[v], acc);
     for (int r = 1; r < world; ++r) {  // rank order: the same fp32 sum, bit for bit, on every rank
@@ -260,8 +286,8 @@ __global__ void __launch_bounds__(512) allreduce_gathered_kernel(const uint4* __
 using namespace b2;
 
 extern "C" int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const* signal_pads_dev, void* out,
-                                          int64_t numel, int dtype, int rank, int world, int max_blocks,
-                                          b2_stream_t stream);
+                                          int64_t numel, int64_t set_stride_bytes, int dtype, int rank, int world,
+                                          int max_blocks, b2_stream_t stream);
 
 #include <atomic>
 static std::atomic<long long> g_ar_timeout_ms{0};
@@ -329,8 +355,8 @@ extern "C" int b2_allreduce_symm(void* const* peer_bufs_dev, uint32_t* const* si
 }
 
 extern "C" int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const* signal_pads_dev, void* out,
-                                          int64_t numel, int dtype, int rank, int world, int max_blocks,
-                                          b2_stream_t stream) {
+                                          int64_t numel, int64_t set_stride_bytes, int dtype, int rank, int world,
+                                          int max_blocks, b2_stream_t stream) {
   if (!local_buf || !signal_pads_dev || !out) return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: null pointer");
   if (dtype != B2_DTYPE_BF16 && dtype != B2_DTYPE_F16)
     return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: dtype must be bfloat16 or float16");
@@ -340,6 +366,10 @@ extern "C" int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const
   if (reinterpret_cast<uintptr_t>(out) % 16 != 0 || reinterpret_cast<uintptr_t>(local_buf) % 16 != 0)
     return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: buffers must be 16-byte aligned");
   const long long nvec = numel / 8;
+  if (set_stride_bytes == 0) set_stride_bytes = numel * 2 * world;
+  if (set_stride_bytes % 16 != 0 || set_stride_bytes < numel * 2 * world)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered: set stride must be a multiple of 16 and hold world slots");
+  const long long set_vec = set_stride_bytes / 16;
   const int threads = 512;
   long long blocks = (nvec + threads - 1) / threads;
   if (blocks > max_blocks) blocks = max_blocks;
@@ -358,8 +388,8 @@ extern "C" int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const
   const uint4* lb = static_cast<const uint4*>(local_buf);
   uint4* o = static_cast<uint4*>(out);
   cudaError_t le = dtype == B2_DTYPE_BF16
-                       ? cudaLaunchKernelEx(&cfg, allreduce_gathered_kernel<true>, lb, signal_pads_dev, o, nvec, rank, world, tmo)
-                       : cudaLaunchKernelEx(&cfg, allreduce_gathered_kernel<false>, lb, signal_pads_dev, o, nvec, rank, world, tmo);
+                       ? cudaLaunchKernelEx(&cfg, allreduce_gathered_kernel<true>, lb, signal_pads_dev, o, nvec, set_vec, rank, world, tmo)
+                       : cudaLaunchKernelEx(&cfg, allreduce_gathered_kernel<false>, lb, signal_pads_dev, o, nvec, set_vec, rank, world, tmo);
   if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm_gathered launch: %s", cudaGetErrorString(le));
   count_launch();
   return B2_OK;

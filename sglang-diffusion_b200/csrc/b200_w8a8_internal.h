@@ -78,6 +78,12 @@ struct GemmArgs {
   void* mc_slot;
   long long mc_set_bytes;
   const uint32_t* mc_counter;
+  // prefill row-parallel layers: scatter epilogue of the persistent kernel (gemm_sm100.cu, RS).  rs_peer_bufs is a HOST
+  // array of the `rs_world` ranks' gather buffers (peer-mapped device addresses); D is unused
+  void* const* rs_peer_bufs;
+  int rs_world, rs_rank;
+  long long rs_set_bytes;
+  const uint32_t* rs_counter;
   // decode shapes (M <= 32): bf16 / f16 activations quantized inside the split-K kernel (A and As are then unused)
   const void* x;
   int64_t ldx;

@@ -344,8 +344,8 @@ extern "C" int b2_symm_gather_counter_word(void);
 
 static int gemm_push_symm(GemmFlavor flavor, const char* op, const void* A, int64_t lda, const void* W, int64_t ldw,
                           const float* As, const float* Bs, const void* bias, int bias_dtype, void* multicast_ptr,
-                          uint32_t* local_signal_pad, int rank, int world, int out_dtype, int M, int N, int K,
-                          b2_stream_t stream) {
+                          uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world, int out_dtype,
+                          int M, int N, int K, b2_stream_t stream) {
   if (int r = check_arch()) return r;
   if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16) return fail(B2_ERR_ARG, "%s: out_dtype must be Half or BFloat16", op);
   if (!multicast_ptr || !local_signal_pad || world < 2 || world > 8 || rank < 0 || rank >= world)
@@ -361,7 +361,10 @@ static int gemm_push_symm(GemmFlavor flavor, const char* op, const void* A, int6
   a.D = multicast_ptr; a.ldd = N; a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K;
   const long long slot = static_cast<long long>(M) * N * 2;
   a.mc_slot = static_cast<uint8_t*>(multicast_ptr) + slot * rank;
-  a.mc_set_bytes = slot * world;
+  if (set_stride_bytes == 0) set_stride_bytes = slot * world;
+  if (set_stride_bytes % 16 != 0 || set_stride_bytes < slot * world)
+    return fail(B2_ERR_ARG, "%s: set stride must be a multiple of 16 and hold world slots", op);
+  a.mc_set_bytes = set_stride_bytes;
   a.mc_counter = local_signal_pad + b2_symm_gather_counter_word();
   char err[256];
   int r = gemm_launch(flavor, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err, sizeof(err));
@@ -370,18 +373,70 @@ static int gemm_push_symm(GemmFlavor flavor, const char* op, const void* A, int6
 }
 
 int b2_gemm_s8_push_symm(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As, const float* Bs,
-                         const void* bias, int bias_dtype, void* multicast_ptr, uint32_t* local_signal_pad, int rank,
-                         int world, int out_dtype, int M, int N, int K, b2_stream_t stream) {
+                         const void* bias, int bias_dtype, void* multicast_ptr, uint32_t* local_signal_pad,
+                         int64_t set_stride_bytes, int rank, int world, int out_dtype, int M, int N, int K,
+                         b2_stream_t stream) {
   return gemm_push_symm(GEMM_S8, "int8_scaled_mm (push)", A, lda, W, ldw, As, Bs, bias, bias_dtype, multicast_ptr,
-                        local_signal_pad, rank, world, out_dtype, M, N, K, stream);
+                        local_signal_pad, set_stride_bytes, rank, world, out_dtype, M, N, K, stream);
 }
 
 int b2_gemm_e4m3_push_symm(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* As,
                            const float* Bs, const void* bias, int bias_dtype, void* multicast_ptr,
-                           uint32_t* local_signal_pad, int rank, int world, int out_dtype, int M, int N, int K,
-                           b2_stream_t stream) {
+                           uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world, int out_dtype,
+                           int M, int N, int K, b2_stream_t stream) {
   return gemm_push_symm(GEMM_E4M3, "fp8_scaled_mm (push)", A, lda, W, ldw, As, Bs, bias, bias_dtype, multicast_ptr,
-                        local_signal_pad, rank, world, out_dtype, M, N, K, stream);
+                        local_signal_pad, set_stride_bytes, rank, world, out_dtype, M, N, K, stream);
+}
+
+static int gemm_scatter_symm(GemmFlavor flavor, const char* op, const void* A, int64_t lda, const void* W, int64_t ldw,
+                             const float* As, const float* Bs, const void* bias, int bias_dtype,
+                             void* const* peer_bufs_host, uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank,
+                             int world, int out_dtype, int M, int N, int K, b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (out_dtype != B2_DTYPE_BF16 && out_dtype != B2_DTYPE_F16) return fail(B2_ERR_ARG, "%s: out_dtype must be Half or BFloat16", op);
+  if (!peer_bufs_host || !local_signal_pad || world < 2 || world > 8 || rank < 0 || rank >= world)
+    return fail(B2_ERR_ARG, "%s: peer buffers / signal pad / rank / world (2..8) invalid", op);
+  for (int r = 0; r < world; ++r)
+    if (!peer_bufs_host[r] || !aligned16(peer_bufs_host[r])) return fail(B2_ERR_ARG, "%s: gather buffer of rank %d is null or misaligned", op, r);
+  if (M <= 0 || M % (32 * world) != 0) return fail(B2_ERR_ARG, "%s: M=%d must be a positive multiple of 32 * world", op, M);
+  if (int r = check_gemm_common(A, lda, W, ldw, peer_bufs_host[rank], N, 2, M, N, K)) return r;
+  if (!As || !Bs || !aligned16(Bs)) return fail(B2_ERR_ARG, "%s: scales must not be null (Bs 16-byte aligned)", op);
+  if (bias && !aligned16(bias)) return fail(B2_ERR_ARG, "%s: bias must be 16-byte aligned", op);
+  if (bias && bias_dtype != B2_DTYPE_BF16 && bias_dtype != B2_DTYPE_F16 && bias_dtype != B2_DTYPE_F32)
+    return fail(B2_ERR_ARG, "%s: unsupported bias dtype", op);
+  if (N % 8 != 0) return fail(B2_ERR_ARG, "%s: N=%d must be a multiple of 8", op, N);
+  const long long slot = static_cast<long long>(M / world) * N * 2;
+  if (set_stride_bytes == 0) set_stride_bytes = slot * world;
+  if (set_stride_bytes % 16 != 0 || set_stride_bytes < slot * world)
+    return fail(B2_ERR_ARG, "%s: set stride must be a multiple of 16 and hold world slots", op);
+  GemmArgs a{};
+  a.A = A; a.lda = lda; a.W = W; a.ldw = ldw; a.As = As; a.Bs = Bs; a.bias = bias; a.bias_dtype = bias_dtype;
+  a.D = peer_bufs_host[rank]; a.ldd = N; a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K;
+  a.rs_peer_bufs = peer_bufs_host;
+  a.rs_world = world;
+  a.rs_rank = rank;
+  a.rs_set_bytes = set_stride_bytes;
+  a.rs_counter = local_signal_pad + b2_symm_gather_counter_word();
+  char err[256];
+  int r = gemm_launch(flavor, a, g_forced_config, &g_last_config, static_cast<cudaStream_t>(stream), err, sizeof(err));
+  if (r) return fail(r, "%s: %s", op, err);
+  return B2_OK;
+}
+
+int b2_gemm_s8_scatter_symm(const int8_t* A, int64_t lda, const int8_t* W, int64_t ldw, const float* As,
+                            const float* Bs, const void* bias, int bias_dtype, void* const* peer_bufs_host,
+                            uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world, int out_dtype,
+                            int M, int N, int K, b2_stream_t stream) {
+  return gemm_scatter_symm(GEMM_S8, "int8_scaled_mm (scatter)", A, lda, W, ldw, As, Bs, bias, bias_dtype, peer_bufs_host,
+                           local_signal_pad, set_stride_bytes, rank, world, out_dtype, M, N, K, stream);
+}
+
+int b2_gemm_e4m3_scatter_symm(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* As,
+                              const float* Bs, const void* bias, int bias_dtype, void* const* peer_bufs_host,
+                              uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world,
+                              int out_dtype, int M, int N, int K, b2_stream_t stream) {
+  return gemm_scatter_symm(GEMM_E4M3, "fp8_scaled_mm (scatter)", A, lda, W, ldw, As, Bs, bias, bias_dtype,
+                           peer_bufs_host, local_signal_pad, set_stride_bytes, rank, world, out_dtype, M, N, K, stream);
 }
 
 int b2_gemm_e4m3_block128(const uint8_t* A, int64_t lda, const uint8_t* W, int64_t ldw, const float* sfa,

@@ -31,6 +31,10 @@ struct KernelParams {
   const int32_t* tile_expert;  // grouped (MoE) mode: expert of every 128-row block of A (-1 = skip), else nullptr
   int batch;                   // batched mode (bmm_fp8): > 1 = the tensor maps are 3-D, tiles enumerate batch-major
   int scalar_scales;           // As / Bs point at ONE fp32 value each (per-tensor scales: bmm_fp8)
+  // scatter epilogue (row-parallel prefill, RS kernels): rows [r * rs_rows, (r + 1) * rs_rows) of the output belong to
+  // rank r and are stored into slot `rs_rank` of set (*rs_counter & 1) of rank r's gather buffer
+  const uint32_t* rs_counter;
+  int rs_rows, rs_rank;
   int tail_tiles;              // BN = 256: tiles of the ragged last wave that are issued as two half-width work items
   int M, N, K;
   int num_m_blocks, num_n_blocks, num_kb;
@@ -227,5 +231,29 @@ static inline bool make_tmap_3d(CUtensorMap* m, CUtensorMapDataType dt, int esiz
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }
+
+// [2 sets][world slots][rows][cols] gather buffer of one rank (16-bit elements): dims (cols, rows, slots, 2)
+static inline bool make_tmap_gather4d(CUtensorMap* m, CUtensorMapDataType dt, const void* base, uint64_t slots,
+                                      uint64_t rows, uint64_t cols, uint64_t set_bytes, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return false;
+  cuuint64_t dims[4] = {cols, rows, slots, 2};
+  cuuint64_t strides[3] = {cols * 2, cols * 2 * rows, set_bytes};
+  cuuint32_t box[4] = {64, box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+// per-peer output maps of the scatter epilogue; the plain kernels carry an empty stand-in
+template <bool RS>
+struct PeerMaps {
+  CUtensorMap m[8];
+};
+template <>
+struct PeerMaps<false> {
+  int unused;
+};
 
 }  // namespace b2

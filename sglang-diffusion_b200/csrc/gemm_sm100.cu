@@ -34,10 +34,14 @@
 namespace b2 {
 
 // OUT_KIND: 0 = bf16, 1 = f16, 2 = 32-bit (f32, or the raw s32 accumulators)
-template <MmaKind KIND, int OUT_KIND, int BN, int CG>
+// RS: scatter epilogue -- every 32-row store box goes to the rank that owns its rows (peers.m[owner], a map over that
+// rank's gather buffer, possibly across NVLink) instead of tmap_d; 16-bit outputs only
+template <MmaKind KIND, int OUT_KIND, int BN, int CG, bool RS = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_w8a8_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                     const __grid_constant__ CUtensorMap tmap_d, const KernelParams p) {
+                     const __grid_constant__ CUtensorMap tmap_d, const KernelParams p,
+                     const __grid_constant__ PeerMaps<RS> peers) {
+  static_assert(!RS || OUT_KIND != 2, "the scatter epilogue stores 16-bit outputs");
   constexpr int OUT_BYTES = OUT_KIND == 2 ? 4 : 2;
   constexpr int B_ROWS = BN / CG;  // rows of the W tile this CTA stages
   constexpr uint32_t A_STAGE_BYTES = BM * BK;
@@ -253,6 +257,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     constexpr int NCH = BN / 32;
     // TMA swizzle of the staging box: 16-byte chunk index ^= (byte offset >> 7) & (BOX_BYTES/16 - 1)
     const int swz = BOX_BYTES == 128 ? (lane & 7) : ((lane >> 1) & 3);
+    int rs_set = 0;
+    if constexpr (RS) rs_set = static_cast<int>(*reinterpret_cast<const volatile uint32_t*>(p.rs_counter) & 1u);  // after the wait above: the previous sum has advanced it
     for (int tile = unit; tile < num_tiles; tile += num_units) {
       int m_blk, n_blk;
       const int half = tile >= full_items ? ((tile - full_items) & 1) : -1;
@@ -379,6 +385,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
               fence_proxy_async_smem();
               __syncwarp();
               if (row0 < p.M && col_box < p.N && elect_one()) {  // the same lane every time
+                if constexpr (RS) {
+                  const int owner = row0 / p.rs_rows;
+                  tma_store_4d(&peers.m[owner], stage_buf, col_box, row0 - owner * p.rs_rows, p.rs_rank, rs_set);
+                } else
                 if (p.batch > 1) tma_store_3d(&tmap_d, stage_buf, col_box, row0, bidx);
                 else tma_store_2d(&tmap_d, stage_buf, col_box, row0);
                 tma_store_commit();
@@ -402,6 +412,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       }
     }
     tma_store_wait_all<0>();
+    if constexpr (RS) __threadfence_system();  // the boxes written to the peers are performed before this grid completes
     if (p.prof && warp == EPI_WARP0 && lane == 0) {
       p.prof[blockIdx.x * 8 + 3] = static_cast<unsigned long long>(prof_epi);
       p.prof[blockIdx.x * 8 + 5] = static_cast<unsigned long long>(prof_wr);
@@ -471,10 +482,11 @@ static const TileConfig& pick_config(int M, int N, int sms, int batch = 1) {
   return kConfigs[best];
 }
 
-template <MmaKind KIND, int OUT_KIND, int BN, int CG>
+template <MmaKind KIND, int OUT_KIND, int BN, int CG, bool RS = false>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const KernelParams& p,
-                      int grid, size_t smem, cudaStream_t st, char* err, size_t err_len) {
-  auto kern = gemm_w8a8_kernel<KIND, OUT_KIND, BN, CG>;
+                      int grid, size_t smem, cudaStream_t st, char* err, size_t err_len,
+                      const PeerMaps<RS>& peers = PeerMaps<RS>{}) {
+  auto kern = gemm_w8a8_kernel<KIND, OUT_KIND, BN, CG, RS>;
   static thread_local int attr_dev = -1;  // per instantiation; the attribute is per-function, per-device context
   int dev = 0;
   cudaGetDevice(&dev);
@@ -500,7 +512,7 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
   attrs[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = weight_prefetch_enabled() ? 2 : 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p, peers);
   if (e != cudaSuccess) {
     snprintf(err, err_len, "gemm kernel launch: %s", cudaGetErrorString(e));
     return B2_ERR_CUDA;
@@ -537,7 +549,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   // M in (32, 64]: still ahead on layers up to ~64 rows of W per SM (profiles/r01e_m64_probe.log: 9.4 vs 12.0 us on
   // 6144 x 4096, 15.7 vs 19.9 us on 7168 x 8192), behind on the widest ones where 128 x 256 persistent tiles stream well
   // (short K -- 8 K-blocks -- leaves the decode kernel nothing to pipeline at M > 32: 8.2 vs 6.8 us on 8192 x 1024)
-  const bool decode_shape = a.tile_expert == nullptr && a.batch <= 1 && !a.scalar_scales && (
+  const bool decode_shape = a.tile_expert == nullptr && a.batch <= 1 && !a.scalar_scales && !a.rs_peer_bufs && (
       a.M <= 32 || (a.M <= 64 && a.N <= 64 * sms && a.K >= 2048) || (a.M <= BM && a.N < 32 * sms));
   if (a.mc_slot != nullptr && !(decode_shape || a.M <= BM)) {
     snprintf(err, err_len, "multicast push epilogue is built for decode shapes (M <= 128) only");
@@ -545,7 +557,7 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   }
   if (a.x != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
   if (a.mc_slot != nullptr) return gemm_launch_splitk(flavor, a, forced_config & 0x80000 ? forced_config : 0, used_config, st, err, err_len);
-  if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert && a.batch <= 1 && !a.scalar_scales) : ((forced_config & 0xff) == 0 && decode_shape))
+  if ((forced_config & 0x80000) ? (a.M <= BM && !a.tile_expert && a.batch <= 1 && !a.scalar_scales && !a.rs_peer_bufs) : ((forced_config & 0xff) == 0 && decode_shape))
     return gemm_launch_splitk(flavor, a, forced_config, used_config, st, err, err_len);
   const TileConfig* cfg = &pick_config(a.M, a.N, sms, a.batch > 1 ? a.batch : 1);
   const int forced_debug = forced_config >> 8;  // developer experiments ride in the upper bits of the forced id
@@ -559,6 +571,17 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
       snprintf(err, err_len, "grouped GEMM takes no bias");
       return B2_ERR_ARG;
     }
+  }
+  const bool scatter = a.rs_peer_bufs != nullptr;
+  if (scatter) {
+    // scatter epilogue (row-parallel prefill): 256-wide tiles only, 16-bit output, every rank's rows a whole number of
+    // 32-row store boxes
+    if (a.tile_expert || a.batch > 1 || a.rs_world < 2 || a.rs_world > 8 || a.M % (32 * a.rs_world) != 0 || a.N % 8 != 0 ||
+        (a.out_dtype != B2_DTYPE_BF16 && a.out_dtype != B2_DTYPE_F16)) {
+      snprintf(err, err_len, "scatter epilogue: needs M %% (32 * world) == 0, N %% 8 == 0, 16-bit output, 2..8 ranks");
+      return B2_ERR_ARG;
+    }
+    if (cfg->bn != 256) cfg = &kConfigs[a.M > BM ? 4 : 3];
   }
   if (used_config) *used_config = cfg->name;
   const int bn = cfg->bn;
@@ -580,6 +603,9 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   p.batch = a.batch > 1 ? a.batch : 1;
   p.scalar_scales = a.scalar_scales;
   p.tail_tiles = 0;
+  p.rs_counter = a.rs_counter;
+  p.rs_rows = scatter ? a.M / a.rs_world : 0;
+  p.rs_rank = a.rs_rank;
   p.M = a.M;
   p.N = a.N;
   p.K = a.K;
@@ -646,6 +672,23 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
   const int grid = (items < units ? items : units) * cg;
   const size_t smem = smem_bytes_for(bn, b_rows, p.stages);
   const int out_kind = a.out_dtype == B2_DTYPE_BF16 ? 0 : (a.out_dtype == B2_DTYPE_F16 ? 1 : 2);
+  if (scatter) {
+    PeerMaps<true> peers;
+    for (int r = 0; r < 8; ++r) {
+      const int src = r < a.rs_world ? r : 0;  // unused entries repeat a valid map
+      if (!make_tmap_gather4d(&peers.m[r], d_dt, a.rs_peer_bufs[src], a.rs_world, p.rs_rows, a.N, a.rs_set_bytes, 32)) {
+        snprintf(err, err_len, "cuTensorMapEncodeTiled failed (scatter map of rank %d: rows=%d N=%d set=%lld)", src,
+                 p.rs_rows, a.N, a.rs_set_bytes);
+        return B2_ERR_CUDA;
+      }
+    }
+#define B2_RS_LAUNCH(KIND, OK)                                                                                        \
+  (cg == 2 ? launch_one<KIND, OK, 256, 2, true>(ta, tb, td, p, grid, smem, st, err, err_len, peers)                   \
+           : launch_one<KIND, OK, 256, 1, true>(ta, tb, td, p, grid, smem, st, err, err_len, peers))
+    if (flavor == GEMM_S8) return out_kind == 0 ? B2_RS_LAUNCH(MmaKind::I8, 0) : B2_RS_LAUNCH(MmaKind::I8, 1);
+    return out_kind == 0 ? B2_RS_LAUNCH(MmaKind::F8, 0) : B2_RS_LAUNCH(MmaKind::F8, 1);
+#undef B2_RS_LAUNCH
+  }
   if (flavor == GEMM_S8) {
     if (out_kind == 0) return launch_cfg<MmaKind::I8, 0>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);
     if (out_kind == 1) return launch_cfg<MmaKind::I8, 1>(*cfg, ta, tb, td, p, grid, smem, st, err, err_len);

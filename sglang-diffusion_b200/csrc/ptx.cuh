@@ -218,6 +218,14 @@ B2_DEVICE void tma_store_3d(const CUtensorMap* m, const void* smem_src, int32_t 
                : "memory");
 }
 
+// 4-D store without a cache hint: the destination may be a PEER's memory (scatter epilogue of the row-parallel GEMM)
+B2_DEVICE void tma_store_4d(const CUtensorMap* m, const void* smem_src, int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
 // the output is written once and never read back by this kernel: evict-first keeps it from pushing the
 // operands out of L2
 B2_DEVICE void tma_store_2d(const CUtensorMap* m, const void* smem_src, int32_t c0, int32_t c1) {

@@ -242,6 +242,37 @@ class QuantLinear(torch.nn.Module):
                                      bias)
         return comm.all_reduce(part).view(*x.shape[:-1], N)
 
+    def forward_reduce_scatter(self, x: torch.Tensor) -> torch.Tensor:
+        """Row-parallel layer whose summed output is wanted ROW-SHARDED: returns rows [tp_rank * M/tp, (tp_rank+1) * M/tp)
+        of the sum -- RowParallelLinear.forward(skip_all_reduce=True) followed by LayerCommunicator._tp_reduce_scatter
+        (python/sglang/srt/layers/linear.py:1467-1490, python/sglang/srt/layers/communicator.py:542-560).  With a
+        SymmAllReduce attached and a prefill-sized M the GEMM's scatter epilogue stores every rank's rows straight
+        into that rank's gather buffer (b2_gemm_*_scatter_symm) and one barrier + a local rank-ordered fp32 sum
+        finish it; otherwise GEMM + reduce_scatter_tensor of the group's backend."""
+        assert self.parallel == "row" and self.tp_size > 1
+        bias = self.bias if self.tp_rank == 0 else None
+        x2d = x.view(-1, x.shape[-1])
+        M, N = x2d.shape[0], self.weight.shape[1]
+        assert M % self.tp_size == 0, f"Expected total tokens {M} % tp_size {self.tp_size} to be 0"
+        comm = getattr(self, "symm_comm", None)
+        if (comm is not None and x.is_cuda and comm.fits_scatter(M, N, x.dtype)
+                and isinstance(self.quant_method, (W8A8Int8LinearMethod, W8A8Fp8LinearMethod))):
+            with capi.static_weights():
+                if isinstance(self.quant_method, W8A8Int8LinearMethod):
+                    q, s = ops.per_token_quant_int8(x2d)
+                else:
+                    q, s = ops.sglang_per_token_quant_fp8(x2d)
+                comm.scatter_gemm(q, self.weight, s.view(-1), self.weight_scale.view(-1), x.dtype, bias)
+                return comm.reduce_scattered(M, N, x.dtype)
+        part = self.quant_method.apply(self, x2d, bias)
+        out = part.new_empty(M // self.tp_size, N)
+        if part.is_cuda:
+            dist.reduce_scatter_tensor(out, part, group=self.tp_group)
+        else:  # gloo has no reduce_scatter_tensor: all-reduce and keep this rank's rows
+            dist.all_reduce(part, group=self.tp_group)
+            out.copy_(part[self.tp_rank * (M // self.tp_size):(self.tp_rank + 1) * (M // self.tp_size)])
+        return out
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         bias = self.bias
         if self.parallel == "row" and self.tp_rank != 0:

@@ -34,6 +34,13 @@ def test_gemm_epilogue_fused_all_reduce_equals_one_shot_bitwise():
 
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_gemm_scatter_epilogue_reduce_scatter_equals_one_shot_rows_bitwise():
+    n = min(torch.cuda.device_count(), 8)
+    r = _torchrun(n, "tools/symm_scatter_check.py", port=29544)
+    assert r.returncode == 0 and "SYMM_SCATTER_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
 @pytest.mark.parametrize("flags", [("--check",), ("--check", "--symm"), ("--check", "--symm", "--int8")])
 def test_tp_linear_layers_against_fp64_shard_products(flags):
     n = min(torch.cuda.device_count(), 8)

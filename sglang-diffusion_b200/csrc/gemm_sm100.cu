@@ -384,16 +384,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
               const int col_box = col_tile + (c / CH_PER_BOX) * BOX_COLS;
               fence_proxy_async_smem();
               __syncwarp();
-              if (row0 < p.M && col_box < p.N && elect_one()) {  // the same lane every time
-                if constexpr (RS) {
-                  const int owner = row0 / p.rs_rows;
-                  tma_store_4d(&peers.m[owner], stage_buf, col_box, row0 - owner * p.rs_rows, p.rs_rank, rs_set);
-                } else
-                if (p.batch > 1) tma_store_3d(&tmap_d, stage_buf, col_box, row0, bidx);
-                else tma_store_2d(&tmap_d, stage_buf, col_box, row0);
-                tma_store_commit();
+              // A box that lies outside the output is not stored and does NOT take a staging buffer: the wait above
+              // only guarantees "at most one store still reading shared memory", which protects the buffer about to
+              // be written only while committed stores strictly alternate between the two buffers.
+              if (row0 < p.M && col_box < p.N) {  // warp-uniform
+                if (elect_one()) {  // the same lane every time
+                  if constexpr (RS) {
+                    const int owner = row0 / p.rs_rows;
+                    tma_store_4d(&peers.m[owner], stage_buf, col_box, row0 - owner * p.rs_rows, p.rs_rank, rs_set);
+                  } else
+                  if (p.batch > 1) tma_store_3d(&tmap_d, stage_buf, col_box, row0, bidx);
+                  else tma_store_2d(&tmap_d, stage_buf, col_box, row0);
+                  tma_store_commit();
+                }
+                buf ^= 1;
               }
-              buf ^= 1;
             }
           }
         }

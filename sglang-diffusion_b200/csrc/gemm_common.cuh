@@ -34,7 +34,7 @@ struct KernelParams {
   // scatter epilogue (row-parallel prefill, RS kernels): rows [r * rs_rows, (r + 1) * rs_rows) of the output belong to
   // rank r and are stored into slot `rs_rank` of set (*rs_counter & 1) of rank r's gather buffer
   const uint32_t* rs_counter;
-  int rs_rows, rs_rank;
+  int rs_rows, rs_rank, rs_rot;
   int tail_tiles;              // BN = 256: tiles of the ragged last wave that are issued as two half-width work items
   int M, N, K;
   int num_m_blocks, num_n_blocks, num_kb;

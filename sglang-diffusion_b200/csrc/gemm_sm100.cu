@@ -128,6 +128,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         const int tidx = tile >= full_items ? full_items + ((tile - full_items) >> 1) : tile;
         const int bidx = p.batch > 1 ? tidx / tiles_pb : 0;  // batched mode: tiles enumerate batch-major
         tile_coords(tidx - bidx * tiles_pb, p, m_blk, n_blk);
+        if constexpr (RS) {  // rank-rotated row order, see the epilogue
+          m_blk += p.rs_rot;
+          if (m_blk >= p.num_m_blocks) m_blk -= p.num_m_blocks;
+        }
         const int expert = p.tile_expert ? __ldg(p.tile_expert + m_blk) : 0;  // grouped (MoE) mode: CG == 1
         if (expert < 0) continue;  // a padding block past the last routed token
         const int m_row = (m_blk * CG + cta_rank) * BM;
@@ -265,6 +269,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       const int tidx = tile >= full_items ? full_items + ((tile - full_items) >> 1) : tile;
       const int bidx = p.batch > 1 ? tidx / tiles_pb : 0;
       tile_coords(tidx - bidx * tiles_pb, p, m_blk, n_blk);
+      if constexpr (RS) {
+        // every rank walks the row blocks starting behind its own share: at any time rank r stores to owner
+        // (r + 1 + t) % world, a permutation -- no owner's NVLink ingress takes all the ranks at once -- and ends on
+        // its own rows, so nothing remote is outstanding at the end of the grid
+        m_blk += p.rs_rot;
+        if (m_blk >= p.num_m_blocks) m_blk -= p.num_m_blocks;
+      }
       const int expert = p.tile_expert ? __ldg(p.tile_expert + m_blk) : 0;
       if (expert < 0) continue;
       const float* Bs_e = p.Bs + static_cast<size_t>(expert) * p.N;  // per-expert channel scales [E, N]
@@ -629,6 +640,11 @@ int gemm_launch(GemmFlavor flavor, const GemmArgs& a, int forced_config, const c
       return e ? atoi(e) : 0;
     }();
     p.debug_flags = dbg | forced_debug;
+  }
+  p.rs_rot = 0;
+  if (scatter) {
+    const int owner0 = (a.rs_rank + 1) % a.rs_world;
+    p.rs_rot = static_cast<int>((static_cast<long long>(owner0) * p.rs_rows) / (BM * cg));  // row block holding that owner's first row
   }
   choose_raster(a.M, a.N, a.K, BM * cg, bn, p.num_m_blocks, p.num_n_blocks, &p.group_m, &p.band_n, &p.policy_a,
                 &p.policy_b);

@@ -778,6 +778,29 @@ def main():
             ceil_ms = c0.elapsed_time(c1)
         ceil_ms = _max_over_ranks(ceil_ms, dev, dist, world)
         ceil_gbs = 8 * (256 << 20) / (ceil_ms * 1e-3) / 1e9  # per rank, both directions together
+        # the step's own traffic is lopsided (1.7x more bytes come back than go in): the floor for THIS step is the time
+        # the same byte counts take as plain concurrent copies, nothing else on the GPU
+        def _copies(stream, dst, src, nbytes):
+            with torch.cuda.stream(stream):
+                left = nbytes
+                while left > 0:
+                    n = min(left, 256 << 20)
+                    dst[:n].copy_(src[:n], non_blocking=True)
+                    left -= n
+        for it in range(2):
+            barrier()
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record()
+            s_in.wait_event(c0)
+            s_out.wait_event(c0)
+            _copies(s_in, db, hb, h2d)
+            _copies(s_out, hb2, db2, d2h)
+            torch.cuda.current_stream(dev).wait_stream(s_in)
+            torch.cuda.current_stream(dev).wait_stream(s_out)
+            c1.record()
+            torch.cuda.synchronize(dev)
+            floor_ms = c0.elapsed_time(c1)
+        floor_ms = _max_over_ranks(floor_ms, dev, dist, world)
         del hb, hb2, db, db2
         e2e = {"value": round(world * ops_step / (e2e_ms * 1e-3) / 1e12, 2), "unit": "TOPS",
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": round(e2e_ms, 3),
@@ -785,7 +808,10 @@ def main():
                "pcie_gbs": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1), "matches_device_path_bitwise": bool(same),
                "link_ceiling_gbs_per_rank": round(ceil_gbs, 1),
                "link_ceiling_note": "concurrent pinned H2D + D2H copies of 256 MiB on every rank at once, slowest rank",
-               "frac_of_link_ceiling": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9 / ceil_gbs, 3)}
+               "frac_of_link_ceiling": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9 / ceil_gbs, 3),
+               "link_floor_ms_per_step": round(floor_ms, 3),
+               "link_floor_note": "the step's own h2d and d2h byte counts as plain concurrent pinned copies, every rank at once",
+               "frac_of_link_floor": round(floor_ms / e2e_ms, 3)}
         del host_layers
 
     # -- cpu baseline (rank 0, N = 1 only)

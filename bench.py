@@ -350,11 +350,15 @@ def tp_leg(b2, dev, dist, world, rank, comm):
                 layer(x)
 
         res = {"M": M, "tp": world}
-        for mode in ("nccl", "b2_allreduce_symm", "b2_fused_push"):
+        for mode in ("nccl", "b2_allreduce_symm", "b2_fused_push", "b2_fused_scatter_allgather"):
             for _, par, _, _, _, layer in layers:
                 layer.symm_comm = comm if (mode != "nccl" and par == "row") else None
                 layer.symm_fused_push = mode == "b2_fused_push"
+                layer.symm_fused_scatter = mode == "b2_fused_scatter_allgather"
                 layer.symm_force = mode != "nccl"  # measure the named path even where the layer's own policy prefers NCCL
+            if mode == "b2_fused_scatter_allgather" and (comm is None or not comm.fits_scatter_all_reduce(M, 8192, torch.bfloat16)):
+                res[mode] = None  # scatter epilogue + gathered sum + all-gather: M % (32 * world) == 0
+                continue
             if mode != "nccl" and (comm is None or not comm.fits(M, 8192, torch.bfloat16)):
                 res[mode] = None
                 continue
@@ -386,6 +390,7 @@ def tp_leg(b2, dev, dist, world, rank, comm):
         for *_, layer in layers:
             layer.symm_comm = None
             layer.symm_fused_push = None
+            layer.symm_fused_scatter = None
             layer.symm_force = False
         if M >= 32 * world and M % (32 * world) == 0:
             # prefill, row-sharded sum (RowParallelLinear(skip_all_reduce) + LayerCommunicator._tp_reduce_scatter of the
@@ -828,7 +833,7 @@ def main():
         try:
             from sglang_diffusion_b200.comm import SymmAllReduce
 
-            comm = SymmAllReduce(max_bytes=256 << 20, device=dev)  # two sets of M = 8192 x N = 8192 bf16 partials
+            comm = SymmAllReduce(max_bytes=256 << 20, device=dev, full_bytes=128 << 20)  # two sets of M = 8192 x N = 8192 bf16 partials + the gathered sum
             SymmAllReduce.set_timeout_ms(20000)  # a lost rank must not hang the box; checked below
         except Exception as e:  # noqa: BLE001
             comm = None

@@ -309,6 +309,18 @@ int b2_gemm_e4m3_scatter_symm(const uint8_t* A, int64_t lda, const uint8_t* W, i
                               uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world,
                               int out_dtype, int M, int N, int K, b2_stream_t stream);
 
+/* All-reduce form of the same (callers that need the full sum on every rank -- RowParallelLinear.forward with
+ * reduce_results, linear.py:1486-1490): after b2_gemm_*_scatter_symm, b2_allreduce_symm_gathered_bcast sums this rank's
+ * rows (numel_slice = (M/world)*N elements) and stores them into rows [rank*M/world, ...) of every rank's copy of a
+ * SECOND symmetric buffer of >= M*N elements (full_bufs_dev: DEVICE array of the `world` peer mappings; plain peer
+ * stores, no multicast mapping needed); after a second barrier this rank's copy holds the whole [M,N] sum, which is
+ * copied to `out`, or left in place when out == NULL (valid until the next call that uses the buffer).  Bit-identical
+ * on every rank and equal to algo 1 of b2_allreduce_symm. */
+int b2_allreduce_symm_gathered_bcast(const void* local_buf, uint32_t* const* signal_pads_dev,
+                                     void* const* full_bufs_dev, void* out, int64_t numel_slice,
+                                     int64_t set_stride_bytes, int dtype, int rank, int world, int max_blocks,
+                                     b2_stream_t stream);
+
 /* Waits of b2_allreduce_symm on a peer.  0 (default): wait for ever -- a late peer (first-iteration skew, weight load,
  * debugger) is not an error, hangs are the host watchdog's business, as with the reference's custom all-reduce.
  * ms > 0: a wait gives up after that long (%globaltimer), stores the barrier number in word 1536 of this rank's

@@ -31,7 +31,7 @@ SYMBOLS = [
     "b2_set_allreduce_timeout_ms", "b2_get_allreduce_timeout_ms",
     "b2_set_fused_decode", "b2_get_fused_decode",
     "b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered",
-    "b2_gemm_s8_scatter_symm", "b2_gemm_e4m3_scatter_symm",
+    "b2_gemm_s8_scatter_symm", "b2_gemm_e4m3_scatter_symm", "b2_allreduce_symm_gathered_bcast",
     "b2_moe_max_padded", "b2_moe_align_block128", "b2_quant_int8_rows_gather", "b2_gemm_s8_grouped", "b2_moe_combine",
 ]
 
@@ -99,8 +99,9 @@ lib.b2_gemm_e4m3_push_symm.argtypes = _push
 lib.b2_gemm_s8_scatter_symm.argtypes = _push   # same layout: the multicast pointer becomes the host array of peer buffers
 lib.b2_gemm_e4m3_scatter_symm.argtypes = _push
 lib.b2_allreduce_symm_gathered.argtypes = [_vp, _vp, _vp, _i64, _i64, _i, _i, _i, _i, _vp]
+lib.b2_allreduce_symm_gathered_bcast.argtypes = [_vp, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _i, _vp]
 for _n in ("b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered",
-           "b2_gemm_s8_scatter_symm", "b2_gemm_e4m3_scatter_symm"):
+           "b2_gemm_s8_scatter_symm", "b2_gemm_e4m3_scatter_symm", "b2_allreduce_symm_gathered_bcast"):
     getattr(lib, _n).restype = _i
 lib.b2_moe_max_padded.argtypes = [_i64, _i]
 lib.b2_moe_max_padded.restype = _i64

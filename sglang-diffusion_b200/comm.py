@@ -25,7 +25,8 @@ _DT = {torch.bfloat16: capi.DTYPE_BF16, torch.float16: capi.DTYPE_F16}
 class SymmAllReduce:
     """One symmetric buffer of `max_bytes` per rank of `group`; every rank must construct it collectively."""
 
-    def __init__(self, group=None, max_bytes: int = 8 << 20, device: Optional[torch.device] = None):
+    def __init__(self, group=None, max_bytes: int = 8 << 20, device: Optional[torch.device] = None,
+                 full_bytes: int = 0):
         import torch.distributed._symmetric_memory as symm_mem  # raises where the build has no symmetric memory
 
         group = group if group is not None else dist.group.WORLD
@@ -48,6 +49,14 @@ class SymmAllReduce:
         self.set_stride = (self.max_bytes // 2) // 16 * 16
         import ctypes
         self._peer_bufs_host = (ctypes.c_void_p * self.world)(*[int(p) for p in self.handle.buffer_ptrs])
+        # second symmetric buffer: the all-gather half of the fused prefill all-reduce lands here (multicast stores)
+        self.full_buf = None
+        self.full_bufs_dev = 0
+        if full_bytes > 0:
+            self.full_buf = symm_mem.empty(int(full_bytes), dtype=torch.uint8, device=self.device)
+            fh = symm_mem.rendezvous(self.full_buf, group.group_name)
+            self._full_handle = fh
+            self.full_bufs_dev = int(fh.buffer_ptrs_dev)
         need = 4 * (1536 + 1)
         if int(self.handle.signal_pad_size) < need:
             raise ValueError(f"signal pad of {self.handle.signal_pad_size} bytes is smaller than the {need} b2_allreduce_symm needs")
@@ -118,6 +127,23 @@ class SymmAllReduce:
                           bdt[bias.dtype] if bias is not None else capi.DTYPE_F32, self._peer_bufs_host,
                           int(self.handle.signal_pad_ptrs[self.rank]), self.set_stride, self.rank, self.world,
                           _DT[out_dtype], M, N, K, torch.cuda.current_stream(q.device).cuda_stream))
+
+    def fits_scatter_all_reduce(self, M: int, N: int, dtype: torch.dtype) -> bool:
+        return (self.fits_scatter(M, N, dtype) and self.full_bufs_dev != 0
+                and M * N * dtype.itemsize <= self.full_buf.numel())
+
+    def all_reduce_scattered(self, M: int, N: int, dtype: torch.dtype, inplace: bool = False) -> torch.Tensor:
+        """After scatter_gemm: barrier, rank-ordered fp32 sum of this rank's rows, peer stores of the result into every
+        rank's `full_buf`, barrier -> the whole [M, N] sum (a fresh tensor, or -- inplace=True -- a view of full_buf that
+        stays valid until the next call using it).  b2_allreduce_symm_gathered_bcast."""
+        out = None if inplace else torch.empty(M, N, dtype=dtype, device=self.device)
+        with torch.cuda.device(self.device):
+            capi.check(capi.lib.b2_allreduce_symm_gathered_bcast(
+                self.buf.data_ptr(), self.pads_dev, self.full_bufs_dev, None if inplace else out.data_ptr(), (M // self.world) * N, self.set_stride, _DT[dtype], self.rank,
+                self.world, self.max_blocks, torch.cuda.current_stream(self.device).cuda_stream))
+        if inplace:
+            return self.full_buf[:M * N * dtype.itemsize].view(dtype).view(M, N)
+        return out
 
     def reduce_scattered(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
         """Barrier + rank-ordered fp32 sum of the `world` slots of this rank's rows -> fresh [M / world, N] tensor."""

@@ -281,6 +281,107 @@ __global__ void __launch_bounds__(512) allreduce_gathered_kernel(const uint4* __
   }
 }
 
+
+// ---- scatter GEMM + sum + all-gather = an all-reduce whose reduce-scatter half ran inside the GEMM ----
+// After the scatter epilogue (gemm_sm100.cu, RS) this rank holds `world` partial copies of ITS rows.  One barrier, the
+// rank-ordered fp32 sum of those slots (local memory), and the result is stored into rows [rank * rows, ...) of EVERY
+// rank's copy of a second symmetric buffer -- plain peer stores, one per peer: the NVSwitch multicast would also loop
+// the rows back to the sender, and it is the ingress side that is busy here ((world-1)/world * M*N*2 bytes per rank
+// either way).  A second barrier, then the full [M, N] sum is in this rank's copy (full[rank]); the other ranks' rows
+// are copied from there to `out` (this rank's rows went to `out` directly) unless the caller consumes it in place.
+// Vector v of a slice belongs to CTA (v / blockDim.x) % gridDim.x on every rank, which is what lets the per-CTA
+// barriers order the copy-out behind the peers' stores.
+template <bool BF16>
+__global__ void __launch_bounds__(512) allreduce_gathered_bcast_kernel(const uint4* __restrict__ local_buf,
+                                                                        uint32_t* const* pads, uint4* const* full,
+                                                                        uint4* __restrict__ out, long long nvec,
+                                                                        long long set_vec, int rank, int world,
+                                                                        unsigned long long timeout_ns) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // this rank's GEMM has completed: its stores are performed
+  uint32_t* pad = pads[rank];
+  const uint32_t epoch = pad[kEpochWord + blockIdx.x];
+  const uint32_t counter = pad[kGatherCounterWord];
+  xgpu_barrier<true>(pads, rank, world, epoch + 1, timeout_ns);
+  const uint4* set = local_buf + static_cast<long long>(counter & 1u) * set_vec;
+  const long long mine = static_cast<long long>(rank) * nvec;
+  uint4* dst[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) dst[r] = r < world ? full[r] + mine : nullptr;
+  if (out != nullptr) dst[rank] = out + mine;  // this rank's own rows go straight to the private output
+  const long long stride = static_cast<long long>(blockDim.x) * gridDim.x;
+  const long long v0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  long long v = v0;
+  for (; v + 3 * stride < nvec; v += 4 * stride) {
+    float acc[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) unpack8<BF16>(__ldcs(set + v + u * stride), acc[u]);
+    for (int r = 1; r < world; ++r) {
+      uint4 t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) t[u] = __ldcs(set + static_cast<long long>(r) * nvec + v + u * stride);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+        unpack8<BF16>(t[u], f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[u][i] = __fadd_rn(acc[u][i], f[i]);
+      }
+    }
+    uint4 o[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) o[u] = pack8<BF16>(acc[u]);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      if (r < world) {
+        const int p = (rank + r) % world;  // start with this rank, then the peers in rotated order
+#pragma unroll
+        for (int u = 0; u < 4; ++u) dst[p][v + u * stride] = o[u];
+      }
+    }
+  }
+  for (; v < nvec; v += stride) {
+    float acc[8];
+    unpack8<BF16>(set[v], acc);
+    for (int r = 1; r < world; ++r) {
+      float f[8];
+      unpack8<BF16>(set[static_cast<long long>(r) * nvec + v], f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
+    }
+    const uint4 o = pack8<BF16>(acc);
+    for (int r = 0; r < world; ++r) dst[r][v] = o;
+  }
+  xgpu_barrier<true>(pads, rank, world, epoch + 2, timeout_ns);  // every rank's rows have landed in this rank's copy
+  if (out != nullptr) {
+    const uint4* local_full = full[rank];
+    for (int r = 0; r < world; ++r) {
+      if (r == rank) continue;
+      const uint4* src = local_full + static_cast<long long>(r) * nvec;
+      uint4* d = out + static_cast<long long>(r) * nvec;
+      long long w = v0;
+      for (; w + 3 * stride < nvec; w += 4 * stride) {
+        uint4 t[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) t[u] = __ldcg(src + w + u * stride);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) d[w + u * stride] = t[u];
+      }
+      for (; w < nvec; w += stride) d[w] = __ldcg(src + w);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    pad[kEpochWord + blockIdx.x] = epoch + 2;
+    __threadfence();
+    const uint32_t t = atomicAdd(&pad[kGatherDoneWord], 1u);
+    if (t == gridDim.x - 1) {
+      pad[kGatherDoneWord] = 0;
+      pad[kGatherCounterWord] = counter + 1;
+    }
+  }
+}
+
 }  // namespace b2
 
 using namespace b2;
@@ -391,6 +492,52 @@ extern "C" int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const
                        ? cudaLaunchKernelEx(&cfg, allreduce_gathered_kernel<true>, lb, signal_pads_dev, o, nvec, set_vec, rank, world, tmo)
                        : cudaLaunchKernelEx(&cfg, allreduce_gathered_kernel<false>, lb, signal_pads_dev, o, nvec, set_vec, rank, world, tmo);
   if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm_gathered launch: %s", cudaGetErrorString(le));
+  count_launch();
+  return B2_OK;
+}
+
+extern "C" int b2_allreduce_symm_gathered_bcast(const void* local_buf, uint32_t* const* signal_pads_dev,
+                                                void* const* full_bufs_dev, void* out, int64_t numel_slice,
+                                                int64_t set_stride_bytes, int dtype, int rank, int world,
+                                                int max_blocks, b2_stream_t stream) {
+  if (!local_buf || !signal_pads_dev || !full_bufs_dev)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered_bcast: null pointer");
+  if (dtype != B2_DTYPE_BF16 && dtype != B2_DTYPE_F16)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered_bcast: dtype must be bfloat16 or float16");
+  if (world < 2 || world > 8 || rank < 0 || rank >= world)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered_bcast: world size must be 2..8, rank inside it");
+  if (numel_slice <= 0 || numel_slice % 8 != 0)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered_bcast: numel_slice must be a positive multiple of 8");
+  if (reinterpret_cast<uintptr_t>(out) % 16 != 0 || reinterpret_cast<uintptr_t>(local_buf) % 16 != 0)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered_bcast: buffers must be 16-byte aligned");
+  const long long nvec = numel_slice / 8;
+  if (set_stride_bytes == 0) set_stride_bytes = numel_slice * 2 * world;
+  if (set_stride_bytes % 16 != 0 || set_stride_bytes < numel_slice * 2 * world)
+    return fail_msg(B2_ERR_ARG, "allreduce_symm_gathered_bcast: set stride must be a multiple of 16 and hold world slots");
+  const long long set_vec = set_stride_bytes / 16;
+  const int threads = 512;
+  long long blocks = (nvec + threads - 1) / threads;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks > kEpochWord / world) blocks = kEpochWord / world;
+  if (blocks < 1) blocks = 1;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(blocks));
+  cfg.blockDim = dim3(threads);
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const unsigned long long tmo = static_cast<unsigned long long>(g_ar_timeout_ms.load()) * 1000000ull;
+  const uint4* lb = static_cast<const uint4*>(local_buf);
+  uint4* const* fb = reinterpret_cast<uint4* const*>(full_bufs_dev);
+  uint4* o = static_cast<uint4*>(out);
+  cudaError_t le =
+      dtype == B2_DTYPE_BF16
+          ? cudaLaunchKernelEx(&cfg, allreduce_gathered_bcast_kernel<true>, lb, signal_pads_dev, fb, o, nvec, set_vec, rank, world, tmo)
+          : cudaLaunchKernelEx(&cfg, allreduce_gathered_bcast_kernel<false>, lb, signal_pads_dev, fb, o, nvec, set_vec, rank, world, tmo);
+  if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm_gathered_bcast launch: %s", cudaGetErrorString(le));
   count_launch();
   return B2_OK;
 }

@@ -41,7 +41,8 @@ def test_gemm_scatter_epilogue_reduce_scatter_equals_one_shot_rows_bitwise():
 
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
-@pytest.mark.parametrize("flags", [("--check",), ("--check", "--symm"), ("--check", "--symm", "--int8")])
+@pytest.mark.parametrize("flags", [("--check",), ("--check", "--symm"), ("--check", "--symm", "--int8"),
+                                   ("--check", "--symm", "--prefill-symm"), ("--check", "--symm", "--prefill-symm", "--int8")])
 def test_tp_linear_layers_against_fp64_shard_products(flags):
     n = min(torch.cuda.device_count(), 8)
     r = _torchrun(n, "tools/tp_bench.py", *flags, port=29542)

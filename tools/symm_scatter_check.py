@@ -23,7 +23,8 @@ dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 SymmAllReduce.set_timeout_ms(20000)
 TIMING = "--time" in sys.argv
-comm_rs = SymmAllReduce(max_bytes=(160 << 20) if TIMING else (72 << 20), device=dev)
+comm_rs = SymmAllReduce(max_bytes=(160 << 20) if TIMING else (72 << 20), device=dev,
+                        full_bytes=(80 << 20) if TIMING else (36 << 20))
 comm_ref = SymmAllReduce(max_bytes=(64 << 20) if TIMING else (32 << 20), device=dev)
 fails = 0
 
@@ -42,9 +43,13 @@ def problem(kind, M, N, K, seed):
     return q, s.view(-1), W, Bs, bias
 
 
+LAST_FULL = [None]
+
+
 def reference(q, s, W, Bs, bias, M, N, dtype=torch.bfloat16):
     part = ops.scaled_mm_out(q, W.t(), s, Bs, comm_ref.partial(M, N, dtype), bias)
     full = comm_ref.all_reduce(part, 1)
+    LAST_FULL[0] = full
     r = M // world
     return full[rank * r:(rank + 1) * r]
 
@@ -68,6 +73,14 @@ for kind in ("int8", "fp8"):
                 bad = (got.view(torch.int16) != want.view(torch.int16)).sum().item()
                 print(f"[rank {rank}] FAIL {kind} M={M} N={N} K={K} call={it} mismatches={bad}/{got.numel()} "
                       f"cfg={capi.last_gemm_config()}", flush=True)
+            if comm_rs.fits_scatter_all_reduce(M, N, torch.bfloat16):  # all-reduce form: + multicast all-gather
+                comm_rs.scatter_gemm(q, W.t(), s, Bs, torch.bfloat16, bias)
+                full = comm_rs.all_reduce_scattered(M, N, torch.bfloat16, inplace=(it == 2))
+                torch.cuda.synchronize()
+                if not torch.equal(full.view(torch.int16), LAST_FULL[0].view(torch.int16)):
+                    fails += 1
+                    print(f"[rank {rank}] FAIL all-reduce form {kind} M={M} N={N} K={K} call={it}", flush=True)
+                dist.barrier()  # the in-place view is read above: keep the peers from overwriting it early
             if it == 1 and comm_rs.multicast_ptr:  # a decode-sized push call in between: different size, same counter
                 qd, sd, Wd, Bsd, biasd = problem("int8", 16, 2048, 1024, 7 + it)
                 wd = ops.scaled_mm_out(qd, Wd.t(), sd, Bsd, comm_ref.partial(16, 2048, torch.bfloat16), biasd)
@@ -135,7 +148,8 @@ if TIMING:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    for M, N, Kfull in ((8192, 4096, 14336), (8192, 4096, 4096), (4096, 5120, 13824), (2048, 4096, 14336)):
+    for M, N, Kfull in ((8192, 4096, 14336), (8192, 4096, 4096), (4096, 5120, 13824), (2048, 4096, 14336),
+                        (1024, 8192, 8192), (512, 4096, 14336), (256, 8192, 8192)):
         K = Kfull // world // 128 * 128
         q, s, W, Bs, bias = problem("int8", M, N, K, 1)
         Wt = W.t()
@@ -164,7 +178,17 @@ if TIMING:
         def scatter_only():  # the same set every time (the counter only advances in the sum): timing only
             comm_rs.scatter_gemm(q, Wt, s, Bs, torch.bfloat16, bias)
 
-        res = {name: timed(fn) for name, fn in (("gemm_only", gemm_only), ("scatter_gemm_only", scatter_only), ("gemm+nccl_all_reduce", nccl_ar),
+        def fused_ar():
+            comm_rs.scatter_gemm(q, Wt, s, Bs, torch.bfloat16, bias)
+            comm_rs.all_reduce_scattered(M, N, torch.bfloat16)
+
+        def fused_ar_inplace():
+            comm_rs.scatter_gemm(q, Wt, s, Bs, torch.bfloat16, bias)
+            comm_rs.all_reduce_scattered(M, N, torch.bfloat16, inplace=True)
+
+        extra = (("fused_scatter_gemm+sum+allgather", fused_ar), ("same_in_place", fused_ar_inplace)) \
+            if comm_rs.fits_scatter_all_reduce(M, N, torch.bfloat16) else ()
+        res = {name: timed(fn) for name, fn in extra + (("gemm_only", gemm_only), ("scatter_gemm_only", scatter_only), ("gemm+nccl_all_reduce", nccl_ar),
                                                 ("gemm+nccl_reduce_scatter", nccl_rs), ("gemm+symm_all_reduce", symm_ar),
                                                 ("fused_scatter_gemm+sum", fused_rs))}
         if rank == 0:

@@ -87,7 +87,9 @@ def main():
     comm = None
     if "--symm" in sys.argv and world > 1:  # decode-sized row-parallel sums through b2_allreduce_symm (peer memory)
         from sglang_diffusion_b200.comm import SymmAllReduce
-        comm = SymmAllReduce(max_bytes=4 << 20, device=dev)
+        # --prefill-symm: room for the scatter-epilogue all-reduce of the M = 8192 row-parallel layers as well
+        big = "--prefill-symm" in sys.argv
+        comm = SymmAllReduce(max_bytes=(272 << 20) if big else (4 << 20), device=dev, full_bytes=(136 << 20) if big else 0)
     g = torch.Generator(device=dev).manual_seed(1234 + rank)
     for name, par, K, N in LAYERS:
         layer = QuantLinear(K, N, method, bias=False, parallel=par, tp_rank=rank, tp_size=shard, device=dev)
@@ -125,8 +127,10 @@ def main():
                     "us_allreduce": round((t_all - t_mm) * 1e6, 1) if par == "row" else 0.0,
                     "allreduce_bytes": M * N * 2 if par == "row" and world > 1 else 0,
                     "tops_aggregate": round(ops / t_all / 1e12, 1),
-                    "allreduce": ("b2_allreduce_symm" if comm is not None and comm.fits(M, N, torch.bfloat16)
-                                  else "nccl") if par == "row" and world > 1 else None,
+                    "allreduce": (("b2_scatter_gemm+sum+allgather" if comm is not None and M * N * 2 >= ((8 << 20) if world < 8 else (32 << 20))
+                                   and comm.fits_scatter_all_reduce(M, N, torch.bfloat16) else
+                                   "b2_allreduce_symm" if comm is not None and comm.fits(M, N, torch.bfloat16)
+                                   else "nccl") if par == "row" and world > 1 else None),
                     "gemm_config": b2.capi.last_gemm_config()}), flush=True)
         del layer
     dist.destroy_process_group()

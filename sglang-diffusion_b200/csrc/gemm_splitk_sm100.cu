@@ -38,7 +38,9 @@ struct SplitParams {
   long long ldd;  // elements
   int M, N, K;
   int num_kb;      // 128-byte K blocks in total
-  int split;       // S = cluster size
+  int split;       // S = CTAs sharing one tile (K split)
+  int amc;         // C = adjacent tiles sharing their activation loads: cluster = C x S CTAs, cluster rank = c * S + s;
+                   // the C CTAs with the same s load a_box_rows / C rows of the A stage each and multicast them
   int stages;
   int a_box_rows;  // activation rows fetched per stage (multiple of 8, >= M)
   int bn;          // weight rows per tile = UMMA N (multiple of 16, 16..256): chosen at run time so that the grid is
@@ -228,8 +230,14 @@ __global__ void __launch_bounds__(NUM_THREADS)
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const int S = p.split;
-  const int rank = S > 1 ? static_cast<int>(cluster_ctarank()) : 0;
-  const int tile = static_cast<int>(blockIdx.x) / S;
+  const int C = p.amc;
+  const int crank = S * C > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+  const int rank = crank % S;   // K-split rank inside the tile
+  const int cidx = crank / S;   // position inside the activation-multicast group
+  const int tile = (static_cast<int>(blockIdx.x) / (S * C)) * C + cidx;
+  uint16_t amc_mask = 0;
+  for (int c = 0; c < C; ++c) amc_mask |= static_cast<uint16_t>(1u << (c * S + rank));
+  const int a_piece_rows = p.a_box_rows / C;
   const int kb0 = static_cast<int>(static_cast<long long>(rank) * p.num_kb / S);
   const int kb1 = static_cast<int>(static_cast<long long>(rank + 1) * p.num_kb / S);
 
@@ -253,7 +261,7 @@ __global__ void __launch_bounds__(NUM_THREADS)
       tma_prefetch_desc(&tmap_b);
       for (int i = 0; i < stages; ++i) {
         mbar_init(&full_bar[i], 1);
-        mbar_init(&empty_bar[i], 1);
+        mbar_init(&empty_bar[i], static_cast<uint32_t>(C));  // every CTA the stage's A tile went to has consumed it
       }
       mbar_init(acc_full, 1);
       mbar_init(a_ready, 128);
@@ -267,19 +275,36 @@ __global__ void __launch_bounds__(NUM_THREADS)
         tma_load_2d(smem_b + static_cast<size_t>(i) * B_STAGE_BYTES, &tmap_b, &full_bar[i], (kb0 + i) * BK, tile * BN,
                     kEvictFirst);
       }
-      if constexpr (!FUSEQ) {
-        pdl_wait_prior_grids();
-        for (int i = 0; i < first_pass; ++i)
-          tma_load_2d(smem_a + static_cast<size_t>(i) * a_stage_bytes, &tmap_a, &full_bar[i], (kb0 + i) * BK, 0,
-                      kEvictLast);
+      if (C == 1) {
+        if constexpr (!FUSEQ) {
+          pdl_wait_prior_grids();
+          for (int i = 0; i < first_pass; ++i)
+            tma_load_2d(smem_a + static_cast<size_t>(i) * a_stage_bytes, &tmap_a, &full_bar[i], (kb0 + i) * BK, 0,
+                        kEvictLast);
+        }
+        pdl_launch_dependents();
       }
-      pdl_launch_dependents();
     }
     __syncwarp();
   }
   if (warp == 1) tmem_alloc<1>(tmem_ptr, TMEM_COLS);
   tc_fence_before_sync();
-  __syncthreads();
+  if (C > 1) {
+    // multicast activation loads land in the PEERS' shared memory and complete on their barriers: those must be
+    // initialised first (the weight loads above are local and already in flight)
+    __syncwarp();
+    cluster_sync_all();
+    if (warp == 0 && lane == 0) {
+      pdl_wait_prior_grids();
+      for (int i = 0; i < first_pass; ++i)
+        tma_load_2d_mc(smem_a + static_cast<size_t>(i) * a_stage_bytes + static_cast<size_t>(cidx * a_piece_rows) * BK,
+                       &tmap_a, &full_bar[i], (kb0 + i) * BK, cidx * a_piece_rows, amc_mask, kEvictLast);
+      pdl_launch_dependents();
+    }
+    __syncwarp();
+  } else {
+    __syncthreads();
+  }
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
 
@@ -325,9 +350,14 @@ __global__ void __launch_bounds__(NUM_THREADS)
         mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
         tma_load_2d(smem_b + static_cast<size_t>(stage) * B_STAGE_BYTES, &tmap_b, &full_bar[stage], kb * BK,
                     tile * BN, kEvictFirst);
-        if constexpr (!FUSEQ)
-          tma_load_2d(smem_a + static_cast<size_t>(stage) * a_stage_bytes, &tmap_a, &full_bar[stage], kb * BK, 0,
-                      kEvictLast);
+        if constexpr (!FUSEQ) {
+          if (C == 1)
+            tma_load_2d(smem_a + static_cast<size_t>(stage) * a_stage_bytes, &tmap_a, &full_bar[stage], kb * BK, 0,
+                        kEvictLast);
+          else
+            tma_load_2d_mc(smem_a + static_cast<size_t>(stage) * a_stage_bytes + static_cast<size_t>(cidx * a_piece_rows) * BK,
+                           &tmap_a, &full_bar[stage], kb * BK, cidx * a_piece_rows, amc_mask, kEvictLast);
+        }
       }
       __syncwarp();
       if (++stage == stages) {
@@ -352,7 +382,8 @@ __global__ void __launch_bounds__(NUM_THREADS)
         for (int k = 0; k < BK / UMMA_K; ++k)
           umma<KIND, 1>(tmem_base, da + static_cast<uint64_t>(k * (UMMA_K >> 4)),
                         db + static_cast<uint64_t>(k * (UMMA_K >> 4)), idesc, (kb > kb0 || k != 0) ? 1u : 0u);
-        umma_commit(&empty_bar[stage]);
+        if (C == 1) umma_commit(&empty_bar[stage]);
+        else umma_commit_mc(&empty_bar[stage], amc_mask);
       }
       __syncwarp();
       if (++stage == stages) {
@@ -426,9 +457,9 @@ __global__ void __launch_bounds__(NUM_THREADS)
       const int col = tile * BN + c;
       if (col >= p.N) continue;  // N % 8 == 0: a group of 4 columns is inside or outside as a whole
       const uint32_t addr = part_base + part_offset(row, c >> 2, p.part_pitch);
-      uint4 acc = ld_dsmem_v4(addr, 0);
+      uint4 acc = ld_dsmem_v4(addr, cidx * S);
       for (int pr = 1; pr < S; ++pr) {
-        const uint4 o = ld_dsmem_v4(addr, pr);
+        const uint4 o = ld_dsmem_v4(addr, cidx * S + pr);
         if constexpr (KIND == MmaKind::I8) {
           acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;  // two's complement: exact int32 sums
         } else {
@@ -478,6 +509,7 @@ __global__ void __launch_bounds__(NUM_THREADS)
 struct SplitPlan {
   int bn, split, stages;
   size_t smem;
+  int amc = 1;
 };
 
 // a_res > 0: the fused-quantizer layout -- `a_res` resident A tiles in front of a ring of weight stages only
@@ -567,7 +599,7 @@ static int launch_splitk(const CUtensorMap& ta, const CUtensorMap& tb, const Spl
   cfg.stream = st;
   cudaLaunchAttribute attrs[2];
   attrs[0].id = cudaLaunchAttributeClusterDimension;
-  attrs[0].val.clusterDim.x = static_cast<unsigned>(p.split);
+  attrs[0].val.clusterDim.x = static_cast<unsigned>(p.split * p.amc);
   attrs[0].val.clusterDim.y = 1;
   attrs[0].val.clusterDim.z = 1;
   attrs[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -600,16 +632,24 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
     const int cap = (forced >> 8) & 31;  // developer sweeps: ring depth cap in bits 8-12
     if (cap >= 1 && cap < plan.stages) plan.stages = cap;
     plan.smem = splitk_smem(plan.bn, a_rows, plan.stages, fuseq ? kb_per_f : 0);
+    plan.amc = 1 << ((forced >> 13) & 3);  // activation multicast group in bits 13-14 (log2)
   } else {
     plan = plan_splitk(a.N, a.K, a_rows, fuseq);
   }
   const int bn = plan.bn;
+  {
+    // the multicast group needs whole groups of tiles, 8-row pieces of the activation box, a cluster of <= 8 CTAs
+    const int tiles_n = (a.N + bn - 1) / bn;
+    while (plan.amc > 1 && (fuseq || plan.split * plan.amc > 8 || tiles_n % plan.amc != 0 || a_rows % (8 * plan.amc) != 0))
+      plan.amc >>= 1;
+  }
   if (plan.smem > static_cast<size_t>(SMEM_LIMIT)) {
     snprintf(err, err_len, "split-K plan does not fit shared memory (bn=%d rows=%d)", bn, a_rows);
     return B2_ERR_ARG;
   }
   static thread_local char name[64];
-  snprintf(name, sizeof(name), "splitk_%dx%d_s%d_st%d%s", a_rows, bn, plan.split, plan.stages, fuseq ? "_fusedq" : "");
+  snprintf(name, sizeof(name), "splitk_%dx%d_s%d_st%d%s%s", a_rows, bn, plan.split, plan.stages, fuseq ? "_fusedq" : "",
+           plan.amc == 4 ? "_a4" : (plan.amc == 2 ? "_a2" : ""));
   if (used_config) *used_config = name;
 
   SplitParams p;
@@ -625,6 +665,7 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
   p.K = a.K;
   p.num_kb = num_kb;
   p.split = plan.split;
+  p.amc = plan.amc;
   p.stages = plan.stages;
   p.a_box_rows = a_rows;
   p.bn = bn;
@@ -643,7 +684,7 @@ int gemm_launch_splitk(GemmFlavor flavor, const GemmArgs& a, int forced, const c
   CUtensorMap ta, tb;
   if (!make_tmap_2d(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.W, a.N, a.K, a.ldw, bn, BK) ||
       (fuseq ? (ta = tb, false)  // no A loads in the fused form: the parameter slot carries a valid (unused) map
-             : !make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, a_rows, BK))) {
+             : !make_tmap_2d(&ta, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a.A, a.M, a.K, a.lda, a_rows / plan.amc, BK))) {
     snprintf(err, err_len, "cuTensorMapEncodeTiled failed (M=%d N=%d K=%d lda=%lld ldw=%lld)", a.M, a.N, a.K,
              (long long)a.lda, (long long)a.ldw);
     return B2_ERR_CUDA;

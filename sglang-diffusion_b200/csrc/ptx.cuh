@@ -330,6 +330,27 @@ B2_DEVICE void umma_commit(uint64_t* bar) {
                : "memory");
 }
 
+// cta_group::1, multicast: arrive on the same-offset barrier in every CTA of `cta_mask` (a stage whose A tile was
+// multicast to several CTAs is free once each of them has consumed it)
+B2_DEVICE void umma_commit_mc(uint64_t* bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(cta_mask)
+      : "memory");
+}
+
+// 2-D tile load delivered to the same shared-memory offset of every CTA in `cta_mask`; each destination's barrier
+// (same offset) receives the bytes
+B2_DEVICE void tma_load_2d_mc(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int32_t c0, int32_t c1,
+                              uint16_t cta_mask, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5, %6;" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(cta_mask), "l"(policy)
+      : "memory");
+}
+
 // cta_group::2: arrive on the same-offset barrier in every CTA of `cta_mask`
 B2_DEVICE void umma_commit_cg2(uint64_t* bar, uint16_t cta_mask) {
   asm volatile(

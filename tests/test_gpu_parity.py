@@ -154,6 +154,22 @@ def test_gemm_s8_splitk_cluster_accumulators_exact(bn_idx, split, M, N, K):
     assert torch.equal(D, exact_acc(A, W))
 
 
+@pytest.mark.parametrize("amc", [1, 2])  # log2 of the activation-multicast group: 2 or 4 adjacent tiles
+@pytest.mark.parametrize("bn_idx,split", [(0, 1), (0, 2), (1, 1), (1, 2), (1, 4), (2, 2)])
+@pytest.mark.parametrize("M,N,K", [(64, 1024, 1168), (128, 2048, 4096), (32, 1536, 640), (40, 512, 2048), (100, 520, 1024)])
+def test_gemm_s8_splitk_activation_multicast_exact(amc, bn_idx, split, M, N, K):
+    """Decode kernel with the activation tile of every stage loaded once per group of 2 / 4 adjacent tiles (each CTA
+    fetches a slice and multicasts it; stages are released by a multicast commit).  Developer option -- measured
+    slower than independent loads (profiles/r02x_amc_sweep.log), the planner never picks it -- kept exact.  Shapes
+    whose tile count or row count does not divide fall back to smaller groups inside the launcher."""
+    g = torch.Generator().manual_seed(M * 5 + N + K + bn_idx + split + amc)
+    A = torch.randint(-128, 128, (M, K), dtype=torch.int8, generator=g).to(DEV)
+    W = torch.randint(-128, 128, (N, K), dtype=torch.int8, generator=g).to(DEV)
+    D = c_gemm_s8(A, W, None, None, None, torch.int32, splitk_cfg(bn_idx, split) | (amc << 13))
+    assert capi.last_gemm_config().startswith("splitk_")
+    assert torch.equal(D, exact_acc(A, W))
+
+
 @pytest.mark.parametrize("bn", [16, 48, 80, 112, 176, 208, 240])
 @pytest.mark.parametrize("split", [1, 4])
 @pytest.mark.parametrize("M,N,K", [(5, 1000, 2048), (64, 1296, 1168)])

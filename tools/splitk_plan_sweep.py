@@ -52,8 +52,9 @@ for M, N, K in shapes:
     As, Bs = torch.rand(M, 1, device=dev), torch.rand(N, 1, device=dev)
     byts = M * K + N * K + 2 * M * N
     res = []
-    cands = [0] + [0x80000 | (bn // 16 - 1) | ((S - 1) << 4) | (cap << 8)
-                   for bn in (32, 64, 96, 128, 192, 256) for S in (1, 2, 4, 8) for cap in (4, 8, 24)]
+    cands = [0, 2, 3, 4] + [0x80000 | (bn // 16 - 1) | ((S - 1) << 4) | (cap << 8) | (amc << 13)
+                   for bn in (32, 64, 96, 128, 192, 256) for S in (1, 2, 4, 8) for cap in (4, 8, 24)
+                   for amc in ((0, 1, 2) if M >= 32 else (0,)) if S << amc <= 8]
     for cfg in cands:
         b2.capi.set_gemm_config(cfg)
         try:
@@ -66,5 +67,5 @@ for M, N, K in shapes:
     auto = res[0]
     res.sort()
     print(f"# {kind} M={M} N={N} K={K}: planner {auto[1]} {auto[0]*1e6:.1f} us = {byts/auto[0]/1e9:.0f} GB/s", flush=True)
-    for t, name, cfg in res[:6]:
+    for t, name, cfg in res[:10]:
         print(f"   {name:28s} {t*1e6:7.1f} us  {byts/t/1e9:7.0f} GB/s", flush=True)

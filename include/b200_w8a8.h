@@ -211,6 +211,23 @@ int b2_linear_w8a8_int8(const void* x, int x_dtype, int64_t ldx, const int8_t* W
                         const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
                         void* workspace, size_t workspace_bytes, b2_stream_t stream);
 
+/* Allocation-free form of b2_linear_w8a8_int8.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arithmetic and result, bit for bit; the codes + row scales between the quantizer and the GEMM live in
+ * a file-scope `static __device__` array of B2_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library
+ * holds it until the process exits) instead of a caller workspace.  The call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine); the caller still passes x, W, Bs, bias and D.
+ * Limit: b2_linear_w8a8_int8_workspace(M, K) <= B2_STATIC_SCRATCH_BYTES (4 MiB: M*K <= ~4.19e6, e.g. M = 128 x
+ * K = 28672 or M = 256 x K = 14336); larger problems are rejected with B2_ERR_ARG and a message -- use the workspace
+ * form.  ALL calls on a device share the one array, which keeps the last call's contents (nothing in it needs to start
+ * at zero: every byte the GEMM reads is written by the quantizer of the same call): calls that overlap on the GPU
+ * -- two streams, or two threads on one device -- race on it; serialise them on one stream. */
+#define B2_STATIC_SCRATCH_BYTES (4u << 20)
+size_t b2_linear_w8a8_int8_static_max_bytes(void);
+int b2_linear_w8a8_int8_static(const void* x, int x_dtype, int64_t ldx, const int8_t* W, int64_t ldw, const float* Bs,
+                               const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
+                               b2_stream_t stream);
+
 /* One-kernel form of the two entries above for M <= 32 (calling thread; default 0 = off, or B2_FUSED_DECODE=1 in the
  * environment): the cluster split-K decode GEMM quantizes its own K slice of the activations into resident
  * shared-memory A tiles (row maxima exchanged over DSMEM) -- no quantizer launch, no codes round trip, workspace

@@ -32,6 +32,7 @@ SYMBOLS = [
     "b2_set_fused_decode", "b2_get_fused_decode",
     "b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered",
     "b2_gemm_s8_scatter_symm", "b2_gemm_e4m3_scatter_symm", "b2_allreduce_symm_gathered_bcast",
+    "b2_linear_w8a8_int8_static_max_bytes", "b2_linear_w8a8_int8_static",
     "b2_moe_max_padded", "b2_moe_align_block128", "b2_quant_int8_rows_gather", "b2_gemm_s8_grouped", "b2_moe_combine",
 ]
 
@@ -103,6 +104,10 @@ lib.b2_allreduce_symm_gathered_bcast.argtypes = [_vp, _vp, _vp, _vp, _i64, _i64,
 for _n in ("b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered",
            "b2_gemm_s8_scatter_symm", "b2_gemm_e4m3_scatter_symm", "b2_allreduce_symm_gathered_bcast"):
     getattr(lib, _n).restype = _i
+lib.b2_linear_w8a8_int8_static_max_bytes.argtypes = []
+lib.b2_linear_w8a8_int8_static_max_bytes.restype = _sz
+lib.b2_linear_w8a8_int8_static.argtypes = [_vp, _i, _i64, _vp, _i64, _vp, _vp, _i, _vp, _i64, _i, _i, _i, _vp]
+lib.b2_linear_w8a8_int8_static.restype = _i
 lib.b2_moe_max_padded.argtypes = [_i64, _i]
 lib.b2_moe_max_padded.restype = _i64
 lib.b2_moe_align_block128.argtypes = [_vp, _i, _i, _vp, _vp, _vp, _vp, _i64, _vp]

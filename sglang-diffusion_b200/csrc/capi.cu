@@ -9,6 +9,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 
 #include "b200_w8a8_internal.h"
 
@@ -658,5 +659,62 @@ int b2_linear_w8a8_fp8(const void* x, int x_dtype, int64_t ldx, const uint8_t* W
   if (int r = b2_quant_fp8_rows(x, x_dtype, ldx, q, K, s, M, K, stream)) return r;
   return b2_gemm_e4m3(q, K, W, ldw, s, Bs, bias, bias_dtype, D, ldd, x_dtype, M, N, K, stream);
 }
+
+// ---- b2_linear_w8a8_int8_static: the fused int8 linear without any allocation by anybody ----
+// The scratch of b2_linear_w8a8_int8 (int8 codes + row scales between the quantizer and the GEMM) lives in a file-scope
+// device array instead of a caller-provided workspace.  Every device that loads the library holds the array until the
+// process exits.  `g_static_scratch` is a host-side stand-in for the symbol here in host code, NOT a device address:
+// the address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_static_scratch[B2_STATIC_SCRATCH_BYTES];
+
+static constexpr int kMaxStaticDevices = 64;
+static void* g_static_scratch_ptr[kMaxStaticDevices];  // per device, filled on first use
+static std::mutex g_static_scratch_mutex;
+
+static int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(B2_ERR_CUDA, "int8_scaled_mm_with_quant (static): cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxStaticDevices)
+    return fail(B2_ERR_ARG, "int8_scaled_mm_with_quant (static): device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e != cudaSuccess || ptr == nullptr)
+      return fail(B2_ERR_CUDA, "int8_scaled_mm_with_quant (static): cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+    g_static_scratch_ptr[dev] = ptr;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return B2_OK;
+}
+
+size_t b2_linear_w8a8_int8_static_max_bytes(void) { return B2_STATIC_SCRATCH_BYTES; }
+
+int b2_linear_w8a8_int8_static(const void* x, int x_dtype, int64_t ldx, const int8_t* W, int64_t ldw, const float* Bs,
+                               const void* bias, int bias_dtype, void* D, int64_t ldd, int M, int N, int K,
+                               b2_stream_t stream) {
+  if (int r = check_arch()) return r;
+  if (int r = check_act_dtype(x_dtype, "int8_scaled_mm_with_quant (static): mat1")) return r;
+  if (M < 0 || N <= 0 || K <= 0) return fail(B2_ERR_ARG, "int8_scaled_mm_with_quant (static): bad sizes M=%d N=%d K=%d", M, N, K);
+  if (M == 0) return B2_OK;
+  const size_t need = ws_bytes(M, K);
+  if (need > static_cast<size_t>(B2_STATIC_SCRATCH_BYTES))
+    return fail(B2_ERR_ARG,
+                "int8_scaled_mm_with_quant (static): M=%d x K=%d needs %zu bytes of scratch, the built-in array holds %zu "
+                "(B2_STATIC_SCRATCH_BYTES); use b2_linear_w8a8_int8 with a caller workspace",
+                M, K, need, static_cast<size_t>(B2_STATIC_SCRATCH_BYTES));
+  void* scratch = nullptr;
+  if (int r = static_scratch_for_current_device(&scratch)) return r;
+  // Nothing in the scratch has to start at zero: the quantizer writes all M x K codes and all M scales before the GEMM
+  // (next in the same stream) reads exactly those; rows past M of the GEMM's activation box are zero-filled by TMA
+  // from the tensor map's extent, not read from the array.
+  int8_t* q = static_cast<int8_t*>(scratch);
+  float* s = reinterpret_cast<float*>(static_cast<uint8_t*>(scratch) +
+                                      ((static_cast<size_t>(M) * K + 255) & ~static_cast<size_t>(255)));
+  if (int r = b2_quant_int8_rows(x, x_dtype, ldx, q, K, s, M, K, stream)) return r;
+  return b2_gemm_s8(q, K, W, ldw, s, Bs, bias, bias_dtype, D, ldd, x_dtype, M, N, K, stream);
+}
+
 
 }  // extern "C"

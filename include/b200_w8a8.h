@@ -303,6 +303,23 @@ int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const* signal_pa
                                int64_t set_stride_bytes, int dtype, int rank, int world, int max_blocks,
                                b2_stream_t stream);
 
+/* Step 2 fused with what follows a row-parallel layer in a decoder block: all-reduce + fused_add_rmsnorm + the next
+ * layer's activation quantizer in ONE launch (the reference's fused all-reduce + RMSNorm hook,
+ * python/sglang/srt/distributed/parallel_state.py:648-698 GroupCoordinator.fused_allreduce_rmsnorm, called from
+ * python/sglang/srt/layers/layernorm.py forward_with_allreduce_fusion; norm arithmetic of
+ * sgl-kernel/csrc/elementwise/fused_add_rms_norm_kernel.cu).  After b2_gemm_*_push_symm:
+ *   t      = out_t( sum over ranks of the pushed partials )      -- fp32 in rank order, one rounding (== step 2)
+ *   sum    = f32(t) + f32(residual);  residual <- out_t(sum)      (residual may be NULL: plain rmsnorm of t)
+ *   y      = out_t( (sum * rsqrt(mean(sum^2) + eps)) * weight )   (written to y_out when not NULL)
+ *   q, s   = quantizer `qmode` of y (B2_QMODE_INT8_ROWS / FP8_ROWS / FP8_GROUP128), layouts of b2_rmsnorm_quant
+ * Equal bit for bit to b2_allreduce_symm_gathered followed by b2_rmsnorm_quant.  One CTA (and one cross-GPU barrier
+ * slot) per row: M <= min(max_blocks, 1024 / world) -- decode shapes. */
+int b2_allreduce_symm_gathered_rmsnorm_quant(const void* local_buf, uint32_t* const* signal_pads_dev, void* residual,
+                                             int64_t ldr, const void* weight, float eps, int qmode, uint8_t* q,
+                                             int64_t ldq, float* s, int64_t s_row_stride, int64_t s_grp_stride,
+                                             void* y_out, int64_t ldy, int M, int N, int64_t set_stride_bytes,
+                                             int dtype, int rank, int world, int max_blocks, b2_stream_t stream);
+
 /* Prefill form (M >= 32 * world): GEMM with a SCATTER epilogue + the same gathered sum = a fused reduce-scatter.
  * The sum of a row-parallel layer is only needed row-sharded when the next operation is token-wise (sequence-parallel
  * norm / quantizer, or an all-gather later): each rank then keeps rows [rank * M/world, (rank+1) * M/world).  The

@@ -105,6 +105,38 @@ class SymmAllReduce:
                                                            torch.cuda.current_stream(self.device).cuda_stream))
         return out
 
+    def fits_reduce_rmsnorm(self, M: int, N: int, dtype: torch.dtype) -> bool:
+        return self.fits_push(M, N, dtype) and M <= min(self.max_blocks, 1024 // self.world) and N <= 32768
+
+    def reduce_gathered_rmsnorm_quant(self, M: int, N: int, dtype: torch.dtype, weight: torch.Tensor, eps: float,
+                                      residual: Optional[torch.Tensor] = None, mode: str = "int8",
+                                      return_normed: bool = False):
+        """After push_gemm: the all-reduce's barrier + local sum, the residual add (in place), RMSNorm and the next
+        layer's activation quantizer in ONE launch (b2_allreduce_symm_gathered_rmsnorm_quant; the reference's
+        fused_allreduce_rmsnorm hook, parallel_state.py:648-698, plus the quantizer that follows it).
+        mode "int8" | "fp8" | "fp8_group128".  Returns (q, scales[, normed]) like ops.rmsnorm_quant."""
+        from . import ops
+
+        qm = {"int8": 0, "fp8": 1, "fp8_group128": 2}[mode]
+        assert weight.is_contiguous() and weight.dtype == dtype and weight.numel() == N
+        if residual is not None:
+            assert residual.is_contiguous() and residual.shape == (M, N) and residual.dtype == dtype
+        q = torch.empty(M, N, dtype=torch.int8 if qm == 0 else ops.fp8_dtype, device=self.device)
+        if qm == 2:
+            s = ops.create_per_token_group_quant_fp8_output_scale((M, N), self.device, 128, True)
+            srow, sgrp = s.stride(0), s.stride(1)
+        else:
+            s = torch.empty(M, 1, dtype=torch.float32, device=self.device)
+            srow, sgrp = 1, 0
+        y = torch.empty(M, N, dtype=dtype, device=self.device) if return_normed else None
+        with torch.cuda.device(self.device):
+            capi.check(capi.lib.b2_allreduce_symm_gathered_rmsnorm_quant(
+                self.buf.data_ptr(), self.pads_dev, None if residual is None else residual.data_ptr(), N,
+                weight.data_ptr(), float(eps), qm, q.data_ptr(), N, s.data_ptr(), srow, sgrp,
+                None if y is None else y.data_ptr(), N, M, N, self.set_stride, _DT[dtype], self.rank, self.world,
+                self.max_blocks, torch.cuda.current_stream(self.device).cuda_stream))
+        return (q, s, y) if return_normed else (q, s)
+
     # ---- prefill: scatter epilogue + gathered sum = fused reduce-scatter (b2_gemm_*_scatter_symm) ----
 
     def fits_scatter(self, M: int, N: int, dtype: torch.dtype) -> bool:

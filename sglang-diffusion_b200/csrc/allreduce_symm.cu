@@ -26,67 +26,9 @@
 #include <cstdio>
 
 #include "b200_w8a8_internal.h"
+#include "symm_common.cuh"
 
 namespace b2 {
-
-#define AR_DEVICE __device__ __forceinline__
-
-AR_DEVICE void st_release_sys(uint32_t* addr, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
-}
-AR_DEVICE void st_relaxed_sys(uint32_t* addr, uint32_t v) {
-  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
-}
-AR_DEVICE uint32_t ld_acquire_sys(const uint32_t* addr) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
-  return v;
-}
-
-// Signal pad of a rank (u32 words): [0, world * blocks) flags, flag (b, r) = last barrier number rank r announced to
-// this rank for CTA b;  [kEpochWord + b] = barrier number CTA b of THIS rank has completed (kept on the device so
-// that a CUDA-graph replay, whose kernel arguments are frozen, still advances).
-constexpr int kEpochWord = 1024;
-// [kTimeoutWord] = barrier number at which a wait of THIS rank gave up (0 = never); see b2_set_allreduce_timeout_ms
-constexpr int kTimeoutWord = 1024 + 512;
-
-// Barrier number `seq` between CTA `blockIdx.x` of all ranks.  A posted release-store to every peer (no NVLink round
-// trip), then an acquire-poll of the local pad.  Barrier numbers only grow and a peer can be at most one barrier
-// ahead, so "flag - seq >= 0" is the arrival test and nothing is ever reset.  Everything this CTA wrote before the
-// barrier (bar.sync makes the release cumulative over the whole CTA) is visible to the peers after it.
-// RELEASE = false when this CTA has written nothing a peer will read since the last barrier (the partials of the
-// preceding GEMM kernel are already visible at its completion; "I have finished READING" needs no release either:
-// the loads have returned before the dependent stores that precede the bar.sync were issued).
-// A peer that is only late (first-iteration skew, a weight load or a compile on one rank, a debugger) must not poison
-// this rank's CUDA context, so the wait never traps.  timeout_ns == 0 (default) waits for ever, like the reference's
-// custom all-reduce (custom_all_reduce.cuh:204-260) and leaves hangs to the host watchdog; otherwise the wait gives up
-// after timeout_ns of %globaltimer, records the barrier number in word kTimeoutWord of the local pad for the host to
-// read (the result of that call is then undefined) and lets the kernel finish.
-template <bool RELEASE>
-AR_DEVICE void xgpu_barrier(uint32_t* const* pads, int rank, int world, uint32_t seq, unsigned long long timeout_ns) {
-  __syncthreads();
-  if (static_cast<int>(threadIdx.x) < world) {
-    const int peer = static_cast<int>(threadIdx.x);
-    uint32_t* send = pads[peer] + static_cast<size_t>(blockIdx.x) * world + rank;
-    if constexpr (RELEASE) st_release_sys(send, seq);
-    else st_relaxed_sys(send, seq);
-    const uint32_t* recv = pads[rank] + static_cast<size_t>(blockIdx.x) * world + peer;
-    unsigned int spins = 0;
-    unsigned long long t0 = 0;
-    while (static_cast<int32_t>(ld_acquire_sys(recv) - seq) < 0) {
-      if (timeout_ns != 0 && (++spins & 1023u) == 0) {
-        unsigned long long now;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-        if (t0 == 0) t0 = now;
-        else if (now - t0 > timeout_ns) {
-          pads[rank][kTimeoutWord] = seq;
-          break;
-        }
-      }
-    }
-  }
-  __syncthreads();
-}
 
 template <bool BF16>
 AR_DEVICE uint4 multimem_ld_reduce_add(const void* mc) {
@@ -220,8 +162,6 @@ __global__ void __launch_bounds__(512) allreduce_one_shot_kernel(uint4* const* b
 // call of a different size could land its set (n+1)&1 inside the region a slow peer is still summing for call n.
 // The same kernel finishes the scatter epilogue of the prefill GEMM (gemm_sm100.cu, RS): there every rank's slots hold
 // only the rows it owns, and `out` is this rank's [M / world, N] share of the sum (a reduce-scatter).
-constexpr int kGatherCounterWord = 1024 + 520;
-constexpr int kGatherDoneWord = 1024 + 521;
 
 template <bool BF16>
 __global__ void __launch_bounds__(512) allreduce_gathered_kernel(const uint4* __restrict__ local_buf,
@@ -538,6 +478,46 @@ extern "C" int b2_allreduce_symm_gathered_bcast(const void* local_buf, uint32_t*
           ? cudaLaunchKernelEx(&cfg, allreduce_gathered_bcast_kernel<true>, lb, signal_pads_dev, fb, o, nvec, set_vec, rank, world, tmo)
           : cudaLaunchKernelEx(&cfg, allreduce_gathered_bcast_kernel<false>, lb, signal_pads_dev, fb, o, nvec, set_vec, rank, world, tmo);
   if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "allreduce_symm_gathered_bcast launch: %s", cudaGetErrorString(le));
+  count_launch();
+  return B2_OK;
+}
+
+extern "C" int b2_allreduce_symm_gathered_rmsnorm_quant(const void* local_buf, uint32_t* const* signal_pads_dev,
+                                                        void* residual, int64_t ldr, const void* weight, float eps,
+                                                        int qmode, uint8_t* q, int64_t ldq, float* s,
+                                                        int64_t s_row_stride, int64_t s_grp_stride, void* y_out,
+                                                        int64_t ldy, int M, int N, int64_t set_stride_bytes, int dtype,
+                                                        int rank, int world, int max_blocks, b2_stream_t stream) {
+  const char* op = "allreduce_symm_gathered_rmsnorm_quant";
+  if (!local_buf || !signal_pads_dev || !weight || !q || !s) return fail_msg(B2_ERR_ARG, "%s: null pointer", op);
+  if (dtype != B2_DTYPE_BF16 && dtype != B2_DTYPE_F16) return fail_msg(B2_ERR_ARG, "%s: dtype must be bfloat16 or float16", op);
+  if (world < 2 || world > 8 || rank < 0 || rank >= world) return fail_msg(B2_ERR_ARG, "%s: world size must be 2..8, rank inside it", op);
+  if (qmode != B2_QMODE_INT8_ROWS && qmode != B2_QMODE_FP8_ROWS && qmode != B2_QMODE_FP8_GROUP128)
+    return fail_msg(B2_ERR_ARG, "%s: qmode must be INT8_ROWS, FP8_ROWS or FP8_GROUP128", op);
+  if (M <= 0 || N <= 0 || N % 8 != 0 || (qmode == B2_QMODE_FP8_GROUP128 && N % 128 != 0))
+    return fail_msg(B2_ERR_ARG, "%s: M=%d N=%d (N must be a multiple of 8; of 128 for the group mode)", op, M, N);
+  if (N > 1024 * 4 * 8) return fail_msg(B2_ERR_ARG, "%s: N=%d exceeds the 32768 columns a CTA can hold in registers", op, N);
+  int blocks_max = max_blocks < kEpochWord / world ? max_blocks : kEpochWord / world;
+  if (M > blocks_max)
+    return fail_msg(B2_ERR_ARG, "%s: M=%d rows need one barrier CTA each, the signal pad takes %d (decode shapes only)", op, M, blocks_max);
+  const uintptr_t al = reinterpret_cast<uintptr_t>(local_buf) | reinterpret_cast<uintptr_t>(weight) |
+                       reinterpret_cast<uintptr_t>(residual) | reinterpret_cast<uintptr_t>(y_out);
+  if (al % 16 != 0 || reinterpret_cast<uintptr_t>(q) % 8 != 0) return fail_msg(B2_ERR_ARG, "%s: buffers must be 16-byte aligned", op);
+  if ((residual && (ldr < N || ldr % 8 != 0)) || (y_out && (ldy < N || ldy % 8 != 0)) || ldq < N || ldq % 8 != 0)
+    return fail_msg(B2_ERR_ARG, "%s: row strides must cover N and keep rows 16-byte (codes: 8-byte) aligned", op);
+  const long long slot_bytes = static_cast<long long>(M) * N * 2;
+  if (set_stride_bytes == 0) set_stride_bytes = slot_bytes * world;
+  if (set_stride_bytes % 16 != 0 || set_stride_bytes < slot_bytes * world)
+    return fail_msg(B2_ERR_ARG, "%s: set stride must be a multiple of 16 and hold world slots", op);
+  FusedQuantArgs a{};
+  a.x = local_buf; a.ldx = N; a.residual = residual; a.ldr = ldr; a.weight = weight; a.eps = eps; a.y = y_out; a.ldy = ldy;
+  a.q = q; a.ldq = ldq; a.s = s; a.s_row_stride = s_row_stride; a.s_grp_stride = s_grp_stride; a.s_exp_stride = 0;
+  a.masked_m = nullptr; a.tokens_per_expert = 1; a.M = M; a.K = N; a.q_eps = 1e-10f; a.fmin = -448.f; a.fmax = 448.f;
+  a.gather_world = world; a.gather_rank = rank; a.gather_set_stride = set_stride_bytes / 2;
+  a.gather_pads = signal_pads_dev;
+  a.gather_timeout_ns = static_cast<unsigned long long>(g_ar_timeout_ms.load()) * 1000000ull;
+  cudaError_t le = fused_quant_launch(3, qmode, dtype, a, static_cast<cudaStream_t>(stream));
+  if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "%s launch: %s", op, cudaGetErrorString(le));
   count_launch();
   return B2_OK;
 }

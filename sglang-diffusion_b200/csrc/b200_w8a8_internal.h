@@ -41,8 +41,15 @@ struct FusedQuantArgs {
   const int32_t* row_map;   // optional gather: output row r quantizes input row row_map[r] / row_div
   int row_div;
   int row_limit;            // ids >= row_limit are padding rows (all-zero codes)
+  // prod 3 (gathered sum + rmsnorm): x is this rank's gather buffer (allreduce_symm.cu, gathered form): 2 sets
+  // `gather_set_stride` ELEMENTS apart of `gather_world` slots of M x K elements (ldx == K); the kernel takes the
+  // barrier and advances the set counter exactly as allreduce_gathered_kernel does
+  int gather_world, gather_rank;
+  int64_t gather_set_stride;
+  uint32_t* const* gather_pads;
+  unsigned long long gather_timeout_ns;
 };
-// prod: 0 none, 1 silu_and_mul, 2 rmsnorm;  mode: 0 int8 rows, 1 fp8 rows, 2 fp8 1x128 (v1), 3 fp8 1x128 (v2)
+// prod: 0 none, 1 silu_and_mul, 2 rmsnorm, 3 gathered sum (row-parallel partials of `gather_world` ranks) + rmsnorm;  mode: 0 int8 rows, 1 fp8 rows, 2 fp8 1x128 (v1), 3 fp8 1x128 (v2)
 cudaError_t fused_quant_launch(int prod, int mode, int x_dtype, const FusedQuantArgs& a, cudaStream_t st);
 cudaError_t quant_fp8_tensor(const void* x, int x_dtype, uint8_t* q, float* s, float* s_repeat, int64_t n,
                              int64_t rows, int is_static, cudaStream_t st);

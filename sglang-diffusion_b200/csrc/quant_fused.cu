@@ -9,6 +9,13 @@
 //                      sgl-kernel/csrc/elementwise/fused_add_rms_norm_kernel.cu -> flashinfer norm.cuh
 //                      FusedAddRMSNormKernel), y = T((s * rsqrt(mean(s^2) + eps)) * w); residual may be NULL (plain
 //                      rmsnorm)
+//     PROD = GATHER_RMSNORM  the same, but x = T(sum over `world` slots of this rank's gather buffer, fp32 in rank
+//                      order) -- the row-parallel partial outputs the preceding GEMM's epilogue pushed to every rank
+//                      (b2_gemm_*_push_symm).  The kernel IS the second half of that all-reduce: cross-GPU barrier,
+//                      local sum, set-counter advance (allreduce_symm.cu, gathered form), followed in registers by
+//                      residual add, RMSNorm and the next layer's quantizer: all-reduce + fused_add_rmsnorm + quantize
+//                      in one launch (python/sglang/srt/distributed/parallel_state.py:648-698 fused_allreduce_rmsnorm,
+//                      python/sglang/srt/layers/layernorm.py forward_with_allreduce_fusion).  One row per CTA.
 //     MODE = INT8_ROWS / FP8_ROWS   per-token scales, arithmetic of quant.cu (vec.h:190-228 / per_token_quant_fp8.cu)
 //            FP8_G128_V1            1x128 groups, s = amax/448, q = e4m3(x / s)      (per_token_group_quant_8bit.cu)
 //            FP8_G128_V2            1x128 groups, s = amax*(1/448), q = e4m3(x*(448/amax))  (..._8bit_v2.cu)
@@ -26,10 +33,11 @@
 #include "b200_w8a8_internal.h"
 #include "ptx.cuh"
 #include "quant_common.cuh"
+#include "symm_common.cuh"
 
 namespace b2 {
 
-enum class Prod { NONE, SILU_MUL, RMSNORM };
+enum class Prod { NONE, SILU_MUL, RMSNORM, GATHER_RMSNORM };
 enum class QM { INT8_ROWS, FP8_ROWS, FP8_G128_V1, FP8_G128_V2 };
 
 B2_DEVICE float tanh_approx(float x) {
@@ -61,7 +69,8 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
   // PACKED (8 per uint4, 16 registers instead of 32: ncu on the fp32-cached form shows issue_active 48 % and
   // long_scoreboard 5.5 warps per issue -- latency-bound at 50 % occupancy).  RMSNORM needs the unrounded fp32 sums
   // for the norm and keeps four fp32 vectors.
-  constexpr bool PACKED = PROD != Prod::RMSNORM;
+  constexpr bool RMS = PROD == Prod::RMSNORM || PROD == Prod::GATHER_RMSNORM;
+  constexpr bool PACKED = !RMS;
   constexpr int NC = 4;               // 16-byte vectors cached per thread (8 was measured: worse below K = 8192)
   constexpr int VEC = 8;              // elements per vector
   constexpr int ROWS = BLOCK / TPR;
@@ -71,6 +80,26 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
 
   pdl_launch_dependents();
   pdl_wait_prior_grids();
+
+  int64_t gather_base = 0;  // element offset of the set in use
+  if constexpr (PROD == Prod::GATHER_RMSNORM) {
+    // this rank's GEMM has completed (wait above): its pushes are performed.  One barrier -- every rank's GEMM has
+    // completed -- then everything below reads local memory only.
+    uint32_t* pad = a.gather_pads[a.gather_rank];
+    const uint32_t epoch = pad[kEpochWord + blockIdx.x];
+    const uint32_t counter = pad[kGatherCounterWord];
+    xgpu_barrier<true>(a.gather_pads, a.gather_rank, a.gather_world, epoch + 1, a.gather_timeout_ns);
+    gather_base = static_cast<int64_t>(counter & 1u) * a.gather_set_stride;
+    if (threadIdx.x == 0) {
+      pad[kEpochWord + blockIdx.x] = epoch + 1;
+      __threadfence();
+      const uint32_t done = atomicAdd(&pad[kGatherDoneWord], 1u);
+      if (done == gridDim.x - 1) {  // last CTA of this call: every CTA has read the counter
+        pad[kGatherDoneWord] = 0;
+        pad[kGatherCounterWord] = counter + 1;
+      }
+    }
+  }
 
   const int r_in_cta = threadIdx.x / TPR;
   const int t = threadIdx.x % TPR;
@@ -109,7 +138,30 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
       for (int j = 0; j < VEC; ++j) f[i][j] = 0.f;
     }
     if (on) {
-      const uint4 raw = ld_stream(reinterpret_cast<const uint4*>(xr) + v);
+      uint4 raw;
+      if constexpr (PROD == Prod::GATHER_RMSNORM) {
+        // rank-ordered fp32 sum of the slots, one rounding to T: bit-identical to allreduce_gathered_kernel
+        const uint4* sp = reinterpret_cast<const uint4*>(xr + gather_base) + v;
+        const int64_t slot_vec = a.M * static_cast<int64_t>(a.K) / VEC;
+        float acc[VEC];
+        {
+          const uint4 p0 = ld_stream(sp);
+          const T* pe = reinterpret_cast<const T*>(&p0);
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) acc[j] = to_f32(pe[j]);
+        }
+        for (int r = 1; r < a.gather_world; ++r) {
+          const uint4 pr = ld_stream(sp + r * slot_vec);
+          const T* pe = reinterpret_cast<const T*>(&pr);
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) acc[j] = __fadd_rn(acc[j], to_f32(pe[j]));
+        }
+        T* ro = reinterpret_cast<T*>(&raw);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) ro[j] = from_f32<T>(acc[j]);
+      } else {
+        raw = ld_stream(reinterpret_cast<const uint4*>(xr) + v);
+      }
       const T* e = reinterpret_cast<const T*>(&raw);
       if constexpr (PROD == Prod::NONE) {
         yc[i] = raw;
@@ -150,7 +202,7 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
   }
 
   constexpr int SHFL_W = TPR < 32 ? TPR : 32;
-  if constexpr (PROD == Prod::RMSNORM) {
+  if constexpr (RMS) {
 #pragma unroll
     for (int o = SHFL_W / 2; o > 0; o >>= 1) sum_sq += __shfl_xor_sync(0xffffffffu, sum_sq, o);
     if constexpr (WPR > 1) {
@@ -295,7 +347,7 @@ template <typename T, Prod PROD, QM MODE>
 static cudaError_t dispatch_fused_tpr(const FusedQuantArgs& a, cudaStream_t st) {
   const int nvec = a.K / 8;
   constexpr int NCH = 4;  // vectors a thread caches (fused_rows_kernel::NC)
-  int tpr = 32;
+  int tpr = PROD == Prod::GATHER_RMSNORM ? 128 : 32;  // the gathered form takes a cross-GPU barrier per CTA: one row per CTA
   while (tpr < 1024 && nvec > tpr * NCH) tpr *= 2;
   // few rows (decode): spread a row over more threads as long as every thread keeps a vector
   while (tpr < 1024 && a.M * static_cast<int64_t>(tpr) < 148 * 1024 && nvec >= tpr * 2) tpr *= 2;
@@ -321,6 +373,9 @@ static cudaError_t dispatch_fused(int prod, int mode, const FusedQuantArgs& a, c
   B2_FUSED_CASE(Prod::RMSNORM, QM::INT8_ROWS)
   B2_FUSED_CASE(Prod::RMSNORM, QM::FP8_ROWS)
   B2_FUSED_CASE(Prod::RMSNORM, QM::FP8_G128_V1)
+  B2_FUSED_CASE(Prod::GATHER_RMSNORM, QM::INT8_ROWS)
+  B2_FUSED_CASE(Prod::GATHER_RMSNORM, QM::FP8_ROWS)
+  B2_FUSED_CASE(Prod::GATHER_RMSNORM, QM::FP8_G128_V1)
 #undef B2_FUSED_CASE
   return cudaErrorInvalidValue;
 }

@@ -257,6 +257,33 @@ class QuantLinear(torch.nn.Module):
                                      bias)
         return comm.all_reduce(part).view(*x.shape[:-1], N)
 
+    def forward_allreduce_rmsnorm_quant(self, x: torch.Tensor, norm_weight: torch.Tensor, eps: float,
+                                        residual: Optional[torch.Tensor] = None, mode: str = "int8",
+                                        return_normed: bool = False):
+        """Row-parallel layer + all-reduce + fused_add_rmsnorm + the NEXT layer's activation quantizer: what follows
+        o_proj / down_proj in a decoder block (RMSNorm.forward_with_allreduce_fusion, python/sglang/srt/layers/
+        layernorm.py:300-340 -> GroupCoordinator.fused_allreduce_rmsnorm, parallel_state.py:648-698, then the quantizer
+        of qkv_proj / gate_up_proj).  `residual` [M, N] is updated in place to sum + residual.  Returns (q, scales[,
+        normed]) as ops.rmsnorm_quant does.  Decode shapes with a SymmAllReduce attached take two launches in total:
+        the GEMM pushing its partials to every rank, and b2_allreduce_symm_gathered_rmsnorm_quant."""
+        assert self.parallel == "row"
+        bias = self.bias if self.tp_rank == 0 else None
+        x2d = x.view(-1, x.shape[-1])
+        M, N = x2d.shape[0], self.weight.shape[1]
+        comm = getattr(self, "symm_comm", None)
+        if (self.tp_size > 1 and comm is not None and x.is_cuda and comm.fits_reduce_rmsnorm(M, N, x.dtype)
+                and isinstance(self.quant_method, (W8A8Int8LinearMethod, W8A8Fp8LinearMethod))):
+            with capi.static_weights():
+                if isinstance(self.quant_method, W8A8Int8LinearMethod):
+                    q, s = ops.per_token_quant_int8(x2d)
+                else:
+                    q, s = ops.sglang_per_token_quant_fp8(x2d)
+                comm.push_gemm(q, self.weight, s.view(-1), self.weight_scale.view(-1), x.dtype, bias)
+                return comm.reduce_gathered_rmsnorm_quant(M, N, x.dtype, norm_weight, eps, residual=residual, mode=mode,
+                                                          return_normed=return_normed)
+        out = self.forward(x).view(M, N)
+        return ops.rmsnorm_quant(out, norm_weight, eps, residual=residual, mode=mode, return_normed=return_normed)
+
     def forward_reduce_scatter(self, x: torch.Tensor) -> torch.Tensor:
         """Row-parallel layer whose summed output is wanted ROW-SHARDED: returns rows [tp_rank * M/tp, (tp_rank+1) * M/tp)
         of the sum -- RowParallelLinear.forward(skip_all_reduce=True) followed by LayerCommunicator._tp_reduce_scatter

@@ -115,6 +115,21 @@ def main():
                 # dynamic 8-bit activations against the exact product of the same quantized weights: e4m3 keeps 3
                 # significand bits (<= 6 % per element), int8 7 bits
                 assert err < (3e-2 if int8 else 6e-2), (name, M, err)
+            if check and par == "row" and world > 1 and M == 64:
+                # row-parallel layer + all-reduce + fused_add_rmsnorm + next quantizer (two launches with --symm) against
+                # the unfused composition: same sums up to the all-reduce's summation order (<= 1 bf16 ulp per element)
+                gn = torch.Generator(device=dev).manual_seed(77)
+                wn = (torch.rand(N, generator=gn, device=dev) + 0.5).bfloat16()
+                res = torch.randn(M, N, generator=gn, device=dev).bfloat16()
+                r1, r2 = res.clone(), res.clone()
+                mode = "int8" if int8 else "fp8"
+                q1, s1, y1 = layer.forward_allreduce_rmsnorm_quant(x, wn, 1e-6, residual=r1, mode=mode, return_normed=True)
+                q2, s2, y2 = b2.ops.rmsnorm_quant(layer(x), wn, 1e-6, residual=r2, mode=mode, return_normed=True)
+                torch.cuda.synchronize()
+                assert (r1.float() - r2.float()).abs().max().item() <= 2.0 ** -6 * r2.float().abs().max().item(), name
+                assert (y1.float() - y2.float()).abs().max().item() <= 2.0 ** -5 * y2.float().abs().max().item(), name
+                d1, d2 = q1.float() * s1, q2.float() * s2
+                assert (d1 - d2).abs().max().item() <= 0.08 * d2.abs().max().item(), name
             iters = 200 if M == 64 else 30
             t_all = timed(lambda: layer(x), iters)
             t_mm = timed(lambda: method.apply(layer, x, None), iters)

@@ -313,7 +313,7 @@ int b2_allreduce_symm_gathered(const void* local_buf, uint32_t* const* signal_pa
  *   y      = out_t( (sum * rsqrt(mean(sum^2) + eps)) * weight )   (written to y_out when not NULL)
  *   q, s   = quantizer `qmode` of y (B2_QMODE_INT8_ROWS / FP8_ROWS / FP8_GROUP128), layouts of b2_rmsnorm_quant
  * Equal bit for bit to b2_allreduce_symm_gathered followed by b2_rmsnorm_quant.  One CTA (and one cross-GPU barrier
- * slot) per row: M <= min(max_blocks, 1024 / world) -- decode shapes. */
+ * slot) per row, at most min(max_blocks, 1024 / world) CTAs; with more rows the CTAs loop. */
 int b2_allreduce_symm_gathered_rmsnorm_quant(const void* local_buf, uint32_t* const* signal_pads_dev, void* residual,
                                              int64_t ldr, const void* weight, float eps, int qmode, uint8_t* q,
                                              int64_t ldq, float* s, int64_t s_row_stride, int64_t s_grp_stride,
@@ -342,6 +342,24 @@ int b2_gemm_e4m3_scatter_symm(const uint8_t* A, int64_t lda, const uint8_t* W, i
                               const float* Bs, const void* bias, int bias_dtype, void* const* peer_bufs_host,
                               uint32_t* local_signal_pad, int64_t set_stride_bytes, int rank, int world,
                               int out_dtype, int M, int N, int K, b2_stream_t stream);
+
+/* Prefill, sequence-parallel norm ("reduce-scatter + fused next-layer norm for large M"): after
+ * b2_gemm_*_scatter_symm every rank sums ITS M/world rows, adds its rows of the residual (residual_local [M/world, N],
+ * updated in place -- the reference splits the residual the same way, communicator.py:556-559), applies RMSNorm and
+ * the next layer's per-token quantizer, and stores codes and scales straight into rows [rank*M/world, ...) of EVERY
+ * rank's activation buffer (act_bufs_dev: DEVICE array of the `world` peer mappings of one symmetric buffer; codes
+ * [M, N] at offset 0, fp32 scales [M] at scale_offset_bytes): the all-gather moves 1-byte codes instead of 2-byte
+ * sums, the norm is computed once per row instead of on every rank, and the summed rows never reach HBM.  A second
+ * barrier closes the kernel: when it completes, this rank's buffer holds all M rows -- the A operand and scales of the
+ * next column-parallel b2_gemm_s8 / b2_gemm_e4m3.  NVLink bytes per rank: (world-1)/world * M*N*2 in the GEMM's
+ * scatter + (world-1) * (M/world) * (N + 4) here, against 2*(world-1)/world * M*N*2 of an all-reduce.
+ * Codes, scales and residual rows equal, bit for bit, b2_allreduce_symm_gathered + b2_rmsnorm_quant on the same rows.
+ * qmode: B2_QMODE_INT8_ROWS or B2_QMODE_FP8_ROWS; M % world == 0, N % 16 == 0. */
+int b2_reduce_scatter_symm_rmsnorm_quant_allgather(const void* local_buf, uint32_t* const* signal_pads_dev,
+                                                   void* residual_local, int64_t ldr, const void* weight, float eps,
+                                                   int qmode, void* const* act_bufs_dev, int64_t scale_offset_bytes,
+                                                   void* y_local, int64_t ldy, int M, int N, int64_t set_stride_bytes,
+                                                   int dtype, int rank, int world, int max_blocks, b2_stream_t stream);
 
 /* All-reduce form of the same (callers that need the full sum on every rank -- RowParallelLinear.forward with
  * reduce_results, linear.py:1486-1490): after b2_gemm_*_scatter_symm, b2_allreduce_symm_gathered_bcast sums this rank's

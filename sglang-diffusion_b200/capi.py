@@ -32,7 +32,7 @@ SYMBOLS = [
     "b2_set_fused_decode", "b2_get_fused_decode",
     "b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered",
     "b2_gemm_s8_scatter_symm", "b2_gemm_e4m3_scatter_symm", "b2_allreduce_symm_gathered_bcast",
-    "b2_allreduce_symm_gathered_rmsnorm_quant",
+    "b2_allreduce_symm_gathered_rmsnorm_quant", "b2_reduce_scatter_symm_rmsnorm_quant_allgather",
     "b2_linear_w8a8_int8_static_max_bytes", "b2_linear_w8a8_int8_static",
     "b2_moe_max_padded", "b2_moe_align_block128", "b2_quant_int8_rows_gather", "b2_gemm_s8_grouped", "b2_moe_combine",
 ]
@@ -104,6 +104,9 @@ lib.b2_allreduce_symm_gathered.argtypes = [_vp, _vp, _vp, _i64, _i64, _i, _i, _i
 lib.b2_allreduce_symm_gathered_rmsnorm_quant.argtypes = [_vp, _vp, _vp, _i64, _vp, _f, _i, _vp, _i64, _vp, _i64, _i64, _vp,
                                                          _i64, _i, _i, _i64, _i, _i, _i, _i, _vp]
 lib.b2_allreduce_symm_gathered_rmsnorm_quant.restype = _i
+lib.b2_reduce_scatter_symm_rmsnorm_quant_allgather.argtypes = [_vp, _vp, _vp, _i64, _vp, _f, _i, _vp, _i64, _vp, _i64, _i, _i,
+                                                               _i64, _i, _i, _i, _i, _vp]
+lib.b2_reduce_scatter_symm_rmsnorm_quant_allgather.restype = _i
 lib.b2_allreduce_symm_gathered_bcast.argtypes = [_vp, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _i, _vp]
 for _n in ("b2_gemm_s8_push_symm", "b2_gemm_e4m3_push_symm", "b2_allreduce_symm_gathered",
            "b2_gemm_s8_scatter_symm", "b2_gemm_e4m3_scatter_symm", "b2_allreduce_symm_gathered_bcast"):

@@ -106,7 +106,7 @@ class SymmAllReduce:
         return out
 
     def fits_reduce_rmsnorm(self, M: int, N: int, dtype: torch.dtype) -> bool:
-        return self.fits_push(M, N, dtype) and M <= min(self.max_blocks, 1024 // self.world) and N <= 32768
+        return self.fits_push(M, N, dtype) and N <= 32768
 
     def reduce_gathered_rmsnorm_quant(self, M: int, N: int, dtype: torch.dtype, weight: torch.Tensor, eps: float,
                                       residual: Optional[torch.Tensor] = None, mode: str = "int8",
@@ -176,6 +176,38 @@ class SymmAllReduce:
         if inplace:
             return self.full_buf[:M * N * dtype.itemsize].view(dtype).view(M, N)
         return out
+
+    def fits_scatter_rmsnorm_allgather(self, M: int, N: int, dtype: torch.dtype) -> bool:
+        return (self.fits_scatter(M, N, dtype) and self.full_bufs_dev != 0 and N % 16 == 0 and N <= 32768
+                and self._act_scale_offset(M, N) + 4 * M <= self.full_buf.numel())
+
+    @staticmethod
+    def _act_scale_offset(M: int, N: int) -> int:
+        return (M * N + 255) // 256 * 256
+
+    def reduce_scattered_rmsnorm_quant_allgather(self, M: int, N: int, dtype: torch.dtype, weight: torch.Tensor,
+                                                 eps: float, residual_local: Optional[torch.Tensor] = None,
+                                                 mode: str = "int8"):
+        """After scatter_gemm: sum of this rank's M/world rows + residual add (its rows, in place) + RMSNorm + per-token
+        quantizer, codes and scales all-gathered into every rank's `full_buf` by peer stores
+        (b2_reduce_scatter_symm_rmsnorm_quant_allgather).  Returns (q [M, N], scales [M, 1]) -- VIEWS of full_buf,
+        valid until the next call that uses it: the input of the next column-parallel GEMM."""
+        from . import ops
+
+        qm = {"int8": 0, "fp8": 1}[mode]
+        rows = M // self.world
+        assert weight.is_contiguous() and weight.dtype == dtype and weight.numel() == N
+        if residual_local is not None:
+            assert residual_local.is_contiguous() and residual_local.shape == (rows, N) and residual_local.dtype == dtype
+        off = self._act_scale_offset(M, N)
+        with torch.cuda.device(self.device):
+            capi.check(capi.lib.b2_reduce_scatter_symm_rmsnorm_quant_allgather(
+                self.buf.data_ptr(), self.pads_dev, None if residual_local is None else residual_local.data_ptr(), N,
+                weight.data_ptr(), float(eps), qm, self.full_bufs_dev, off, None, N, M, N, self.set_stride, _DT[dtype],
+                self.rank, self.world, self.max_blocks, torch.cuda.current_stream(self.device).cuda_stream))
+        q = self.full_buf[:M * N].view(torch.int8 if qm == 0 else ops.fp8_dtype).view(M, N)
+        s = self.full_buf[off:off + 4 * M].view(torch.float32).view(M, 1)
+        return q, s
 
     def reduce_scattered(self, M: int, N: int, dtype: torch.dtype) -> torch.Tensor:
         """Barrier + rank-ordered fp32 sum of the `world` slots of this rank's rows -> fresh [M / world, N] tensor."""

@@ -498,8 +498,7 @@ extern "C" int b2_allreduce_symm_gathered_rmsnorm_quant(const void* local_buf, u
     return fail_msg(B2_ERR_ARG, "%s: M=%d N=%d (N must be a multiple of 8; of 128 for the group mode)", op, M, N);
   if (N > 1024 * 4 * 8) return fail_msg(B2_ERR_ARG, "%s: N=%d exceeds the 32768 columns a CTA can hold in registers", op, N);
   int blocks_max = max_blocks < kEpochWord / world ? max_blocks : kEpochWord / world;
-  if (M > blocks_max)
-    return fail_msg(B2_ERR_ARG, "%s: M=%d rows need one barrier CTA each, the signal pad takes %d (decode shapes only)", op, M, blocks_max);
+  if (blocks_max < 1) blocks_max = 1;
   const uintptr_t al = reinterpret_cast<uintptr_t>(local_buf) | reinterpret_cast<uintptr_t>(weight) |
                        reinterpret_cast<uintptr_t>(residual) | reinterpret_cast<uintptr_t>(y_out);
   if (al % 16 != 0 || reinterpret_cast<uintptr_t>(q) % 8 != 0) return fail_msg(B2_ERR_ARG, "%s: buffers must be 16-byte aligned", op);
@@ -516,6 +515,52 @@ extern "C" int b2_allreduce_symm_gathered_rmsnorm_quant(const void* local_buf, u
   a.gather_world = world; a.gather_rank = rank; a.gather_set_stride = set_stride_bytes / 2;
   a.gather_pads = signal_pads_dev;
   a.gather_timeout_ns = static_cast<unsigned long long>(g_ar_timeout_ms.load()) * 1000000ull;
+  a.gather_max_blocks = blocks_max;
+  cudaError_t le = fused_quant_launch(3, qmode, dtype, a, static_cast<cudaStream_t>(stream));
+  if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "%s launch: %s", op, cudaGetErrorString(le));
+  count_launch();
+  return B2_OK;
+}
+
+extern "C" int b2_reduce_scatter_symm_rmsnorm_quant_allgather(
+    const void* local_buf, uint32_t* const* signal_pads_dev, void* residual_local, int64_t ldr, const void* weight,
+    float eps, int qmode, void* const* act_bufs_dev, int64_t scale_offset_bytes, void* y_local, int64_t ldy, int M, int N,
+    int64_t set_stride_bytes, int dtype, int rank, int world, int max_blocks, b2_stream_t stream) {
+  const char* op = "reduce_scatter_symm_rmsnorm_quant_allgather";
+  if (!local_buf || !signal_pads_dev || !weight || !act_bufs_dev) return fail_msg(B2_ERR_ARG, "%s: null pointer", op);
+  if (dtype != B2_DTYPE_BF16 && dtype != B2_DTYPE_F16) return fail_msg(B2_ERR_ARG, "%s: dtype must be bfloat16 or float16", op);
+  if (world < 2 || world > 8 || rank < 0 || rank >= world) return fail_msg(B2_ERR_ARG, "%s: world size must be 2..8, rank inside it", op);
+  if (qmode != B2_QMODE_INT8_ROWS && qmode != B2_QMODE_FP8_ROWS)
+    return fail_msg(B2_ERR_ARG, "%s: qmode must be INT8_ROWS or FP8_ROWS", op);
+  if (M <= 0 || M % world != 0 || N <= 0 || N % 16 != 0 || N > 32768)
+    return fail_msg(B2_ERR_ARG, "%s: M=%d must be a positive multiple of world, N=%d a multiple of 16 up to 32768", op, M, N);
+  const int64_t codes = static_cast<int64_t>(M) * N;
+  if (scale_offset_bytes < codes || scale_offset_bytes % 16 != 0)
+    return fail_msg(B2_ERR_ARG, "%s: the scales must start at a 16-byte aligned offset behind the M*N codes", op);
+  const uintptr_t al = reinterpret_cast<uintptr_t>(local_buf) | reinterpret_cast<uintptr_t>(weight) |
+                       reinterpret_cast<uintptr_t>(residual_local) | reinterpret_cast<uintptr_t>(y_local);
+  if (al % 16 != 0) return fail_msg(B2_ERR_ARG, "%s: buffers must be 16-byte aligned", op);
+  const int rows = M / world;
+  if ((residual_local && (ldr < N || ldr % 8 != 0)) || (y_local && (ldy < N || ldy % 8 != 0)))
+    return fail_msg(B2_ERR_ARG, "%s: row strides must cover N and keep rows 16-byte aligned", op);
+  const long long slot_bytes = static_cast<long long>(rows) * N * 2;
+  if (set_stride_bytes == 0) set_stride_bytes = slot_bytes * world;
+  if (set_stride_bytes % 16 != 0 || set_stride_bytes < slot_bytes * world)
+    return fail_msg(B2_ERR_ARG, "%s: set stride must be a multiple of 16 and hold world slots", op);
+  int blocks_max = max_blocks < kEpochWord / world ? max_blocks : kEpochWord / world;
+  if (blocks_max < 1) blocks_max = 1;
+  FusedQuantArgs a{};
+  a.x = local_buf; a.ldx = N; a.residual = residual_local; a.ldr = ldr; a.weight = weight; a.eps = eps;
+  a.y = y_local; a.ldy = ldy;
+  a.q = nullptr; a.ldq = N; a.s = nullptr; a.s_row_stride = 1; a.s_grp_stride = 0; a.s_exp_stride = 0;
+  a.masked_m = nullptr; a.tokens_per_expert = 1; a.M = rows; a.K = N; a.q_eps = 1e-10f; a.fmin = -448.f; a.fmax = 448.f;
+  a.gather_world = world; a.gather_rank = rank; a.gather_set_stride = set_stride_bytes / 2;
+  a.gather_pads = signal_pads_dev;
+  a.gather_timeout_ns = static_cast<unsigned long long>(g_ar_timeout_ms.load()) * 1000000ull;
+  a.gather_max_blocks = blocks_max;
+  a.out_peers = reinterpret_cast<uint8_t* const*>(act_bufs_dev);
+  a.out_row0 = static_cast<int64_t>(rank) * rows;
+  a.out_scale_offset = scale_offset_bytes;
   cudaError_t le = fused_quant_launch(3, qmode, dtype, a, static_cast<cudaStream_t>(stream));
   if (le != cudaSuccess) return fail_msg(B2_ERR_CUDA, "%s launch: %s", op, cudaGetErrorString(le));
   count_launch();

@@ -48,6 +48,12 @@ struct FusedQuantArgs {
   int64_t gather_set_stride;
   uint32_t* const* gather_pads;
   unsigned long long gather_timeout_ns;
+  int gather_max_blocks;    // grid bound = barrier slots of the signal pad; the kernel loops over rows beyond it
+  // all-gather form (row modes only): codes go to row out_row0 + r of EVERY rank's buffer out_peers[p] (row stride ldq
+  // bytes) and the scales to the fp32 array out_scale_offset bytes into it; a second barrier closes the kernel.
+  // nullptr: outputs are local (q, s above).
+  uint8_t* const* out_peers;
+  int64_t out_row0, out_scale_offset;
 };
 // prod: 0 none, 1 silu_and_mul, 2 rmsnorm, 3 gathered sum (row-parallel partials of `gather_world` ranks) + rmsnorm;  mode: 0 int8 rows, 1 fp8 rows, 2 fp8 1x128 (v1), 3 fp8 1x128 (v2)
 cudaError_t fused_quant_launch(int prod, int mode, int x_dtype, const FusedQuantArgs& a, cudaStream_t st);

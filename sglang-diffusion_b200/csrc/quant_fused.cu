@@ -82,6 +82,7 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
   pdl_wait_prior_grids();
 
   int64_t gather_base = 0;  // element offset of the set in use
+  uint32_t gather_epoch = 0;
   if constexpr (PROD == Prod::GATHER_RMSNORM) {
     // this rank's GEMM has completed (wait above): its pushes are performed.  One barrier -- every rank's GEMM has
     // completed -- then everything below reads local memory only.
@@ -90,8 +91,9 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
     const uint32_t counter = pad[kGatherCounterWord];
     xgpu_barrier<true>(a.gather_pads, a.gather_rank, a.gather_world, epoch + 1, a.gather_timeout_ns);
     gather_base = static_cast<int64_t>(counter & 1u) * a.gather_set_stride;
+    gather_epoch = epoch;
     if (threadIdx.x == 0) {
-      pad[kEpochWord + blockIdx.x] = epoch + 1;
+      if (a.out_peers == nullptr) pad[kEpochWord + blockIdx.x] = epoch + 1;  // (with peers: epoch + 2, at the end)
       __threadfence();
       const uint32_t done = atomicAdd(&pad[kGatherDoneWord], 1u);
       if (done == gridDim.x - 1) {  // last CTA of this call: every CTA has read the counter
@@ -103,7 +105,8 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
 
   const int r_in_cta = threadIdx.x / TPR;
   const int t = threadIdx.x % TPR;
-  const int64_t row = static_cast<int64_t>(blockIdx.x) * ROWS + r_in_cta;
+  auto do_rows = [&](int64_t row_base) {
+  const int64_t row = row_base + r_in_cta;
   bool active = row < a.M;
   int64_t expert = 0, token = row;
   if (a.masked_m != nullptr) {  // [E, T, ...] layout: rows past masked_m[e] are neither read nor written
@@ -298,7 +301,17 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
       scale = __fdiv_rn(amax, 448.f);
       inv = (scale == 0.f) ? 0.f : __frcp_rn(scale);
     }
-    if (t == 0) a.s[expert * a.s_exp_stride + token * a.s_row_stride] = scale;
+    if (t == 0) {
+      bool local_scale = true;
+      if constexpr (PROD == Prod::GATHER_RMSNORM) {
+        if (a.out_peers != nullptr) {
+          local_scale = false;
+          for (int pr = 0; pr < a.gather_world; ++pr)
+            reinterpret_cast<float*>(a.out_peers[pr] + a.out_scale_offset)[a.out_row0 + rr] = scale;
+        }
+      }
+      if (local_scale) a.s[expert * a.s_exp_stride + token * a.s_row_stride] = scale;
+    }
 #pragma unroll
     for (int i = 0; i < NC; ++i) {
       const int v = t + i * TPR;
@@ -319,9 +332,38 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
             o2[j >> 1] = f32x2_to_e4m3x2(p, r);
           }
         }
-        reinterpret_cast<uint2*>(qr)[v] = out;
+        if constexpr (PROD == Prod::GATHER_RMSNORM) {
+          if (a.out_peers != nullptr) {
+#pragma unroll 1
+            for (int pi = 0; pi < a.gather_world; ++pi) {
+              const int pr = (a.gather_rank + pi) % a.gather_world;  // own copy first, then the peers in rotated order
+              reinterpret_cast<uint2*>(a.out_peers[pr] + (a.out_row0 + rr) * a.ldq)[v] = out;
+            }
+          } else {
+            reinterpret_cast<uint2*>(qr)[v] = out;
+          }
+        } else {
+          reinterpret_cast<uint2*>(qr)[v] = out;
+        }
       }
     }
+  }
+  };  // do_rows
+
+  if constexpr (PROD == Prod::GATHER_RMSNORM) {
+    // persistent over rows: the grid is bounded by the barrier slots of the signal pad (one per CTA)
+    for (int64_t rb = static_cast<int64_t>(blockIdx.x) * ROWS; rb < a.M; rb += static_cast<int64_t>(gridDim.x) * ROWS) {
+      do_rows(rb);
+      __syncthreads();  // s_red is reused by the next row
+    }
+    if (a.out_peers != nullptr) {
+      // all-gather form: the codes and scales of this CTA's rows are on their way to every rank; after this barrier
+      // CTA b of every rank has stored its rows, so when this kernel completes on a rank, ALL rows are in its copy
+      xgpu_barrier<true>(a.gather_pads, a.gather_rank, a.gather_world, gather_epoch + 2, a.gather_timeout_ns);
+      if (threadIdx.x == 0) a.gather_pads[a.gather_rank][kEpochWord + blockIdx.x] = gather_epoch + 2;
+    }
+  } else {
+    do_rows(static_cast<int64_t>(blockIdx.x) * ROWS);
   }
 }
 
@@ -329,7 +371,8 @@ template <typename T, Prod PROD, QM MODE, int TPR>
 static cudaError_t launch_fused(const FusedQuantArgs& a, cudaStream_t st) {
   constexpr int BLOCK = TPR >= 128 ? TPR : 128;
   constexpr int ROWS = BLOCK / TPR;
-  const int64_t grid = (a.M + ROWS - 1) / ROWS;
+  int64_t grid = (a.M + ROWS - 1) / ROWS;
+  if (PROD == Prod::GATHER_RMSNORM && grid > a.gather_max_blocks) grid = a.gather_max_blocks;  // the kernel loops over rows
   if (grid > 0x7fffffffll) return cudaErrorInvalidValue;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(static_cast<unsigned>(grid));
@@ -339,7 +382,7 @@ static cudaError_t launch_fused(const FusedQuantArgs& a, cudaStream_t st) {
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = (weight_prefetch_enabled() && a.M <= 128) ? 1 : 0;  // decode chains, see quant.cu launch_rows
+  cfg.numAttrs = ((weight_prefetch_enabled() && a.M <= 128) || PROD == Prod::GATHER_RMSNORM) ? 1 : 0;  // decode chains, see quant.cu launch_rows
   return cudaLaunchKernelEx(&cfg, fused_rows_kernel<T, PROD, MODE, TPR, BLOCK>, a);
 }
 

@@ -92,6 +92,39 @@ for kind in ("int8", "fp8"):
                     fails += 1
                     print(f"[rank {rank}] FAIL interleaved push call after {kind} M={M}", flush=True)
 
+# reduce-scatter + residual add + RMSNorm + quantizer + all-gather of the codes, one launch behind the scatter GEMM:
+# against the separate steps (rows of the one-shot sum -> ops.rmsnorm_quant on this rank's rows -> NCCL all-gather)
+for mode in ("int8", "fp8"):
+    for M, N, K in ((32 * world, 512, 256), (1024, 4096, 512), (2048, 5120, 640), (1024 + 32 * world, 1040, 384)):
+        if M % (32 * world) or not comm_rs.fits_scatter_rmsnorm_allgather(M, N, torch.bfloat16):
+            continue
+        for it in range(2):
+            q, s, W, Bs, bias = problem("int8", M, N, K, 3 * M + N + it)
+            rows = M // world
+            g = torch.Generator(device=dev).manual_seed(41 + it)  # same on every rank
+            wnorm = (torch.rand(N, generator=g, device=dev) + 0.5).bfloat16()
+            res_full = torch.randn(M, N, generator=g, device=dev).bfloat16()
+            res_a = res_full[rank * rows:(rank + 1) * rows].clone() if it == 0 else None
+            res_b = None if res_a is None else res_a.clone()
+            want_rows = reference(q, s, W, Bs, bias, M, N).clone()
+            qa, sa = ops.rmsnorm_quant(want_rows, wnorm, 1e-6, residual=res_a, mode=mode)
+            qa_all = torch.empty(M, N, dtype=torch.uint8, device=dev)
+            sa_all = torch.empty(M, 1, dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(qa_all, qa.view(torch.uint8).contiguous())
+            dist.all_gather_into_tensor(sa_all, sa.contiguous())
+            comm_rs.scatter_gemm(q, W.t(), s, Bs, torch.bfloat16, bias)
+            qb, sb = comm_rs.reduce_scattered_rmsnorm_quant_allgather(M, N, torch.bfloat16, wnorm, 1e-6,
+                                                                      residual_local=res_b, mode=mode)
+            torch.cuda.synchronize()
+            ok = (torch.equal(qa_all, qb.view(torch.uint8)) and torch.equal(sa_all, sb)
+                  and (res_a is None or torch.equal(res_a.view(torch.int16), res_b.view(torch.int16))))
+            if not ok:
+                fails += 1
+                nbad = (qa_all != qb.view(torch.uint8)).sum().item()
+                print(f"[rank {rank}] FAIL rs+rmsnorm+quant+allgather {mode} M={M} N={N} it={it} bad codes {nbad} "
+                      f"bad scales {(sa_all != sb).sum().item()}", flush=True)
+            dist.barrier()  # the views live in the shared buffer: keep the peers' next call behind this rank's reads
+
 # f16 output once
 M, N, K = 64 * world, 1024, 512
 g = torch.Generator(device=dev).manual_seed(5 + rank)
@@ -188,6 +221,33 @@ if TIMING:
 
         extra = (("fused_scatter_gemm+sum+allgather", fused_ar), ("same_in_place", fused_ar_inplace)) \
             if comm_rs.fits_scatter_all_reduce(M, N, torch.bfloat16) else ()
+        gq = torch.Generator(device=dev).manual_seed(3)
+        wnorm = (torch.rand(N, generator=gq, device=dev) + 0.5).bfloat16()
+        res_full = torch.randn(M, N, generator=gq, device=dev).bfloat16()
+        res_loc = res_full[rank * (M // world):(rank + 1) * (M // world)].clone()
+        q_all = torch.empty(M, N, dtype=torch.int8, device=dev)
+        s_all = torch.empty(M, 1, dtype=torch.float32, device=dev)
+
+        def nccl_ar_norm():  # all-reduce, then norm + quantizer of all M rows on every rank
+            ops.scaled_mm_out(q, Wt, s, Bs, plain, bias)
+            dist.all_reduce(plain)
+            ops.rmsnorm_quant(plain, wnorm, 1e-6, residual=res_full, mode="int8")
+
+        def nccl_rs_norm_ag():  # sequence-parallel norm with NCCL collectives
+            ops.scaled_mm_out(q, Wt, s, Bs, plain, bias)
+            dist.reduce_scatter_tensor(rs_out, plain)
+            ql, sl = ops.rmsnorm_quant(rs_out, wnorm, 1e-6, residual=res_loc, mode="int8")
+            dist.all_gather_into_tensor(q_all, ql)
+            dist.all_gather_into_tensor(s_all, sl)
+
+        def fused_rs_norm_ag():
+            comm_rs.scatter_gemm(q, Wt, s, Bs, torch.bfloat16, bias)
+            comm_rs.reduce_scattered_rmsnorm_quant_allgather(M, N, torch.bfloat16, wnorm, 1e-6, residual_local=res_loc, mode="int8")
+
+        if comm_rs.fits_scatter_rmsnorm_allgather(M, N, torch.bfloat16):
+            extra = extra + (("gemm+nccl_all_reduce+rmsnorm_quant", nccl_ar_norm),
+                             ("gemm+nccl_rs+rmsnorm_quant+nccl_ag", nccl_rs_norm_ag),
+                             ("scatter_gemm+fused_sum_rmsnorm_quant_allgather", fused_rs_norm_ag))
         res = {name: timed(fn) for name, fn in extra + (("gemm_only", gemm_only), ("scatter_gemm_only", scatter_only), ("gemm+nccl_all_reduce", nccl_ar),
                                                 ("gemm+nccl_reduce_scatter", nccl_rs), ("gemm+symm_all_reduce", symm_ar),
                                                 ("fused_scatter_gemm+sum", fused_rs))}

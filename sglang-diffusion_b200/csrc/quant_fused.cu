@@ -367,10 +367,15 @@ __global__ void __launch_bounds__(BLOCK) fused_rows_kernel(FusedQuantArgs a) {
   }
 }
 
-template <typename T, Prod PROD, QM MODE, int TPR>
+template <typename T, Prod PROD, QM MODE, int TPR, int MIN_BLOCK = 128>
 static cudaError_t launch_fused(const FusedQuantArgs& a, cudaStream_t st) {
-  constexpr int BLOCK = TPR >= 128 ? TPR : 128;
+  constexpr int BLOCK = TPR >= MIN_BLOCK ? TPR : MIN_BLOCK;
   constexpr int ROWS = BLOCK / TPR;
+  if constexpr (PROD == Prod::GATHER_RMSNORM && MIN_BLOCK == 128) {
+    // more rows than barrier slots (prefill, sequence-parallel norm): the CTAs loop over rows, so give every CTA
+    // 512 threads = several rows in flight per iteration
+    if (a.M > a.gather_max_blocks && TPR < 512) return launch_fused<T, PROD, MODE, TPR, 512>(a, st);
+  }
   int64_t grid = (a.M + ROWS - 1) / ROWS;
   if (PROD == Prod::GATHER_RMSNORM && grid > a.gather_max_blocks) grid = a.gather_max_blocks;  // the kernel loops over rows
   if (grid > 0x7fffffffll) return cudaErrorInvalidValue;

@@ -284,6 +284,37 @@ class QuantLinear(torch.nn.Module):
         out = self.forward(x).view(M, N)
         return ops.rmsnorm_quant(out, norm_weight, eps, residual=residual, mode=mode, return_normed=return_normed)
 
+    def forward_reduce_scatter_rmsnorm_quant(self, x: torch.Tensor, norm_weight: torch.Tensor, eps: float,
+                                             residual_local: Optional[torch.Tensor] = None, mode: str = "int8"):
+        """Prefill form of forward_allreduce_rmsnorm_quant with a sequence-parallel norm: the row-parallel GEMM scatters
+        its partials to the row owners, every rank sums, adds ITS rows of the residual (`residual_local`
+        [M / tp, N], updated in place; LayerCommunicator._tp_reduce_scatter splits the residual the same way,
+        communicator.py:542-560), norms and quantizes its M / tp rows, and the 1-byte codes + scales are all-gathered
+        by peer stores.  Returns (q [M, N], scales [M, 1]) for the next column-parallel layer -- views of the
+        communicator's buffer when the fused path runs (valid until its next use)."""
+        assert self.parallel == "row" and self.tp_size > 1
+        bias = self.bias if self.tp_rank == 0 else None
+        x2d = x.view(-1, x.shape[-1])
+        M, N = x2d.shape[0], self.weight.shape[1]
+        comm = getattr(self, "symm_comm", None)
+        if (comm is not None and x.is_cuda and mode in ("int8", "fp8") and comm.fits_scatter_rmsnorm_allgather(M, N, x.dtype)
+                and isinstance(self.quant_method, (W8A8Int8LinearMethod, W8A8Fp8LinearMethod))):
+            with capi.static_weights():
+                if isinstance(self.quant_method, W8A8Int8LinearMethod):
+                    q, s = ops.per_token_quant_int8(x2d)
+                else:
+                    q, s = ops.sglang_per_token_quant_fp8(x2d)
+                comm.scatter_gemm(q, self.weight, s.view(-1), self.weight_scale.view(-1), x.dtype, bias)
+                return comm.reduce_scattered_rmsnorm_quant_allgather(M, N, x.dtype, norm_weight, eps,
+                                                                     residual_local=residual_local, mode=mode)
+        rows = self.forward_reduce_scatter(x)
+        ql, sl = ops.rmsnorm_quant(rows, norm_weight, eps, residual=residual_local, mode=mode)
+        q_all = torch.empty(M, N, dtype=ql.dtype, device=x.device)
+        s_all = torch.empty(M, 1, dtype=torch.float32, device=x.device)
+        dist.all_gather_into_tensor(q_all.view(torch.uint8), ql.view(torch.uint8).contiguous(), group=self.tp_group)
+        dist.all_gather_into_tensor(s_all, sl.contiguous(), group=self.tp_group)
+        return q_all, s_all
+
     def forward_reduce_scatter(self, x: torch.Tensor) -> torch.Tensor:
         """Row-parallel layer whose summed output is wanted ROW-SHARDED: returns rows [tp_rank * M/tp, (tp_rank+1) * M/tp)
         of the sum -- RowParallelLinear.forward(skip_all_reduce=True) followed by LayerCommunicator._tp_reduce_scatter

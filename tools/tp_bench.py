@@ -130,6 +130,28 @@ def main():
                 assert (y1.float() - y2.float()).abs().max().item() <= 2.0 ** -5 * y2.float().abs().max().item(), name
                 d1, d2 = q1.float() * s1, q2.float() * s2
                 assert (d1 - d2).abs().max().item() <= 0.08 * d2.abs().max().item(), name
+            if check and par == "row" and world > 1 and M % world == 0:
+                # sequence-parallel norm form against the all-reduce composition on this rank's rows, and the
+                # all-gathered codes equal on every rank
+                gn = torch.Generator(device=dev).manual_seed(78)
+                wn = (torch.rand(N, generator=gn, device=dev) + 0.5).bfloat16()
+                rows = M // world
+                res = torch.randn(M, N, generator=gn, device=dev).bfloat16()[rank * rows:(rank + 1) * rows]
+                r1, r2 = res.clone(), res.clone()
+                mode = "int8" if int8 else "fp8"
+                full = layer(x).clone()
+                q1, s1 = layer.forward_reduce_scatter_rmsnorm_quant(x, wn, 1e-6, residual_local=r1, mode=mode)
+                q1, s1 = q1.clone(), s1.clone()
+                q2, s2 = b2.ops.rmsnorm_quant(full[rank * rows:(rank + 1) * rows].contiguous(), wn, 1e-6, residual=r2, mode=mode)
+                torch.cuda.synchronize()
+                assert (r1.float() - r2.float()).abs().max().item() <= 2.0 ** -6 * r2.float().abs().max().item(), name
+                d1 = q1[rank * rows:(rank + 1) * rows].float() * s1[rank * rows:(rank + 1) * rows]
+                d2 = q2.float() * s2
+                assert (d1 - d2).abs().max().item() <= 0.08 * d2.abs().max().item(), name
+                q0 = q1.view(torch.uint8).clone()
+                dist.broadcast(q0, 0)
+                assert torch.equal(q0, q1.view(torch.uint8)), name
+                dist.barrier()
             iters = 200 if M == 64 else 30
             t_all = timed(lambda: layer(x), iters)
             t_mm = timed(lambda: method.apply(layer, x, None), iters)

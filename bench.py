@@ -427,6 +427,64 @@ def tp_leg(b2, dev, dist, world, rank, comm):
             for *_, layer in layers:
                 layer.symm_comm = None
             res["nvlink_bytes_out_per_rank_per_row_layer_reduce_scatter"] = (world - 1) * M * 8192 * 2 // world
+        # row-parallel layer -> all-reduce -> fused_add_rmsnorm -> quantizer of the next layer (what a decoder block does
+        # behind o_proj / down_proj): NCCL all-reduce + the fused norm/quant kernel against the library's two launches
+        # (decode: pushed GEMM + gathered sum/norm/quant; prefill: scatter GEMM + sequence-parallel sum/norm/quant +
+        # all-gather of the codes by peer stores)
+        try:
+            from sglang_diffusion_b200 import ops as _ops
+            gn = torch.Generator(device=dev).manual_seed(7)
+            wn = (torch.rand(8192, generator=gn, device=dev) + 0.5).bfloat16()
+            res_full = torch.randn(M, 8192, generator=gn, device=dev).bfloat16()
+            seq_par = M > 128
+            can_fuse = comm is not None and M % world == 0 and (
+                comm.fits_scatter_rmsnorm_allgather(M, 8192, torch.bfloat16) if seq_par
+                else comm.fits_reduce_rmsnorm(M, 8192, torch.bfloat16))
+            rows_loc = M // world if M % world == 0 else 0
+            res_loc = res_full[rank * rows_loc:(rank + 1) * rows_loc].clone()
+            chain = {}
+            for mode in ("nccl_allreduce+rmsnorm_quant", "b2_fused_norm_chain"):
+                fused = mode == "b2_fused_norm_chain"
+                if fused and not can_fuse:
+                    chain[mode] = None
+                    continue
+                per_layer = {}
+                for x, (name, par, K, N, _, layer) in zip(xs, layers):
+                    if par != "row":
+                        continue
+                    layer.symm_comm = comm if fused else None
+                    if not fused:
+                        fn = lambda: _ops.rmsnorm_quant(layer(x), wn, 1e-6, residual=res_full, mode="fp8")  # noqa: E731
+                    elif seq_par:
+                        fn = lambda: layer.forward_reduce_scatter_rmsnorm_quant(x, wn, 1e-6, residual_local=res_loc, mode="fp8")  # noqa: E731
+                    else:
+                        fn = lambda: layer.forward_allreduce_rmsnorm_quant(x, wn, 1e-6, residual=res_full, mode="fp8")  # noqa: E731
+                    per_layer[name] = round(_time_device(fn, dev, dist, world, 100 if M <= 64 else 5,
+                                                         graph_inner=10 if M <= 64 else 0) * 1e3, 1)
+                    layer.symm_comm = None
+                chain[mode] = {"us_per_row_layer_incl_norm_and_quant": per_layer}
+            if can_fuse:  # parity of the fused chain against the NCCL composition (other summation order: a few bf16 ulps)
+                for x, (name, par, K, N, _, layer) in zip(xs, layers):
+                    if par != "row":
+                        continue
+                    r1 = res_full.clone()
+                    q1, s1 = _ops.rmsnorm_quant(layer(x), wn, 1e-6, residual=r1, mode="fp8")
+                    layer.symm_comm = comm
+                    if seq_par:
+                        q2, s2 = layer.forward_reduce_scatter_rmsnorm_quant(x, wn, 1e-6, residual_local=res_loc.clone(), mode="fp8")
+                    else:
+                        q2, s2 = layer.forward_allreduce_rmsnorm_quant(x, wn, 1e-6, residual=res_full.clone(), mode="fp8")
+                    layer.symm_comm = None
+                    d1, d2 = q1.float() * s1, q2.float() * s2
+                    err = ((d1 - d2).abs().max() / d1.abs().max()).item()
+                    check["fused_norm_chain_vs_nccl_max_rel_err"] = max(check.get("fused_norm_chain_vs_nccl_max_rel_err", 0.0), round(err, 5))
+                    check["ok"] = check["ok"] and err < 0.15  # one e4m3 step (2^-3 of the value) where a code sits on a rounding boundary
+                    dist.barrier()
+            res["norm_chain"] = chain
+        except Exception as e:  # noqa: BLE001  (a leg that cannot run must not take the headline down)
+            res["norm_chain_error"] = f"{type(e).__name__}: {e}"
+            for *_, layer in layers:
+                layer.symm_comm = None
         res["allreduce_bytes_per_row_layer"] = M * 8192 * 2
         rows.append(res)
     check["max_rel_err"] = round(check["max_rel_err"], 5)

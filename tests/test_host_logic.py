@@ -216,3 +216,74 @@ def test_tp2_and_dp2_composition_over_gloo(tmp_path):
     assert torch.equal(bf16_bits(res[0]["row"]), bf16_bits(want))
     # and it approximates the unsharded layer (different quantization grid per shard)
     torch.testing.assert_close(res[0]["row"].float(), full.float(), rtol=5e-2, atol=5e-2)
+
+
+# ------------------------------ row-parallel layer + norm + next quantizer, fallback composition over gloo ----
+
+def _oracle_rmsnorm_quant(x, weight, eps=1e-6, residual=None, mode="int8", return_normed=False):
+    """CPU stand-in for ops.rmsnorm_quant (oracle restatements): residual updated in place, int8 rows."""
+    assert mode == "int8"
+    y, new_res = restate.rmsnorm(x, weight, eps, residual)
+    if residual is not None:
+        residual.copy_(new_res)
+    q_u8, s = restate.per_token_quant_int8_cpu(y.contiguous())
+    q = (q_u8.to(torch.int16) - 128).to(torch.int8)
+    return (q, s.view(-1, 1), y) if return_normed else (q, s.view(-1, 1))
+
+
+def _norm_chain_worker(rank, world, port, outdir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from sglang_diffusion_b200 import linear as lin
+
+        lin.ops.rmsnorm_quant = _oracle_rmsnorm_quant  # this process only
+        M, N, K = 6, 64, 256
+        x, W, Bs, bias = mk_int8_problem(M, N, K, seed=78)
+        g = torch.Generator().manual_seed(5)
+        wn = (torch.rand(N, generator=g) + 0.5).bfloat16()
+        res_full = torch.randn(M, N, generator=g).bfloat16()
+        row = b2.QuantLinear(K, N, OracleInt8Method(), bias=True, parallel="row", tp_rank=rank, tp_size=world)
+        row.weight.data.copy_(row.shard_of(W))
+        row.weight_scale.data.copy_(Bs.view(-1, 1))
+        row.bias.data.copy_(bias)
+        row.quant_method.process_weights_after_loading(row)
+        k0 = rank * (K // world)
+        xs = x[:, k0:k0 + K // world].contiguous()
+        rows = M // world
+        summed = row(xs).clone()
+        rs = row.forward_reduce_scatter(xs)
+        r_ar = res_full.clone()
+        q_ar, s_ar = row.forward_allreduce_rmsnorm_quant(xs, wn, 1e-6, residual=r_ar, mode="int8")
+        r_sp = res_full[rank * rows:(rank + 1) * rows].clone()
+        q_sp, s_sp = row.forward_reduce_scatter_rmsnorm_quant(xs, wn, 1e-6, residual_local=r_sp, mode="int8")
+        torch.save({"summed": summed, "rs": rs, "q_ar": q_ar, "s_ar": s_ar, "r_ar": r_ar, "q_sp": q_sp, "s_sp": s_sp,
+                    "r_sp": r_sp}, os.path.join(outdir, f"n{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_row_parallel_norm_chain_fallbacks_over_gloo(tmp_path):
+    """QuantLinear.forward_reduce_scatter / forward_allreduce_rmsnorm_quant / forward_reduce_scatter_rmsnorm_quant
+    without a peer-memory communicator (the composition every rank count and dtype can fall back to): reduce-scatter
+    rows equal the all-reduce's rows; the all-reduce form equals norm + quantizer of the summed rows on every rank; the
+    sequence-parallel form gathers exactly the same codes and scales, and each rank's residual rows match."""
+    world = 2
+    mp.spawn(_norm_chain_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    res = [torch.load(os.path.join(tmp_path, f"n{r}.pt")) for r in range(world)]
+    M, N = 6, 64
+    rows = M // world
+    g = torch.Generator().manual_seed(5)
+    wn = (torch.rand(N, generator=g) + 0.5).bfloat16()
+    res_full = torch.randn(M, N, generator=g).bfloat16()
+    summed = res[0]["summed"]
+    assert torch.equal(bf16_bits(summed), bf16_bits(res[1]["summed"]))
+    want_res = res_full.clone()
+    want_q, want_s = _oracle_rmsnorm_quant(summed, wn, 1e-6, residual=want_res)
+    for r in range(world):
+        assert torch.equal(bf16_bits(res[r]["rs"]), bf16_bits(summed[r * rows:(r + 1) * rows]))
+        assert torch.equal(res[r]["q_ar"], want_q) and torch.equal(res[r]["s_ar"], want_s)
+        assert torch.equal(bf16_bits(res[r]["r_ar"]), bf16_bits(want_res))
+        assert torch.equal(res[r]["q_sp"], want_q) and torch.equal(res[r]["s_sp"], want_s)
+        assert torch.equal(bf16_bits(res[r]["r_sp"]), bf16_bits(want_res[r * rows:(r + 1) * rows]))
